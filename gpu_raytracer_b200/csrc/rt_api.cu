@@ -1,0 +1,694 @@
+// rt_api.cu — the C ABI of librtb200.so (include/rtb200.h): context, buffer
+// manager, upload-time validation + device re-layout, dispatch, read-back.
+//
+// Mirrors the reference's dispatch surface: BufferManager (src/buffers.rs) and
+// ComputeRenderer (src/compute.rs) with ProgressiveState (src/renderer.rs:821-855).
+// There is no CPU fallback anywhere in this file: every render entry point
+// launches rt_trace_shade / rt_path_trace on the context's CUDA stream.
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+#include <string>
+#include <vector>
+
+#include "rt_kernels.cuh"
+
+namespace {
+
+thread_local std::string g_create_error;
+
+template <class T>
+struct DevBuf {
+    T* ptr = nullptr;
+    size_t capacity = 0; // elements
+    ~DevBuf() { if (ptr) cudaFree(ptr); }
+    // returns 1 if reallocated, 0 if not, <0 cuda error
+    int reserve(size_t n) {
+        if (n <= capacity && ptr) return 0;
+        if (ptr) { cudaFree(ptr); ptr = nullptr; capacity = 0; }
+        size_t cap = n ? n : 1;
+        cudaError_t e = cudaMalloc((void**)&ptr, cap * sizeof(T));
+        if (e != cudaSuccess) return -1;
+        capacity = cap;
+        return 1;
+    }
+};
+
+struct WideBvh { // host-side result of validation + node re-layout
+    bool ordered_ok = false;
+    std::string why_not;
+    std::vector<float4> nodes;      // 4 per internal node
+    std::vector<uint2> leaves;      // (start, effective count) of every reachable non-empty leaf
+    uint32_t root_ref = RT_CHILD_ABSENT;
+    float root_min[3] = {0, 0, 0}, root_max[3] = {0, 0, 0};
+    uint32_t max_depth = 0;
+};
+
+} // namespace
+
+struct RtContext {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    bool timed = false;
+    std::string err;
+    uint64_t launches = 0;
+    int last_traversal = 0;
+
+    // BufferManager state (src/buffers.rs:13-45)
+    DevBuf<uint32_t> meta;
+    size_t meta_len = 0; // u32
+    size_t scene_metadata_capacity_bytes = 0;
+    RtSceneMetadataOffsets offsets{};
+    bool have_meta = false;
+    DevBuf<RtTriangle> tris;
+    size_t n_tris = 0;
+    size_t tri_buffers = 1; // reference starts with one bound buffer (src/buffers.rs:92-99)
+    DevBuf<RtMaterial> mats;
+    size_t n_mats = 0, mats_capacity = 64;
+    DevBuf<RtTextureInfo> textures;
+    size_t n_textures = 0, textures_capacity = 64;
+    DevBuf<uint32_t> texdata;
+    size_t texdata_len = 0, texdata_capacity = 256 * 1024;
+    bool meta_dirty = true, tris_dirty = true, mats_dirty = true, tex_dirty = true, texdata_dirty = true;
+    size_t last_spheres = 0, last_lights = 0, last_nodes = 0, last_indices = 0, last_vertices = 0,
+           last_tris = 0, last_mats = 0, last_textures = 0, last_texdata = 0;
+
+    // re-laid-out scene for the ORDERED policy
+    WideBvh wide;
+    DevBuf<float4> wnodes;
+    DevBuf<float4> wtris;
+    DevBuf<uint2> wleaves;
+    DevBuf<uint32_t> dflag;
+    bool relayout_dirty = true;
+    bool relayout_ok = false;
+
+    // outputs (src/renderer.rs:452-475) + progressive state (src/renderer.rs:821-855)
+    uint32_t width = 0, height = 0;
+    DevBuf<float4> accum;
+    DevBuf<RtHitRecord> hits;
+    DevBuf<uchar4> chan[3];
+    DevBuf<uchar4> composite;
+    uint32_t tiles_x = 0, tiles_y = 0, tiles_per_frame = 0, current_tile = 0;
+    bool needs_recompute = true, is_progressive = false;
+};
+
+namespace {
+
+int fail(RtContext* c, int code, const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    if (c) c->err = buf; else g_create_error = buf;
+    return code;
+}
+#define CK(c, call)                                                                         \
+    do {                                                                                    \
+        cudaError_t e_ = (call);                                                            \
+        if (e_ != cudaSuccess)                                                              \
+            return fail(c, RT_ERR_CUDA, "%s failed: %s", #call, cudaGetErrorString(e_));    \
+    } while (0)
+
+// Walks the uploaded BVH exactly as the reference's DFS would if every box were
+// hit (shader/src/bvh.rs:40-85) and emits the two-child node layout.  The ORDERED
+// policy is enabled only if that walk is a tree (no node reached twice), stays
+// shallower than the reference's 63-entry stack limit (so the `stack_ptr < 63`
+// quirk can never trigger), and visits leaves in non-overlapping, increasing
+// triangle_start order (so "first in DFS order" == "smaller position").
+void build_wide(const RtBvhNode* nodes, uint32_t n_nodes, uint32_t n_indices, WideBvh& w) {
+    w = WideBvh();
+    if (n_nodes == 0) { w.why_not = "no BVH nodes (brute-force path)"; return; }
+    auto eff_count = [&](const RtBvhNode& nd) -> uint32_t {
+        if (nd.triangle_start >= n_indices) return 0u; // bvh.rs:109-111 break
+        uint64_t room = (uint64_t)n_indices - nd.triangle_start;
+        return (uint32_t)(nd.triangle_count < room ? nd.triangle_count : room);
+    };
+    auto is_leaf = [&](const RtBvhNode& nd) { return nd.left_child == RT_INVALID_INDEX; }; // bvh.rs:60
+    auto valid_child = [&](uint32_t c) { return c != RT_INVALID_INDEX && c < n_nodes; };   // bvh.rs:45
+    std::vector<uint32_t> wide_index(n_nodes, 0xFFFFFFFFu);
+    std::vector<uint8_t> seen(n_nodes, 0);
+    struct Item { uint32_t node, depth; };
+    std::vector<Item> stack;
+    stack.push_back({0u, 0u});
+    uint64_t prev_end = 0;
+    uint32_t n_internal = 0;
+    // pass 1: DFS in reference order; number internal nodes; check leaves
+    while (!stack.empty()) {
+        Item it = stack.back();
+        stack.pop_back();
+        const RtBvhNode& nd = nodes[it.node];
+        if (seen[it.node]) { w.why_not = "BVH is not a tree (node reachable twice)"; return; }
+        seen[it.node] = 1;
+        if (it.depth > w.max_depth) w.max_depth = it.depth;
+        if (it.depth >= 60) { w.why_not = "BVH deeper than 60 levels"; return; }
+        if (is_leaf(nd)) {
+            uint32_t cnt = eff_count(nd);
+            if (cnt) {
+                if (nd.triangle_start < prev_end) { w.why_not = "leaf ranges not increasing in DFS order"; return; }
+                prev_end = (uint64_t)nd.triangle_start + cnt;
+                if (nd.triangle_start & RT_LEAF_FLAG) { w.why_not = "triangle_start >= 2^31"; return; }
+                w.leaves.push_back(make_uint2(nd.triangle_start, cnt));
+            }
+        } else {
+            wide_index[it.node] = n_internal++;
+            if (valid_child(nd.right_child)) stack.push_back({nd.right_child, it.depth + 1});
+            if (valid_child(nd.left_child)) stack.push_back({nd.left_child, it.depth + 1});
+        }
+    }
+    auto ref_of = [&](uint32_t c) -> uint32_t {
+        if (!valid_child(c)) return RT_CHILD_ABSENT;
+        const RtBvhNode& nd = nodes[c];
+        if (is_leaf(nd)) return eff_count(nd) ? (RT_LEAF_FLAG | nd.triangle_start) : RT_CHILD_ABSENT;
+        return wide_index[c];
+    };
+    auto as_f = [](uint32_t u) { float f; memcpy(&f, &u, 4); return f; };
+    w.nodes.assign((size_t)n_internal * 4, make_float4(0, 0, 0, 0));
+    const float inf = INFINITY;
+    for (uint32_t i = 0; i < n_nodes; i++) {
+        if (wide_index[i] == 0xFFFFFFFFu) continue;
+        const RtBvhNode& nd = nodes[i];
+        float lmin[3] = {inf, inf, inf}, lmax[3] = {-inf, -inf, -inf}, rmin[3] = {inf, inf, inf},
+              rmax[3] = {-inf, -inf, -inf};
+        uint32_t lref = ref_of(nd.left_child), rref = ref_of(nd.right_child);
+        if (valid_child(nd.left_child)) { memcpy(lmin, nodes[nd.left_child].bounds.min, 12); memcpy(lmax, nodes[nd.left_child].bounds.max, 12); }
+        if (valid_child(nd.right_child)) { memcpy(rmin, nodes[nd.right_child].bounds.min, 12); memcpy(rmax, nodes[nd.right_child].bounds.max, 12); }
+        float4* q = &w.nodes[(size_t)wide_index[i] * 4];
+        q[0] = make_float4(lmin[0], lmin[1], lmin[2], lmax[0]);
+        q[1] = make_float4(lmax[1], lmax[2], rmin[0], rmin[1]);
+        q[2] = make_float4(rmin[2], rmax[0], rmax[1], rmax[2]);
+        q[3] = make_float4(as_f(lref), as_f(rref), 0.0f, 0.0f);
+    }
+    const RtBvhNode& root = nodes[0];
+    memcpy(w.root_min, root.bounds.min, 12);
+    memcpy(w.root_max, root.bounds.max, 12);
+    if (is_leaf(root)) w.root_ref = eff_count(root) ? (RT_LEAF_FLAG | root.triangle_start) : RT_CHILD_ABSENT;
+    else w.root_ref = wide_index[0];
+    w.ordered_ok = true;
+}
+
+// ---- device re-layout kernels -------------------------------------------------
+// One thread per triangle_indices position: gather the indexed triangle into
+// (v0, e1, e2, material, index).  e1 = v1 - v0 and e2 = v2 - v0 are the same two
+// IEEE subtractions intersection.rs:102-103 performs per test, hoisted to upload.
+__global__ void relayout_triangles(const uint32_t* __restrict__ meta, RtSceneMetadataOffsets off,
+                                   const RtTriangle* __restrict__ tris, uint64_t n_tris, uint32_t tpb,
+                                   float4* __restrict__ out, uint32_t* __restrict__ flag) {
+    uint32_t pos = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pos >= off.triangle_indices_count) return;
+    uint32_t ti = meta[(uint64_t)off.triangle_indices_offset + pos];
+    float4 a = make_float4(0, 0, 0, 0), b = a, c = a;
+    c.z = __uint_as_float(ti);
+    // triangle_access.rs:26-48: valid iff it falls inside one of the <=3 bound buffers
+    bool valid = ti < n_tris && (ti / tpb) <= 2u;
+    if (valid) {
+        RtTriangle t = tris[ti];
+        if (t.v0_index >= off.vertices_count || t.v1_index >= off.vertices_count || t.v2_index >= off.vertices_count) {
+            atomicOr(flag, 1u); // the reference would read out of bounds
+        } else {
+            const uint32_t* vb = meta + off.vertices_offset;
+            float v0x = __uint_as_float(vb[(uint64_t)t.v0_index * 3]), v0y = __uint_as_float(vb[(uint64_t)t.v0_index * 3 + 1]),
+                  v0z = __uint_as_float(vb[(uint64_t)t.v0_index * 3 + 2]);
+            float v1x = __uint_as_float(vb[(uint64_t)t.v1_index * 3]), v1y = __uint_as_float(vb[(uint64_t)t.v1_index * 3 + 1]),
+                  v1z = __uint_as_float(vb[(uint64_t)t.v1_index * 3 + 2]);
+            float v2x = __uint_as_float(vb[(uint64_t)t.v2_index * 3]), v2y = __uint_as_float(vb[(uint64_t)t.v2_index * 3 + 1]),
+                  v2z = __uint_as_float(vb[(uint64_t)t.v2_index * 3 + 2]);
+            a = make_float4(v0x, v0y, v0z, v1x - v0x);
+            b = make_float4(v1y - v0y, v1z - v0z, v2x - v0x, v2y - v0y);
+            c.x = v2z - v0z;
+            c.y = __uint_as_float(t.material_id);
+        }
+    }
+    c.w = __uint_as_float(1u); // `remaining`, fixed up per leaf below
+    out[(uint64_t)pos * 3] = a;
+    out[(uint64_t)pos * 3 + 1] = b;
+    out[(uint64_t)pos * 3 + 2] = c;
+}
+// One warp per leaf: remaining[start + i] = count - i.
+__global__ void relayout_leaf_counts(const uint2* __restrict__ leaves, uint32_t n_leaves, float4* __restrict__ out) {
+    uint32_t leaf = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31u;
+    if (leaf >= n_leaves) return;
+    uint2 l = leaves[leaf];
+    for (uint32_t i = lane; i < l.y; i += 32u)
+        reinterpret_cast<uint32_t*>(out + (uint64_t)(l.x + i) * 3 + 2)[3] = l.y - i;
+}
+
+} // namespace
+
+// =============================================================== C ABI ======
+extern "C" {
+
+int rt_create(int device, RtContext** out) {
+    if (!out) return fail(nullptr, RT_ERR_INVALID_ARGUMENT, "rt_create: out is NULL");
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0)
+        return fail(nullptr, RT_ERR_CUDA, "rt_create: no CUDA device (%s); this library has no CPU fallback",
+                    e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+    if (device < 0 || device >= count) return fail(nullptr, RT_ERR_INVALID_ARGUMENT, "rt_create: device %d of %d", device, count);
+    if ((e = cudaSetDevice(device)) != cudaSuccess) return fail(nullptr, RT_ERR_CUDA, "cudaSetDevice: %s", cudaGetErrorString(e));
+    RtContext* c = new RtContext();
+    c->device = device;
+    if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess ||
+        (e = cudaEventCreate(&c->ev0)) != cudaSuccess || (e = cudaEventCreate(&c->ev1)) != cudaSuccess) {
+        fail(nullptr, RT_ERR_CUDA, "rt_create: %s", cudaGetErrorString(e));
+        delete c;
+        return RT_ERR_CUDA;
+    }
+    // BufferManager::new default capacities, src/buffers.rs:66-84
+    c->scene_metadata_capacity_bytes = 64 * sizeof(RtSphere) + 32 * sizeof(RtLight) + 256 * sizeof(RtBvhNode) +
+                                       1024 * sizeof(uint32_t) + 1024 * sizeof(RtVertex);
+    if (c->meta.reserve(c->scene_metadata_capacity_bytes / 4) < 0 || c->mats.reserve(c->mats_capacity) < 0 ||
+        c->textures.reserve(c->textures_capacity) < 0 || c->texdata.reserve(c->texdata_capacity) < 0 ||
+        c->tris.reserve(64) < 0 || c->dflag.reserve(1) < 0) {
+        fail(nullptr, RT_ERR_CUDA, "rt_create: cudaMalloc failed");
+        delete c;
+        return RT_ERR_CUDA;
+    }
+    *out = c;
+    return RT_OK;
+}
+
+void rt_destroy(RtContext* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    if (c->stream) { cudaStreamSynchronize(c->stream); cudaStreamDestroy(c->stream); }
+    if (c->ev0) cudaEventDestroy(c->ev0);
+    if (c->ev1) cudaEventDestroy(c->ev1);
+    delete c;
+}
+
+const char* rt_last_error(const RtContext* c) { return c ? c->err.c_str() : g_create_error.c_str(); }
+
+int rt_resize(RtContext* c, uint32_t w, uint32_t h) {
+    if (!c) return RT_ERR_INVALID_ARGUMENT;
+    if (w == 0 || h == 0 || w > 65535u || h > 65535u) return fail(c, RT_ERR_INVALID_ARGUMENT, "rt_resize: %ux%u", w, h);
+    CK(c, cudaSetDevice(c->device));
+    size_t n = (size_t)w * h;
+    if (c->accum.reserve(n) < 0 || c->hits.reserve(n) < 0 || c->composite.reserve(n) < 0 || c->chan[0].reserve(n) < 0 ||
+        c->chan[1].reserve(n) < 0 || c->chan[2].reserve(n) < 0)
+        return fail(c, RT_ERR_CUDA, "rt_resize: cudaMalloc failed for %ux%u", w, h);
+    c->width = w; c->height = h;
+    CK(c, cudaMemsetAsync(c->accum.ptr, 0, n * sizeof(float4), c->stream));
+    CK(c, cudaMemsetAsync(c->hits.ptr, 0, n * sizeof(RtHitRecord), c->stream));
+    CK(c, cudaMemsetAsync(c->composite.ptr, 0, n * 4, c->stream));
+    for (int i = 0; i < 3; i++) CK(c, cudaMemsetAsync(c->chan[i].ptr, 0, n * 4, c->stream));
+    // ProgressiveState::resize, src/renderer.rs:838-848
+    rt_tile_count(w, h, RT_TILE_SIZE, &c->tiles_x, &c->tiles_y);
+    c->tiles_per_frame = rt_tiles_per_frame(c->tiles_x * c->tiles_y);
+    c->needs_recompute = true; c->current_tile = 0; c->is_progressive = false;
+    return RT_OK;
+}
+
+int rt_synchronize(RtContext* c) {
+    if (!c) return RT_ERR_INVALID_ARGUMENT;
+    CK(c, cudaSetDevice(c->device));
+    CK(c, cudaStreamSynchronize(c->stream));
+    return RT_OK;
+}
+
+int rt_update_scene_metadata(RtContext* c, const RtSphere* spheres, uint32_t ns, const RtLight* lights, uint32_t nl,
+                             const RtBvhNode* nodes, uint32_t nn, const uint32_t* tri_idx, uint32_t ni,
+                             const RtVertex* verts, uint32_t nv, RtSceneMetadataOffsets* out_offsets) {
+    if (!c) return RT_ERR_INVALID_ARGUMENT;
+    if ((ns && !spheres) || (nl && !lights) || (nn && !nodes) || (ni && !tri_idx) || (nv && !verts))
+        return fail(c, RT_ERR_INVALID_ARGUMENT, "rt_update_scene_metadata: NULL array with non-zero count");
+    CK(c, cudaSetDevice(c->device));
+    // src/buffers.rs:167-184
+    size_t ss = (size_t)ns * sizeof(RtSphere), ls = (size_t)nl * sizeof(RtLight), bs = (size_t)nn * sizeof(RtBvhNode),
+           is = (size_t)ni * 4, vs = (size_t)nv * sizeof(RtVertex);
+    size_t total = ss + ls + bs + is + vs;
+    if (total / 4 > 0xFFFFFFFFull) return fail(c, RT_ERR_INVALID_ARGUMENT, "scene metadata exceeds u32 offsets");
+    bool needs_resize = total > c->scene_metadata_capacity_bytes;
+    bool any_changed = ns != c->last_spheres || nl != c->last_lights || nn != c->last_nodes || ni != c->last_indices ||
+                       nv != c->last_vertices;
+    if (needs_resize) { // src/buffers.rs:186-204: double, with the default floors
+        size_t sc = (size_t)ns * 2 > 64 ? (size_t)ns * 2 : 64, lc = (size_t)nl * 2 > 32 ? (size_t)nl * 2 : 32,
+               bc = (size_t)nn * 2 > 256 ? (size_t)nn * 2 : 256, ic = (size_t)ni * 2 > 1024 ? (size_t)ni * 2 : 1024,
+               vc = (size_t)nv * 2 > 1024 ? (size_t)nv * 2 : 1024;
+        c->scene_metadata_capacity_bytes = sc * sizeof(RtSphere) + lc * sizeof(RtLight) + bc * sizeof(RtBvhNode) + ic * 4 +
+                                           vc * sizeof(RtVertex);
+        if (c->meta.reserve(c->scene_metadata_capacity_bytes / 4) < 0)
+            return fail(c, RT_ERR_CUDA, "scene metadata cudaMalloc(%zu) failed", c->scene_metadata_capacity_bytes);
+    }
+    if (c->meta_dirty || needs_resize || any_changed) { // src/buffers.rs:212-255
+        char* d = reinterpret_cast<char*>(c->meta.ptr);
+        size_t o = 0;
+        if (ss) CK(c, cudaMemcpyAsync(d + o, spheres, ss, cudaMemcpyHostToDevice, c->stream)); o += ss;
+        if (ls) CK(c, cudaMemcpyAsync(d + o, lights, ls, cudaMemcpyHostToDevice, c->stream)); o += ls;
+        if (bs) CK(c, cudaMemcpyAsync(d + o, nodes, bs, cudaMemcpyHostToDevice, c->stream)); o += bs;
+        if (is) CK(c, cudaMemcpyAsync(d + o, tri_idx, is, cudaMemcpyHostToDevice, c->stream)); o += is;
+        if (vs) CK(c, cudaMemcpyAsync(d + o, verts, vs, cudaMemcpyHostToDevice, c->stream));
+        // validation + node re-layout while the host arrays are still borrowed
+        build_wide(nodes, nn, ni, c->wide);
+        if (c->wide.ordered_ok) {
+            if (c->wnodes.reserve(c->wide.nodes.size()) < 0 || c->wleaves.reserve(c->wide.leaves.size()) < 0)
+                return fail(c, RT_ERR_CUDA, "wide BVH cudaMalloc failed");
+            if (!c->wide.nodes.empty())
+                CK(c, cudaMemcpyAsync(c->wnodes.ptr, c->wide.nodes.data(), c->wide.nodes.size() * sizeof(float4),
+                                      cudaMemcpyHostToDevice, c->stream));
+            if (!c->wide.leaves.empty())
+                CK(c, cudaMemcpyAsync(c->wleaves.ptr, c->wide.leaves.data(), c->wide.leaves.size() * sizeof(uint2),
+                                      cudaMemcpyHostToDevice, c->stream));
+        }
+        // pageable host memory: the copies above are staged before return, but the
+        // std::vectors must outlive the DMA -> wait here (upload is not the hot path)
+        CK(c, cudaStreamSynchronize(c->stream));
+        c->meta_len = total / 4;
+        c->meta_dirty = false;
+        c->relayout_dirty = true;
+        c->last_spheres = ns; c->last_lights = nl; c->last_nodes = nn; c->last_indices = ni; c->last_vertices = nv;
+    }
+    // src/buffers.rs:257-268
+    RtSceneMetadataOffsets off;
+    off.spheres_offset = 0; off.spheres_count = ns;
+    off.lights_offset = (uint32_t)(ss / 4); off.lights_count = nl;
+    off.bvh_nodes_offset = (uint32_t)((ss + ls) / 4); off.bvh_nodes_count = nn;
+    off.triangle_indices_offset = (uint32_t)((ss + ls + bs) / 4); off.triangle_indices_count = ni;
+    off.vertices_offset = (uint32_t)((ss + ls + bs + is) / 4); off.vertices_count = nv;
+    c->offsets = off;
+    c->have_meta = true;
+    if (out_offsets) *out_offsets = off;
+    return needs_resize ? 1 : 0;
+}
+
+int rt_update_triangles(RtContext* c, const RtTriangle* tris, uint64_t n) {
+    if (!c || (n && !tris)) return c ? fail(c, RT_ERR_INVALID_ARGUMENT, "rt_update_triangles: NULL") : RT_ERR_INVALID_ARGUMENT;
+    CK(c, cudaSetDevice(c->device));
+    // src/buffers.rs:274-303: one more bound buffer per RT_MAX_TRIANGLES_PER_BUFFER
+    size_t needed = (size_t)((n + RT_MAX_TRIANGLES_PER_BUFFER - 1) / RT_MAX_TRIANGLES_PER_BUFFER);
+    if (needed < 1) needed = 1;
+    bool needs_resize = false;
+    if (c->tri_buffers < needed) { c->tri_buffers = needed; needs_resize = true; }
+    bool changed = n != c->last_tris;
+    if (c->tris_dirty || needs_resize || changed) {
+        if (c->tris.reserve((size_t)n) < 0) return fail(c, RT_ERR_CUDA, "triangle cudaMalloc(%llu) failed", (unsigned long long)n);
+        if (n) CK(c, cudaMemcpyAsync(c->tris.ptr, tris, (size_t)n * sizeof(RtTriangle), cudaMemcpyHostToDevice, c->stream));
+        CK(c, cudaStreamSynchronize(c->stream));
+        c->n_tris = (size_t)n;
+        c->tris_dirty = false;
+        c->last_tris = (size_t)n;
+        c->relayout_dirty = true;
+    }
+    return needs_resize ? 1 : 0;
+}
+
+int rt_update_materials(RtContext* c, const RtMaterial* mats, uint64_t n) {
+    if (!c || (n && !mats)) return c ? fail(c, RT_ERR_INVALID_ARGUMENT, "rt_update_materials: NULL") : RT_ERR_INVALID_ARGUMENT;
+    CK(c, cudaSetDevice(c->device));
+    bool needs_resize = n > c->mats_capacity; // src/buffers.rs:339-352
+    if (needs_resize) {
+        c->mats_capacity = (size_t)n * 2 > 64 ? (size_t)n * 2 : 64;
+        if (c->mats.reserve(c->mats_capacity) < 0) return fail(c, RT_ERR_CUDA, "materials cudaMalloc failed");
+    }
+    if (c->mats_dirty || needs_resize || n != c->last_mats) {
+        if (n) CK(c, cudaMemcpyAsync(c->mats.ptr, mats, (size_t)n * sizeof(RtMaterial), cudaMemcpyHostToDevice, c->stream));
+        CK(c, cudaStreamSynchronize(c->stream));
+        c->n_mats = (size_t)n; c->mats_dirty = false; c->last_mats = (size_t)n;
+    }
+    return needs_resize ? 1 : 0;
+}
+
+int rt_update_textures(RtContext* c, const RtTextureInfo* tex, uint64_t n) {
+    if (!c || (n && !tex)) return c ? fail(c, RT_ERR_INVALID_ARGUMENT, "rt_update_textures: NULL") : RT_ERR_INVALID_ARGUMENT;
+    CK(c, cudaSetDevice(c->device));
+    bool needs_resize = n > c->textures_capacity; // src/buffers.rs:381-394
+    if (needs_resize) {
+        c->textures_capacity = (size_t)n * 2 > 64 ? (size_t)n * 2 : 64;
+        if (c->textures.reserve(c->textures_capacity) < 0) return fail(c, RT_ERR_CUDA, "textures cudaMalloc failed");
+    }
+    if (c->tex_dirty || needs_resize || n != c->last_textures) {
+        if (n) CK(c, cudaMemcpyAsync(c->textures.ptr, tex, (size_t)n * sizeof(RtTextureInfo), cudaMemcpyHostToDevice, c->stream));
+        CK(c, cudaStreamSynchronize(c->stream));
+        c->n_textures = (size_t)n; c->tex_dirty = false; c->last_textures = (size_t)n;
+    }
+    return needs_resize ? 1 : 0;
+}
+
+int rt_update_texture_data(RtContext* c, const uint8_t* bytes, uint64_t nb) {
+    if (!c || (nb && !bytes)) return c ? fail(c, RT_ERR_INVALID_ARGUMENT, "rt_update_texture_data: NULL") : RT_ERR_INVALID_ARGUMENT;
+    CK(c, cudaSetDevice(c->device));
+    // src/buffers.rs:422-432: 4 bytes little-endian per u32, last word zero-padded.
+    size_t words = (size_t)((nb + 3) / 4);
+    bool needs_resize = words > c->texdata_capacity;
+    if (needs_resize) {
+        c->texdata_capacity = words * 2 > 256 * 1024 ? words * 2 : 256 * 1024;
+        if (c->texdata.reserve(c->texdata_capacity) < 0) return fail(c, RT_ERR_CUDA, "texture data cudaMalloc failed");
+    }
+    if (c->texdata_dirty || needs_resize || nb != c->last_texdata) {
+        if (words) {
+            CK(c, cudaMemsetAsync(c->texdata.ptr + (words - 1), 0, 4, c->stream));
+            CK(c, cudaMemcpyAsync(c->texdata.ptr, bytes, (size_t)nb, cudaMemcpyHostToDevice, c->stream)); // x86 is LE
+        }
+        CK(c, cudaStreamSynchronize(c->stream));
+        c->texdata_len = words; c->texdata_dirty = false; c->last_texdata = (size_t)nb;
+    }
+    return needs_resize ? 1 : 0;
+}
+
+void rt_mark_scene_metadata_dirty(RtContext* c) { if (c) c->meta_dirty = true; }
+void rt_mark_triangles_dirty(RtContext* c) { if (c) c->tris_dirty = true; }
+void rt_mark_materials_dirty(RtContext* c) { if (c) c->mats_dirty = true; }
+void rt_mark_textures_dirty(RtContext* c) { if (c) c->tex_dirty = true; }
+void rt_mark_texture_data_dirty(RtContext* c) { if (c) c->texdata_dirty = true; }
+void rt_mark_all_dirty(RtContext* c) {
+    if (c) c->meta_dirty = c->tris_dirty = c->mats_dirty = c->tex_dirty = c->texdata_dirty = true;
+}
+int rt_needs_update(const RtContext* c) {
+    return c && (c->meta_dirty || c->tris_dirty || c->mats_dirty || c->tex_dirty || c->texdata_dirty) ? 1 : 0;
+}
+uint32_t rt_triangles_per_buffer(const RtContext*) { return RT_MAX_TRIANGLES_PER_BUFFER; }
+int rt_get_metadata_offsets(const RtContext* c, RtSceneMetadataOffsets* out) {
+    if (!c || !out || !c->have_meta) return RT_ERR_NOT_READY;
+    *out = c->offsets;
+    return RT_OK;
+}
+
+} // extern "C"
+
+namespace {
+
+// Bring the ORDERED-policy buffers up to date (GPU gather of triangles).
+int prepare_relayout(RtContext* c) {
+    if (!c->relayout_dirty) return RT_OK;
+    c->relayout_ok = false;
+    if (c->have_meta && c->wide.ordered_ok) {
+        uint32_t ni = c->offsets.triangle_indices_count;
+        if (c->wtris.reserve((size_t)ni * 3 + 3) < 0) return fail(c, RT_ERR_CUDA, "wtris cudaMalloc failed");
+        CK(c, cudaMemsetAsync(c->dflag.ptr, 0, 4, c->stream));
+        if (ni) {
+            relayout_triangles<<<(ni + 255) / 256, 256, 0, c->stream>>>(c->meta.ptr, c->offsets, c->tris.ptr, c->n_tris,
+                                                                        RT_MAX_TRIANGLES_PER_BUFFER, c->wtris.ptr, c->dflag.ptr);
+            c->launches++;
+            uint32_t nl = (uint32_t)c->wide.leaves.size();
+            if (nl) {
+                relayout_leaf_counts<<<(nl * 32 + 255) / 256, 256, 0, c->stream>>>(c->wleaves.ptr, nl, c->wtris.ptr);
+                c->launches++;
+            }
+        }
+        uint32_t flag = 0;
+        CK(c, cudaMemcpyAsync(&flag, c->dflag.ptr, 4, cudaMemcpyDeviceToHost, c->stream));
+        CK(c, cudaStreamSynchronize(c->stream));
+        CK(c, cudaGetLastError());
+        if (flag & 1u) return fail(c, RT_ERR_INVALID_SCENE, "a triangle references a vertex index >= vertices_count");
+        c->relayout_ok = true;
+    }
+    c->relayout_dirty = false;
+    return RT_OK;
+}
+
+void fill_scene(RtContext* c, KParams& k) {
+    k.meta = c->meta.ptr; k.meta_len = c->meta_len; k.off = c->offsets;
+    k.tris = c->tris.ptr; k.n_tris = c->n_tris;
+    k.ctx_triangles_per_buffer = RT_MAX_TRIANGLES_PER_BUFFER;
+    k.mats = c->mats.ptr; k.n_mats = (uint32_t)c->n_mats;
+    k.wnodes = c->wnodes.ptr; k.wtris = c->wtris.ptr;
+    k.root_ref = c->wide.root_ref;
+    memcpy(k.root_min, c->wide.root_min, 12); memcpy(k.root_max, c->wide.root_max, 12);
+    k.accum = c->accum.ptr; k.hits = c->hits.ptr;
+    for (int i = 0; i < 3; i++) k.chan[i] = c->chan[i].ptr;
+    k.composite = c->composite.ptr;
+}
+
+void fill_camera(KParams& k, const RtCamera& cam) {
+    memcpy(k.cam_pos, cam.position, 12); memcpy(k.cam_dir, cam.direction, 12); memcpy(k.cam_up, cam.up, 12);
+    // ray.rs:34 / wavefront.rs:89 — evaluated once on the host with glibc tanf (the
+    // same function the oracle calls); CUDA's tanf is not bit-identical to it.
+    k.fov_scale = tanf(cam.fov * 0.5f * 3.14159265358979323846f / 180.0f);
+}
+
+int launch(RtContext* c, const KParams& k, uint32_t blocks, uint32_t traversal) {
+    if (blocks == 0) return RT_OK;
+    bool ordered;
+    if (traversal == RT_TRAVERSAL_LITERAL) ordered = false;
+    else {
+        // the ORDERED layout bakes in the context's buffer split; a dispatch whose
+        // push constants carry another triangles_per_buffer takes the literal path
+        ordered = c->relayout_ok && k.off.bvh_nodes_count > 0 && k.triangles_per_buffer == RT_MAX_TRIANGLES_PER_BUFFER &&
+                  memcmp(&k.off, &c->offsets, sizeof(RtSceneMetadataOffsets)) == 0;
+        if (!ordered && traversal == RT_TRAVERSAL_ORDERED)
+            return fail(c, RT_ERR_INVALID_SCENE, "ordered traversal unavailable: %s",
+                        c->wide.why_not.empty() ? "push constants differ from the uploaded scene" : c->wide.why_not.c_str());
+    }
+    CK(c, cudaEventRecord(c->ev0, c->stream));
+    if (ordered) rt_trace_shade<true><<<blocks, 256, 0, c->stream>>>(k);
+    else rt_trace_shade<false><<<blocks, 256, 0, c->stream>>>(k);
+    CK(c, cudaGetLastError());
+    CK(c, cudaEventRecord(c->ev1, c->stream));
+    c->timed = true;
+    c->launches++;
+    c->last_traversal = ordered ? RT_TRAVERSAL_ORDERED : RT_TRAVERSAL_LITERAL;
+    return RT_OK;
+}
+
+int check_ready(RtContext* c) {
+    if (!c) return RT_ERR_INVALID_ARGUMENT;
+    if (c->width == 0) return fail(c, RT_ERR_NOT_READY, "rt_resize has not been called");
+    if (!c->have_meta) return fail(c, RT_ERR_NOT_READY, "rt_update_scene_metadata has not been called");
+    return RT_OK;
+}
+
+} // namespace
+
+extern "C" {
+
+int rt_dispatch(RtContext* c, const RtPushConstants* pc) {
+    int r = check_ready(c);
+    if (r) return r;
+    if (!pc) return fail(c, RT_ERR_INVALID_ARGUMENT, "rt_dispatch: pc is NULL");
+    uint32_t channel = rt_pc_color_channel(pc);
+    // src/compute.rs:227-229: get_compute_bind_group(channel).expect("Invalid color channel")
+    if (channel > 2u) return fail(c, RT_ERR_INVALID_CHANNEL, "Invalid color channel %u", channel);
+    if ((uint32_t)pc->resolution[0] != c->width || (uint32_t)pc->resolution[1] != c->height)
+        return fail(c, RT_ERR_INVALID_ARGUMENT, "push-constant resolution %gx%g != output size %ux%u", pc->resolution[0],
+                    pc->resolution[1], c->width, c->height);
+    CK(c, cudaSetDevice(c->device));
+    if ((r = prepare_relayout(c)) != RT_OK) return r;
+    KParams k;
+    memset(&k, 0, sizeof k);
+    fill_scene(c, k);
+    k.off = pc->metadata_offsets; // the shader trusts the push constants (scene_access.rs)
+    // offsets pointing outside the uploaded buffer read as 0 (meta_at bounds check)
+    k.width = c->width; k.height = c->height; k.res_x = pc->resolution[0]; k.res_y = pc->resolution[1];
+    fill_camera(k, pc->camera);
+    k.rect_x0 = pc->tile_offset[0]; k.rect_y0 = pc->tile_offset[1];
+    k.rect_w = pc->tile_size_packed & 0xFFFFu; k.rect_h = (pc->tile_size_packed >> 16) & 0xFFFFu;
+    k.use_tiles = 0;
+    k.mode = rt_pc_wavefront_mode(pc) != 0 ? RT_MODE_WAVEFRONT0 : RT_MODE_LEGACY;
+    k.cur_depth = rt_pc_current_bounce(pc); k.max_depth = rt_pc_max_bounce(pc);
+    k.outputs = RT_OUT_CHANNELS | RT_OUT_HITS | RT_OUT_ACCUM;
+    k.channel = channel;
+    k.triangles_per_buffer = pc->triangles_per_buffer;
+    k.triangle_count = pc->triangle_count;
+    k.n_mats = (uint32_t)c->n_mats; // materials.len() is the bound buffer's length (lib.rs:307)
+    uint32_t bw = (k.rect_w + 15u) / 16u, bh = (k.rect_h + 15u) / 16u; // src/compute.rs:248-250
+    return launch(c, k, bw * bh, RT_TRAVERSAL_AUTO);
+}
+
+int rt_render_frame(RtContext* c, const RtCamera* cam, const RtFrameParams* fp) {
+    int r = check_ready(c);
+    if (r) return r;
+    if (!cam || !fp) return fail(c, RT_ERR_INVALID_ARGUMENT, "rt_render_frame: NULL argument");
+    if (fp->mode != RT_MODE_LEGACY && fp->mode != RT_MODE_WAVEFRONT0)
+        return fail(c, RT_ERR_INVALID_ARGUMENT, "rt_render_frame: mode %u not available", fp->mode);
+    CK(c, cudaSetDevice(c->device));
+    if ((r = prepare_relayout(c)) != RT_OK) return r;
+    KParams k;
+    memset(&k, 0, sizeof k);
+    fill_scene(c, k);
+    k.width = c->width; k.height = c->height; k.res_x = (float)c->width; k.res_y = (float)c->height;
+    fill_camera(k, *cam);
+    k.use_tiles = 1;
+    k.tiles_x = c->tiles_x; k.n_tiles_total = c->tiles_x * c->tiles_y;
+    k.tile_stride = fp->tile_stride ? fp->tile_stride : 1u;
+    k.tile_phase = fp->tile_stride ? fp->tile_phase : 0u;
+    if (k.tile_phase >= k.tile_stride) return fail(c, RT_ERR_INVALID_ARGUMENT, "tile_phase >= tile_stride");
+    k.mode = fp->mode; k.outputs = fp->outputs; k.channel = 0xFFu;
+    k.cur_depth = 0; k.max_depth = 4; // PushConstants::new, shared/src/lib.rs:1088
+    k.reset_accum = fp->reset_accum;
+    k.triangles_per_buffer = RT_MAX_TRIANGLES_PER_BUFFER;
+    k.triangle_count = (uint32_t)c->n_tris;
+    uint32_t my_tiles = k.n_tiles_total > k.tile_phase ? (k.n_tiles_total - k.tile_phase + k.tile_stride - 1) / k.tile_stride : 0;
+    return launch(c, k, my_tiles * 64u, fp->traversal);
+}
+
+int rt_run_compute(RtContext* c, const RtCamera* cam, int needs_recompute) {
+    int r = check_ready(c);
+    if (r) return r;
+    if (!cam) return fail(c, RT_ERR_INVALID_ARGUMENT, "rt_run_compute: camera is NULL");
+    if (needs_recompute) { c->needs_recompute = true; c->current_tile = 0; c->is_progressive = false; } // trigger_recompute
+    // handle_progressive_rendering_setup, src/compute.rs:53-82
+    if (c->needs_recompute && !c->is_progressive) { c->is_progressive = true; c->current_tile = 0; c->needs_recompute = false; }
+    if (!c->is_progressive) return 0;
+    uint32_t total = c->tiles_x * c->tiles_y;
+    if (c->current_tile >= total) { c->is_progressive = false; return 0; } // check_rendering_completion :85-100
+    uint32_t remaining = total - c->current_tile;
+    uint32_t this_frame = c->tiles_per_frame < remaining ? c->tiles_per_frame : remaining; // :103-106
+    for (uint32_t i = 0; i < this_frame; i++) { // execute_compute_pass :157-162
+        uint32_t tile = c->current_tile + i;
+        uint32_t tx = tile % c->tiles_x, ty = tile / c->tiles_x; // calculate_tile_dimensions :194-209
+        uint32_t ox = tx * RT_TILE_SIZE, oy = ty * RT_TILE_SIZE;
+        uint32_t tw = RT_TILE_SIZE < c->width - ox ? RT_TILE_SIZE : c->width - ox;
+        uint32_t th = RT_TILE_SIZE < c->height - oy ? RT_TILE_SIZE : c->height - oy;
+        for (uint32_t ch = 0; ch < 3; ch++) { // process_tile :184-190
+            RtPushConstants pc; // PushConstants::new, src/compute.rs:232-243
+            memset(&pc, 0, sizeof pc);
+            pc.resolution[0] = (float)c->width; pc.resolution[1] = (float)c->height;
+            pc.camera = *cam;
+            pc.triangle_count = (uint32_t)c->n_tris; pc.material_count = (uint32_t)c->n_mats;
+            pc.tile_offset[0] = ox; pc.tile_offset[1] = oy;
+            pc.tile_size_packed = rt_pack_tile_size(tw, th);
+            pc.total_tiles[0] = c->tiles_x; pc.total_tiles[1] = c->tiles_y;
+            pc.triangles_per_buffer = RT_MAX_TRIANGLES_PER_BUFFER;
+            pc.metadata_offsets = c->offsets;
+            pc.packed_flags = rt_pack_flags(ch, 0, 4, 0);
+            pc.frame_seed = 0;
+            if ((r = rt_dispatch(c, &pc)) != RT_OK) return r;
+        }
+    }
+    c->current_tile += this_frame;
+    return (int)(total - c->current_tile);
+}
+
+static int read_back(RtContext* c, void* dst, const void* src, size_t bytes) {
+    if (!c || !dst) return RT_ERR_INVALID_ARGUMENT;
+    if (c->width == 0) return fail(c, RT_ERR_NOT_READY, "rt_resize has not been called");
+    CK(c, cudaSetDevice(c->device));
+    CK(c, cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, c->stream));
+    CK(c, cudaStreamSynchronize(c->stream));
+    return RT_OK;
+}
+int rt_read_channel_rgba8(RtContext* c, uint32_t channel, void* dst) {
+    if (!c) return RT_ERR_INVALID_ARGUMENT;
+    if (channel > 2u) return fail(c, RT_ERR_INVALID_CHANNEL, "Invalid color channel %u", channel);
+    return read_back(c, dst, c->chan[channel].ptr, (size_t)c->width * c->height * 4);
+}
+int rt_read_composite_rgba8(RtContext* c, void* dst) { return c ? read_back(c, dst, c->composite.ptr, (size_t)c->width * c->height * 4) : RT_ERR_INVALID_ARGUMENT; }
+int rt_read_accum_f32(RtContext* c, void* dst) { return c ? read_back(c, dst, c->accum.ptr, (size_t)c->width * c->height * 16) : RT_ERR_INVALID_ARGUMENT; }
+int rt_read_hit_records(RtContext* c, void* dst) { return c ? read_back(c, dst, c->hits.ptr, (size_t)c->width * c->height * 16) : RT_ERR_INVALID_ARGUMENT; }
+int rt_write_accum_f32(RtContext* c, const void* src) {
+    if (!c || !src) return RT_ERR_INVALID_ARGUMENT;
+    if (c->width == 0) return fail(c, RT_ERR_NOT_READY, "rt_resize has not been called");
+    CK(c, cudaSetDevice(c->device));
+    CK(c, cudaMemcpyAsync(c->accum.ptr, src, (size_t)c->width * c->height * 16, cudaMemcpyHostToDevice, c->stream));
+    CK(c, cudaStreamSynchronize(c->stream));
+    return RT_OK;
+}
+void* rt_device_accum(RtContext* c) { return c ? c->accum.ptr : nullptr; }
+void* rt_device_composite(RtContext* c) { return c ? c->composite.ptr : nullptr; }
+float rt_last_kernel_ms(RtContext* c) {
+    if (!c || !c->timed) return -1.0f;
+    cudaSetDevice(c->device);
+    if (cudaEventSynchronize(c->ev1) != cudaSuccess) return -1.0f;
+    float ms = -1.0f;
+    if (cudaEventElapsedTime(&ms, c->ev0, c->ev1) != cudaSuccess) return -1.0f;
+    return ms;
+}
+uint64_t rt_launch_count(const RtContext* c) { return c ? c->launches : 0; }
+int rt_last_traversal(const RtContext* c) { return c ? c->last_traversal : 0; }
+
+} // extern "C"

@@ -1,0 +1,503 @@
+// rt_kernels.cuh — device code of the per-pixel ray tracing path (sm_100a).
+//
+// Replaces the reference compute shader `main_cs` (shader/src/lib.rs:25-89) and
+// everything it calls.  Two closest-hit policies produce identical results:
+//   * LITERAL: the reference's own traversal — unordered, un-pruned stack DFS
+//     over the 48-byte BvhNode array read from the scene-metadata buffer
+//     (shader/src/bvh.rs:18-133), including the `stack_ptr < 63` quirk.
+//   * ORDERED: near-first, conservatively t-pruned traversal over a 64-byte
+//     two-child node layout and 48-byte pre-gathered triangles built at upload
+//     (rt_api.cu), fetched with 128-bit loads.  Equal-t ties are resolved as the
+//     reference's visit order would ("first in DFS order wins" == smaller
+//     position in triangle_indices), so primitive ids stay bit-exact.
+// No tensor cores: this is pointer chasing plus scalar fp32, not a contraction.
+#pragma once
+#include <cuda_fp16.h>
+#include <float.h>
+#include "../../include/rt_shared.h"
+#include "../../include/rtb200.h"
+#include "rt_math.cuh"
+
+#define RT_LEAF_FLAG 0x80000000u
+#define RT_CHILD_INTERNAL 0xFFFFFFFFu
+#define RT_CHILD_ABSENT 0xFFFFFFFEu
+// Conservative pruning margin of the ORDERED policy: a node is culled only if its
+// slab entry distance exceeds closest_t * RT_PRUNE_SCALE + RT_PRUNE_ABS.  The
+// margin absorbs the rounding difference between the slab t of a box face and the
+// Möller–Trumbore t of a triangle lying in that face (flat terrain triangles have
+// zero-thickness boxes), so a culled node can never hold the reference's winner.
+#define RT_PRUNE_SCALE 1.001f
+#define RT_PRUNE_ABS 1.0e-4f
+
+struct KParams {
+    // image + camera (push constants: shared/src/lib.rs:215-227)
+    uint32_t width, height;   // resolution as u32 (`resolution[i] as u32`)
+    float res_x, res_y;       // resolution as f32
+    float cam_pos[3], cam_dir[3], cam_up[3];
+    float fov_scale;          // tan(fov*0.5*PI/180), evaluated on the host (glibc tanf)
+    // work: pixel rectangle of one dispatch, or tiles of a fused frame
+    uint32_t rect_x0, rect_y0, rect_w, rect_h;
+    uint32_t tiles_x, n_tiles_total, tile_stride, tile_phase; // fused frame: 128x128 tile split
+    uint32_t use_tiles;       // 1: fused frame over tiles; 0: single rect
+    uint32_t mode;            // RT_MODE_*
+    uint32_t outputs;         // RT_OUT_*
+    uint32_t channel;         // single dispatch: colour channel (0..2, >2 = unfiltered); fused: ignored
+    uint32_t cur_depth, max_depth; // wavefront flags
+    uint32_t reset_accum;
+    // scene in the reference layout
+    const uint32_t* meta;
+    uint64_t meta_len;
+    RtSceneMetadataOffsets off;
+    const RtTriangle* tris;
+    uint64_t n_tris;
+    uint32_t triangles_per_buffer;     // value in the push constants
+    uint32_t ctx_triangles_per_buffer; // actual split of the bound buffers
+    uint32_t triangle_count;           // push_constants.triangle_count (brute-force loop bound)
+    const RtMaterial* mats;
+    uint32_t n_mats;
+    // re-laid-out scene (ORDERED policy)
+    const float4* wnodes;  // 4 x float4 per internal node
+    const float4* wtris;   // 3 x float4 per triangle position
+    uint32_t root_ref;     // internal index, or RT_LEAF_FLAG|start, or RT_CHILD_ABSENT
+    float root_min[3], root_max[3];
+    // outputs
+    float4* accum;
+    RtHitRecord* hits;
+    uchar4* chan[3];
+    uchar4* composite;
+};
+
+struct Ray {
+    V3 o, d;
+};
+
+struct Hit {
+    float t;
+    uint32_t kind;  // 0 miss 1 sphere 2 triangle
+    uint32_t prim;  // sphere index / triangle index
+    uint32_t material_id;
+    V3 point, normal;
+};
+
+__device__ __forceinline__ uint32_t meta_at(const KParams& p, uint64_t i) {
+    return i < p.meta_len ? __ldg(p.meta + i) : 0u;
+}
+__device__ __forceinline__ float meta_f(const KParams& p, uint64_t i) { return __uint_as_float(meta_at(p, i)); }
+
+// ---------------------------------------------------------------- camera rays
+// shader/src/ray.rs:22-53 (legacy: double normalise, u32 resolution) and
+// shader/src/wavefront.rs:75-112 (wavefront: single normalise, f32 resolution).
+__device__ __forceinline__ Ray camera_ray(const KParams& p, uint32_t px, uint32_t py, float jx, float jy,
+                                          bool wavefront) {
+    float w = wavefront ? p.res_x : (float)p.width;
+    float h = wavefront ? p.res_y : (float)p.height;
+    float u = ((float)px + jx) / w;
+    float v = ((float)py + jy) / h;
+    float aspect = w / h;
+    float cx = (u * 2.0f - 1.0f) * aspect * p.fov_scale;
+    float cy = (1.0f - v * 2.0f) * p.fov_scale;
+    V3 forward = mka(p.cam_dir), up = mka(p.cam_up);
+    V3 right = cross3(forward, up);
+    V3 true_up = cross3(right, forward);
+    V3 dir = forward + right * cx + true_up * cy;
+    V3 dn = normalize3(dir);
+    if (!wavefront) dn = normalize3(dn); // Ray::new normalises again (ray.rs:14-19)
+    Ray r;
+    r.o = mka(p.cam_pos);
+    r.d = dn;
+    return r;
+}
+
+// ---------------------------------------------------------------- primitives
+// shader/src/intersection.rs:52-87
+__device__ __forceinline__ bool sphere_t(const Ray& ray, V3 c, float r, float max_t, float* t_out) {
+    V3 oc = ray.o - c;
+    float a = dot3(ray.d, ray.d);
+    float b = 2.0f * dot3(oc, ray.d);
+    float cq = dot3(oc, oc) - r * r;
+    float disc = b * b - 4.0f * a * cq;
+    if (disc < 0.0f) return false;
+    float sq = sqrtf(disc);
+    float t1 = (-b - sq) / (2.0f * a);
+    float t2 = (-b + sq) / (2.0f * a);
+    float t = t1 > RT_MIN_RAY_DISTANCE ? t1 : t2;
+    if (t > RT_MIN_RAY_DISTANCE && t < max_t) { *t_out = t; return true; }
+    return false;
+}
+
+// shader/src/intersection.rs:91-138 with e1/e2 given.  Returns t (accepted iff
+// RT_MIN_RAY_DISTANCE < t; the caller applies the `< max_t` / tie rule) or -1.
+__device__ __forceinline__ float triangle_t(const Ray& ray, V3 v0, V3 e1, V3 e2) {
+    V3 h = cross3(ray.d, e2);
+    float a = dot3(e1, h);
+    if (fabsf(a) < RT_MIN_RAY_DISTANCE) return -1.0f;
+    float f = 1.0f / a;
+    V3 s = ray.o - v0;
+    float u = f * dot3(s, h);
+    if (u < 0.0f || u > 1.0f) return -1.0f;
+    V3 q = cross3(s, e1);
+    float v = f * dot3(ray.d, q);
+    if (v < 0.0f || u + v > 1.0f) return -1.0f;
+    float t = f * dot3(e2, q);
+    return (t > RT_MIN_RAY_DISTANCE) ? t : -1.0f;
+}
+
+// shader/src/intersection.rs:151-164; returns tmin_max through *entry.
+__device__ __forceinline__ bool slab(V3 o, V3 inv, V3 bmin, V3 bmax, float* entry) {
+    V3 t1 = (bmin - o) * inv;
+    V3 t2 = (bmax - o) * inv;
+    float tminx = fminf(t1.x, t2.x), tminy = fminf(t1.y, t2.y), tminz = fminf(t1.z, t2.z);
+    float tmaxx = fmaxf(t1.x, t2.x), tmaxy = fmaxf(t1.y, t2.y), tmaxz = fmaxf(t1.z, t2.z);
+    float tmin_max = fmaxf(fmaxf(tminx, tminy), tminz);
+    float tmax_min = fminf(fminf(tmaxx, tmaxy), tmaxz);
+    *entry = tmin_max;
+    return tmax_min >= 0.0f && tmin_max <= tmax_min;
+}
+
+// ------------------------------------------------- LITERAL closest-hit policy
+// shader/src/triangle_access.rs:18-61.  The reference binds the flat triangle
+// array as <=3 buffers of ctx_triangles_per_buffer; index arithmetic uses the
+// push-constant value.
+__device__ __forceinline__ bool fetch_triangle_ref(const KParams& p, uint32_t index, V3* v0, V3* v1, V3* v2,
+                                                   uint32_t* mat) {
+    uint32_t tpb = p.triangles_per_buffer;
+    if (tpb == 0u) return false;
+    uint32_t bi = index / tpb;
+    uint64_t li = index % tpb;
+    if (bi > 2u) return false;
+    uint64_t base = (uint64_t)bi * p.ctx_triangles_per_buffer;
+    uint64_t len = p.n_tris > base ? p.n_tris - base : 0;
+    if (len > p.ctx_triangles_per_buffer) len = p.ctx_triangles_per_buffer;
+    if (li >= len) return false;
+    const uint4 t = __ldg(reinterpret_cast<const uint4*>(p.tris) + base + li);
+    uint64_t vo = p.off.vertices_offset;
+    *v0 = mk(meta_f(p, vo + (uint64_t)t.x * 3), meta_f(p, vo + (uint64_t)t.x * 3 + 1), meta_f(p, vo + (uint64_t)t.x * 3 + 2));
+    *v1 = mk(meta_f(p, vo + (uint64_t)t.y * 3), meta_f(p, vo + (uint64_t)t.y * 3 + 1), meta_f(p, vo + (uint64_t)t.y * 3 + 2));
+    *v2 = mk(meta_f(p, vo + (uint64_t)t.z * 3), meta_f(p, vo + (uint64_t)t.z * 3 + 1), meta_f(p, vo + (uint64_t)t.z * 3 + 2));
+    *mat = t.w;
+    return true;
+}
+
+struct TriBest {
+    float t;       // closest accepted t so far (seeded with max_t)
+    uint32_t prim; // triangle index of the winner
+    uint32_t mat;
+    V3 v0, e1, e2; // winner's geometry (for point/normal)
+    bool hit;
+};
+
+__device__ __forceinline__ void literal_test(const KParams& p, const Ray& ray, uint32_t tri_index, TriBest& b) {
+    V3 v0, v1, v2;
+    uint32_t mat;
+    if (!fetch_triangle_ref(p, tri_index, &v0, &v1, &v2, &mat)) return;
+    V3 e1 = v1 - v0, e2 = v2 - v0;
+    float t = triangle_t(ray, v0, e1, e2);
+    if (t > 0.0f && t < b.t) {
+        b.t = t; b.prim = tri_index; b.mat = mat; b.v0 = v0; b.e1 = e1; b.e2 = e2; b.hit = true;
+    }
+}
+
+// shader/src/bvh.rs:18-133 (stack quirk included) / lib.rs:272-296 (brute force)
+__device__ void closest_triangle_literal(const KParams& p, const Ray& ray, float max_t, TriBest& b) {
+    b.t = max_t; b.hit = false; b.prim = 0xFFFFFFFFu; b.mat = 0xFFFFFFFFu;
+    uint32_t node_count = p.off.bvh_nodes_count;
+    if (node_count == 0u) {
+        for (uint32_t i = 0; i < p.triangle_count; i++) literal_test(p, ray, i, b);
+        return;
+    }
+    V3 inv = mk(1.0f / ray.d.x, 1.0f / ray.d.y, 1.0f / ray.d.z);
+    uint32_t stack[64];
+    int sp = 0;
+    stack[sp++] = 0u;
+    while (sp > 0) {
+        uint32_t n = stack[--sp];
+        if (n == 0xFFFFFFFFu || n >= node_count) continue;
+        uint64_t no = (uint64_t)p.off.bvh_nodes_offset + (uint64_t)n * 12;
+        V3 bmin = mk(meta_f(p, no), meta_f(p, no + 1), meta_f(p, no + 2));
+        V3 bmax = mk(meta_f(p, no + 4), meta_f(p, no + 5), meta_f(p, no + 6));
+        float entry;
+        if (!slab(ray.o, inv, bmin, bmax, &entry)) continue;
+        uint32_t left = meta_at(p, no + 8), right = meta_at(p, no + 9);
+        if (left == 0xFFFFFFFFu) {
+            uint32_t start = meta_at(p, no + 10), count = meta_at(p, no + 11);
+            for (uint32_t i = 0; i < count; i++) {
+                if (start + i >= p.off.triangle_indices_count) break;
+                uint32_t ti = meta_at(p, (uint64_t)p.off.triangle_indices_offset + start + i);
+                literal_test(p, ray, ti, b);
+            }
+        } else {
+            if (right != 0xFFFFFFFFu && sp < 63) stack[sp++] = right;
+            if (left != 0xFFFFFFFFu && sp < 63) stack[sp++] = left;
+        }
+    }
+}
+
+// ------------------------------------------------- ORDERED closest-hit policy
+// Wide node i = 4 x float4:
+//   q0 = (L.min.x, L.min.y, L.min.z, L.max.x)   q1 = (L.max.y, L.max.z, R.min.x, R.min.y)
+//   q2 = (R.min.z, R.max.x, R.max.y, R.max.z)   q3 = (Lref, Rref, -, -) as u32
+// ref: internal node index, or RT_LEAF_FLAG|first triangle position, or RT_CHILD_ABSENT.
+// Triangle position j = 3 x float4: (v0.xyz, e1.x) (e1.yz, e2.xy) (e2.z, material, tri_index, remaining)
+// where `remaining` counts the triangles left in the leaf including this one.
+__device__ __forceinline__ void ordered_leaf(const KParams& p, const Ray& ray, uint32_t start, TriBest& b,
+                                             uint32_t& best_pos) {
+    uint32_t pos = start;
+    for (;;) {
+        const float4* tp = p.wtris + (uint64_t)pos * 3;
+        float4 a = __ldg(tp), c = __ldg(tp + 1), d = __ldg(tp + 2);
+        V3 v0 = mk(a.x, a.y, a.z), e1 = mk(a.w, c.x, c.y), e2 = mk(c.z, c.w, d.x);
+        float t = triangle_t(ray, v0, e1, e2);
+        // reference: strict `t < closest` in visit order; with re-ordered visits the
+        // equal-t winner is the smaller position in triangle_indices.
+        if (t > 0.0f && (t < b.t || (t == b.t && b.hit && pos < best_pos))) {
+            b.t = t; b.hit = true; best_pos = pos;
+            b.mat = __float_as_uint(d.y); b.prim = __float_as_uint(d.z);
+            b.v0 = v0; b.e1 = e1; b.e2 = e2;
+        }
+        uint32_t remaining = __float_as_uint(d.w);
+        if (remaining <= 1u) break;
+        pos++;
+    }
+}
+
+__device__ void closest_triangle_ordered(const KParams& p, const Ray& ray, float max_t, TriBest& b) {
+    b.t = max_t; b.hit = false; b.prim = 0xFFFFFFFFu; b.mat = 0xFFFFFFFFu;
+    uint32_t best_pos = 0u;
+    uint32_t cur = p.root_ref;
+    if (cur == RT_CHILD_ABSENT) return;
+    V3 inv = mk(1.0f / ray.d.x, 1.0f / ray.d.y, 1.0f / ray.d.z);
+    {
+        float entry;
+        if (!slab(ray.o, inv, mka(p.root_min), mka(p.root_max), &entry)) return;
+    }
+    uint32_t stack[64];
+    int sp = 0;
+    for (;;) {
+        if (cur & RT_LEAF_FLAG) {
+            ordered_leaf(p, ray, cur & ~RT_LEAF_FLAG, b, best_pos);
+        } else {
+            const float4* np = p.wnodes + (uint64_t)cur * 4;
+            float4 q0 = __ldg(np), q1 = __ldg(np + 1), q2 = __ldg(np + 2), q3 = __ldg(np + 3);
+            uint32_t lref = __float_as_uint(q3.x), rref = __float_as_uint(q3.y);
+            float el, er;
+            bool hl = slab(ray.o, inv, mk(q0.x, q0.y, q0.z), mk(q0.w, q1.x, q1.y), &el);
+            bool hr = slab(ray.o, inv, mk(q1.z, q1.w, q2.x), mk(q2.y, q2.z, q2.w), &er);
+            float limit = b.t * RT_PRUNE_SCALE + RT_PRUNE_ABS;
+            hl = hl && (lref != RT_CHILD_ABSENT) && (el <= limit);
+            hr = hr && (rref != RT_CHILD_ABSENT) && (er <= limit);
+            if (hl && hr) {
+                // near child first; equal entry -> left first (the reference's order)
+                bool right_first = er < el;
+                uint32_t nearc = right_first ? rref : lref, farc = right_first ? lref : rref;
+                stack[sp++] = farc;
+                cur = nearc;
+                continue;
+            } else if (hl) { cur = lref; continue; }
+            else if (hr) { cur = rref; continue; }
+        }
+        if (sp == 0) break;
+        cur = stack[--sp];
+    }
+}
+
+// ---------------------------------------------------------------- closest hit
+// shader/src/lib.rs:174-269: spheres first (brute force), then triangles seeded
+// with the sphere t; the triangle wins only if strictly closer.
+template <bool ORDERED>
+__device__ __forceinline__ Hit find_closest(const KParams& p, const Ray& ray) {
+    Hit h;
+    h.t = FLT_MAX; h.kind = 0u; h.prim = 0xFFFFFFFFu; h.material_id = 0xFFFFFFFFu;
+    h.point = mk(0, 0, 0); h.normal = mk(0, 0, 0);
+    float closest = FLT_MAX - 2.0f;
+    uint32_t sphere_idx = 0xFFFFFFFFu;
+    for (uint32_t i = 0; i < p.off.spheres_count; i++) {
+        uint64_t o = (uint64_t)p.off.spheres_offset + (uint64_t)i * 5;
+        float t;
+        if (sphere_t(ray, mk(meta_f(p, o), meta_f(p, o + 1), meta_f(p, o + 2)), meta_f(p, o + 3), closest, &t)) {
+            closest = t; sphere_idx = i;
+        }
+    }
+    TriBest b;
+    if (ORDERED) closest_triangle_ordered(p, ray, closest, b);
+    else closest_triangle_literal(p, ray, closest, b);
+    if (b.hit) { // b.t < sphere t by construction
+        h.t = b.t; h.kind = 2u; h.prim = b.prim; h.material_id = b.mat;
+        h.point = ray.o + ray.d * b.t;
+        h.normal = normalize3(cross3(b.e1, b.e2)); // geometric, un-flipped (intersection.rs:132)
+    } else if (sphere_idx != 0xFFFFFFFFu) {
+        uint64_t o = (uint64_t)p.off.spheres_offset + (uint64_t)sphere_idx * 5;
+        V3 c = mk(meta_f(p, o), meta_f(p, o + 1), meta_f(p, o + 2));
+        h.t = closest; h.kind = 1u; h.prim = sphere_idx; h.material_id = meta_at(p, o + 4);
+        h.point = ray.o + ray.d * closest;
+        h.normal = normalize3(h.point - c);
+    }
+    return h;
+}
+
+// -------------------------------------------------------------------- shading
+struct MatEval {
+    V3 albedo, emission;
+    float metallic, roughness, ior, transmission;
+};
+// shader/src/material.rs:6-63; only the first 32 bytes of the 128-byte Material are read.
+__device__ __forceinline__ MatEval load_material(const KParams& p, uint32_t id) {
+    const float4* mp = reinterpret_cast<const float4*>(p.mats + id);
+    float4 a = __ldg(mp), b = __ldg(mp + 1);
+    MatEval m;
+    m.albedo = mk(a.x, a.y, a.z);
+    m.emission = mk(b.x, b.y, b.z);
+    uint32_t mr = __float_as_uint(a.w), it = __float_as_uint(b.w);
+    m.metallic = f16lo(mr); m.roughness = f16hi(mr);
+    m.ior = f16lo(it); m.transmission = f16hi(it);
+    return m;
+}
+// shader/src/material.rs:76-83
+__device__ __forceinline__ V3 evaluate_brdf(const MatEval& m, float I) {
+    V3 diffuse = m.albedo / 3.14159265358979323846f;
+    float is_m = (m.metallic > 0.5f) ? 1.0f : 0.0f;
+    V3 metallic_c = m.albedo * I * 0.5f;
+    V3 dielectric_c = diffuse * I;
+    return metallic_c * is_m + dielectric_c * (1.0f - is_m);
+}
+// shader/src/lighting.rs:20-139.  fmaxf(x, 0) scrubs the NaN that
+// normalize((0,0,0)) produces for point lights.
+__device__ __forceinline__ V3 calculate_lighting(const KParams& p, const Hit& h, const MatEval& m) {
+    V3 total = mk(0.0f, 0.0f, 0.0f);
+    total = total + m.albedo * 0.1f;
+    for (uint32_t li = 0; li < p.off.lights_count; li++) {
+        uint64_t o = (uint64_t)p.off.lights_offset + (uint64_t)li * 13;
+        V3 lpos = mk(meta_f(p, o), meta_f(p, o + 1), meta_f(p, o + 2));
+        uint32_t ltype = meta_at(p, o + 3);
+        V3 lcol = mk(meta_f(p, o + 4), meta_f(p, o + 5), meta_f(p, o + 6));
+        float lint = meta_f(p, o + 7);
+        V3 ldir = mk(meta_f(p, o + 8), meta_f(p, o + 9), meta_f(p, o + 10));
+        V3 nld = -normalize3(ldir);
+        float dir_intensity = fmaxf(dot3(h.normal, nld), 0.0f) * lint;
+        V3 to_light = lpos - h.point;
+        float distance = length3(to_light);
+        V3 pdir = normalize3(to_light);
+        float att = round_through_f16(1.0f / (1.0f + distance * distance * 0.01f));
+        float point_intensity = fmaxf(dot3(h.normal, pdir), 0.0f) * lint * att;
+        float spot_factor = fmaxf(dot3(nld, pdir), 0.0f);
+        float spot_intensity = point_intensity * spot_factor;
+        float is_dir = (ltype == 0u) ? 1.0f : 0.0f, is_point = (ltype == 1u) ? 1.0f : 0.0f,
+              is_spot = (ltype == 2u) ? 1.0f : 0.0f;
+        float I = dir_intensity * is_dir + point_intensity * is_point + spot_intensity * is_spot;
+        V3 contrib = evaluate_brdf(m, I);
+        float valid = (I > 0.0f) ? 1.0f : 0.0f; // index_valid is 1 inside the loop bound
+        total = total + contrib * lcol * valid;
+    }
+    return total + m.emission;
+}
+// shader/src/lib.rs:300-338 for all three colour channels at once: channel c only
+// enters through ior_for_channel(c) and the final component select, and every
+// Vec3 op is component-wise, so out.c equals pass c's value bit for bit.
+// `channel` < 3 evaluates that single pass; >= 3 the fused triple.
+__device__ __forceinline__ V3 shade_hit(const KParams& p, const Hit& h, uint32_t channel) {
+    if (h.material_id >= p.n_mats) return mk(1.0f, 0.0f, 1.0f);
+    MatEval m = load_material(p, h.material_id);
+    V3 lighting = calculate_lighting(p, h, m);
+    float T = fminf(fmaxf(m.transmission, 0.0f), 1.0f);
+    if (!(T > 0.0f)) return lighting;
+    const float offs[4] = {-0.018f, 0.0f, 0.035f, 0.0f};
+    float denom = m.ior - 1.0f;
+    V3 a = lighting * (1.0f - T);
+    if (channel < 3u || channel == 0xFFu) {
+        if (channel == 0xFFu) {
+            float d0 = ((m.ior + offs[0]) - 1.0f) / denom, d1 = ((m.ior + offs[1]) - 1.0f) / denom,
+                  d2 = ((m.ior + offs[2]) - 1.0f) / denom;
+            return mk(a.x + (0.2f * d0) * T, a.y + (0.2f * d1) * T, a.z + (0.3f * d2) * T);
+        }
+        float d = ((m.ior + offs[channel]) - 1.0f) / denom;
+        return a + mk(0.2f, 0.2f, 0.3f) * d * T;
+    }
+    float d = ((m.ior + offs[3]) - 1.0f) / denom;
+    return a + mk(0.2f, 0.2f, 0.3f) * d * T;
+}
+
+// ----------------------------------------------------------------- the kernel
+// Work decomposition: a 256-thread block covers a 16x16 pixel block; each warp an
+// 8x4 sub-block (coherent primary rays).  In a fused frame the block list
+// enumerates the 128x128 reference tiles (src/compute.rs:194-209) assigned to this
+// context (tile i with i % tile_stride == tile_phase), 64 blocks per tile.
+__device__ __forceinline__ bool pixel_of_thread(const KParams& p, uint32_t* px, uint32_t* py) {
+    uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
+    uint32_t lx = (warp & 1u) * 8u + (lane & 7u), ly = (warp >> 1) * 4u + (lane >> 3);
+    uint32_t x0, y0, w, h;
+    uint32_t blk = blockIdx.x;
+    if (p.use_tiles) {
+        uint32_t tile_local = blk >> 6, sub = blk & 63u;
+        uint32_t tile = p.tile_phase + tile_local * p.tile_stride;
+        if (tile >= p.n_tiles_total) return false;
+        uint32_t tx = tile % p.tiles_x, ty = tile / p.tiles_x;
+        x0 = tx * RT_TILE_SIZE; y0 = ty * RT_TILE_SIZE; w = RT_TILE_SIZE; h = RT_TILE_SIZE;
+        lx += (sub & 7u) * 16u; ly += (sub >> 3) * 16u;
+    } else {
+        uint32_t bw = (p.rect_w + 15u) >> 4;
+        x0 = p.rect_x0; y0 = p.rect_y0; w = p.rect_w; h = p.rect_h;
+        lx += (blk % bw) * 16u; ly += (blk / bw) * 16u;
+    }
+    *px = x0 + lx; *py = y0 + ly;
+    // is_pixel_in_bounds, shader/src/lib.rs:152-163
+    return lx < w && ly < h && *px < p.width && *py < p.height;
+}
+
+template <bool ORDERED>
+__global__ void __launch_bounds__(256) rt_trace_shade(const __grid_constant__ KParams p) {
+    uint32_t px, py;
+    if (!pixel_of_thread(p, &px, &py)) return;
+    const bool wavefront = p.mode == RT_MODE_WAVEFRONT0;
+    const bool fused = p.use_tiles != 0u;
+    const uint32_t channel = fused ? 0xFFu : p.channel;
+    V3 color = mk(0.0f, 0.0f, 0.0f);
+    Hit h;
+    h.t = FLT_MAX; h.kind = 0u; h.prim = 0xFFFFFFFFu; h.material_id = 0xFFFFFFFFu;
+    if (!wavefront) {
+        Ray ray = camera_ray(p, px, py, 0.5f, 0.5f, false);
+        h = find_closest<ORDERED>(p, ray);
+        if (h.kind != 0u) color = shade_hit(p, h, channel); // miss: (0,0,0), lib.rs:77
+    } else if (p.cur_depth <= p.max_depth) {
+        // run_wavefront_raytracing, lib.rs:92-149: throughput (1,1,1); sky on miss
+        Ray ray = camera_ray(p, px, py, 0.5f, 0.5f, true);
+        h = find_closest<ORDERED>(p, ray);
+        V3 tp = mk(1.0f, 1.0f, 1.0f);
+        V3 c = (h.kind != 0u) ? shade_hit(p, h, channel) * tp : mk(0.1f, 0.2f, 0.3f) * tp;
+        color = color + c;
+    }
+    const size_t pix = (size_t)py * p.width + px;
+    if (!fused) {
+        // filter_color_by_channel (lib.rs:342-349) + Rgba8Unorm store
+        uchar4 o = make_uchar4(0, 0, 0, 255);
+        if (channel == 0u) o.x = (unsigned char)unorm8(color.x);
+        else if (channel == 1u) o.y = (unsigned char)unorm8(color.y);
+        else o.z = (unsigned char)unorm8(color.z);
+        p.chan[channel][pix] = o;
+        if (p.outputs & RT_OUT_ACCUM) {
+            float4 a = p.accum[pix];
+            if (channel == 0u) a.x = color.x; else if (channel == 1u) a.y = color.y; else a.z = color.z;
+            a.w = 1.0f;
+            p.accum[pix] = a;
+        }
+    } else {
+        uint32_t r8 = unorm8(color.x), g8 = unorm8(color.y), b8 = unorm8(color.z);
+        if (p.outputs & RT_OUT_CHANNELS) {
+            p.chan[0][pix] = make_uchar4((unsigned char)r8, 0, 0, 255);
+            p.chan[1][pix] = make_uchar4(0, (unsigned char)g8, 0, 255);
+            p.chan[2][pix] = make_uchar4(0, 0, (unsigned char)b8, 255);
+        }
+        if (p.outputs & RT_OUT_COMPOSITE) // main_fs, lib.rs:368-391
+            p.composite[pix] = make_uchar4((unsigned char)r8, (unsigned char)g8, (unsigned char)b8, 255);
+        if (p.outputs & RT_OUT_ACCUM) {
+            float4 a = make_float4(color.x, color.y, color.z, 1.0f);
+            if (!p.reset_accum) {
+                float4 old = p.accum[pix];
+                a.x = old.x + color.x; a.y = old.y + color.y; a.z = old.z + color.z; a.w = old.w + 1.0f;
+            }
+            p.accum[pix] = a;
+        }
+    }
+    if (p.outputs & RT_OUT_HITS) {
+        uint4 rec = make_uint4(h.kind, h.prim, __float_as_uint(h.t), h.material_id);
+        reinterpret_cast<uint4*>(p.hits)[pix] = rec;
+    }
+}

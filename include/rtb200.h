@@ -1,0 +1,147 @@
+/* rtb200.h — C ABI of librtb200.so: the B200 (sm_100a) implementation of the
+ * reference's per-pixel ray tracing path, behind the reference's own dispatch
+ * surface.  Plain pointers and sizes only; every entry point cites the
+ * reference interface it replaces (paths relative to the reference tree).
+ *
+ * Conventions: functions return 0 (RT_OK) / a positive documented value on
+ * success and a negative RtStatus on failure; the text is in rt_last_error().
+ * Host memory passed in is borrowed for the duration of the call only
+ * (same as wgpu `queue.write_buffer`, src/buffers.rs:236).  All GPU work is
+ * asynchronous on the context's stream (same as `queue.submit`,
+ * src/compute.rs:165); rt_synchronize / rt_read_* wait for it.
+ * A context is bound to one GPU and is not thread-safe; use one per GPU.
+ * There is no CPU fallback: without a CUDA device rt_create fails.
+ */
+#ifndef RTB200_H
+#define RTB200_H
+#include <stdint.h>
+#include "rt_shared.h"
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum RtStatus {
+    RT_OK = 0,
+    RT_ERR_INVALID_ARGUMENT = -1,
+    RT_ERR_CUDA = -2,
+    RT_ERR_INVALID_SCENE = -3,   /* upload-time validation failed */
+    RT_ERR_INVALID_CHANNEL = -4, /* src/compute.rs:228-229 `.expect("Invalid color channel")` */
+    RT_ERR_NOT_READY = -5,
+    RT_ERR_NCCL = -6
+} RtStatus;
+
+typedef struct RtContext RtContext;
+
+/* Closest-hit record per pixel (the reference's IntersectionResult,
+ * shader/src/intersection.rs:10-38, plus a primitive id). */
+typedef struct RtHitRecord {
+    uint32_t kind;        /* 0 miss, 1 sphere, 2 triangle */
+    uint32_t prim;        /* sphere index / triangle index; 0xFFFFFFFF on miss */
+    uint32_t t_bits;      /* IEEE-754 bits of t; f32::MAX on miss */
+    uint32_t material_id; /* 0xFFFFFFFF on miss */
+} RtHitRecord;
+
+enum {
+    RT_OUT_ACCUM = 1u,     /* float4 accumulation buffer (rgb sum, sample count) */
+    RT_OUT_HITS = 2u,      /* RtHitRecord per pixel (sample 0 / primary ray) */
+    RT_OUT_CHANNELS = 4u,  /* the three Rgba8Unorm channel images (src/renderer.rs:452-475) */
+    RT_OUT_COMPOSITE = 8u  /* main_fs composite (R.x,G.y,B.z,1), shader/src/lib.rs:368-391 */
+};
+enum {
+    RT_MODE_LEGACY = 0,    /* main_cs legacy branch, shader/src/lib.rs:59-79 (what src/main.rs runs) */
+    RT_MODE_WAVEFRONT0 = 1,/* main_cs wavefront branch at depth 0, lib.rs:92-149 */
+    RT_MODE_PATH = 2       /* EXTENSION (reference stubs it): bounces + spp, SPEC.md */
+};
+enum { RT_TRAVERSAL_AUTO = 0, RT_TRAVERSAL_LITERAL = 1, RT_TRAVERSAL_ORDERED = 2 };
+
+/* Whole-frame parameters of the fused path (no reference analogue: replaces the
+ * per-tile x per-channel loop of src/compute.rs:157-191 by one launch). */
+typedef struct RtFrameParams {
+    uint32_t mode;         /* RT_MODE_* */
+    uint32_t outputs;      /* RT_OUT_* mask */
+    uint32_t spp;          /* samples added by this call (>=1) */
+    uint32_t first_sample; /* index of the first sample (progressive resume) */
+    uint32_t max_depth;    /* RT_MODE_PATH: max bounce depth */
+    uint32_t base_seed;    /* frame_seed of sample s is base_seed + s */
+    uint32_t reset_accum;  /* 1: overwrite accumulation; 0: add to it */
+    uint32_t tile_stride;  /* multi-GPU tile split: this context renders the */
+    uint32_t tile_phase;   /*   128x128 tiles i with i % tile_stride == tile_phase (0,0 = all) */
+    uint32_t traversal;    /* RT_TRAVERSAL_* */
+    uint32_t _reserved[2];
+} RtFrameParams;
+
+/* ---- context: stands in for RenderState.device/queue + the three output
+ * textures (src/renderer.rs:93-246, 452-475) and BufferManager::new
+ * (src/buffers.rs:66-154). */
+int rt_create(int device, RtContext** out);
+void rt_destroy(RtContext* ctx);
+const char* rt_last_error(const RtContext* ctx); /* ctx may be NULL: last create error */
+/* RenderState::resize + ProgressiveState::resize (src/renderer.rs:477, 838) */
+int rt_resize(RtContext* ctx, uint32_t width, uint32_t height);
+int rt_synchronize(RtContext* ctx);
+
+/* ---- BufferManager (src/buffers.rs).  Return 1 if the device buffer was
+ * (re)allocated, 0 if not, <0 on error — the reference returns `bool resized`. */
+/* update_scene_metadata, src/buffers.rs:157-271; offsets per :257-268 */
+int rt_update_scene_metadata(RtContext* ctx, const RtSphere* spheres, uint32_t n_spheres,
+                             const RtLight* lights, uint32_t n_lights, const RtBvhNode* nodes,
+                             uint32_t n_nodes, const uint32_t* triangle_indices, uint32_t n_indices,
+                             const RtVertex* vertices, uint32_t n_vertices,
+                             RtSceneMetadataOffsets* out_offsets);
+/* update_triangles, src/buffers.rs:274-336 (split over <=3 bindings there; one flat array here) */
+int rt_update_triangles(RtContext* ctx, const RtTriangle* triangles, uint64_t n);
+/* update_materials, src/buffers.rs:339-378 */
+int rt_update_materials(RtContext* ctx, const RtMaterial* materials, uint64_t n);
+/* update_textures, src/buffers.rs:381-419 (bound but never read by the shader) */
+int rt_update_textures(RtContext* ctx, const RtTextureInfo* textures, uint64_t n);
+/* update_texture_data, src/buffers.rs:422-470 (bytes packed little-endian into u32) */
+int rt_update_texture_data(RtContext* ctx, const uint8_t* bytes, uint64_t n_bytes);
+/* mark_*_dirty / needs_update, src/buffers.rs:473-501 */
+void rt_mark_scene_metadata_dirty(RtContext* ctx);
+void rt_mark_triangles_dirty(RtContext* ctx);
+void rt_mark_materials_dirty(RtContext* ctx);
+void rt_mark_textures_dirty(RtContext* ctx);
+void rt_mark_texture_data_dirty(RtContext* ctx);
+void rt_mark_all_dirty(RtContext* ctx);
+int rt_needs_update(const RtContext* ctx);
+/* BufferManager.triangles_per_buffer (src/buffers.rs:49-53, 103) */
+uint32_t rt_triangles_per_buffer(const RtContext* ctx);
+/* offsets of the last metadata upload (what run_compute passes on, src/compute.rs:109-134) */
+int rt_get_metadata_offsets(const RtContext* ctx, RtSceneMetadataOffsets* out);
+
+/* ---- dispatch (src/compute.rs) */
+/* One reference dispatch: process_color_channel, src/compute.rs:212-251 —
+ * main_cs over ceil(w/16) x ceil(h/16) groups with these push constants; writes
+ * the channel's Rgba8Unorm image. */
+int rt_dispatch(RtContext* ctx, const RtPushConstants* pc);
+/* ComputeRenderer::run_compute, src/compute.rs:12-50: progressive step — renders
+ * the next tiles_per_frame tiles x 3 channels (TileHelper, shared/src/lib.rs:
+ * 1187-1203; ProgressiveState, src/renderer.rs:821-855).  needs_recompute!=0
+ * restarts at tile 0.  Returns the number of tiles still pending after the call. */
+int rt_run_compute(RtContext* ctx, const RtCamera* camera, int needs_recompute);
+/* Fused whole frame: all tiles, three channels, composite and accumulation in
+ * one launch. */
+int rt_render_frame(RtContext* ctx, const RtCamera* camera, const RtFrameParams* params);
+
+/* ---- outputs (the reference never reads back; these are the headless
+ * replacement of the surface present, src/renderer.rs:778-818) */
+int rt_read_channel_rgba8(RtContext* ctx, uint32_t channel, void* dst); /* W*H*4 bytes */
+int rt_read_composite_rgba8(RtContext* ctx, void* dst);                /* W*H*4 bytes */
+int rt_read_accum_f32(RtContext* ctx, void* dst);                      /* W*H*16 bytes */
+int rt_write_accum_f32(RtContext* ctx, const void* src);               /* resume */
+int rt_read_hit_records(RtContext* ctx, void* dst);                    /* W*H*16 bytes */
+/* raw device pointers for zero-copy consumers (torch / NCCL) */
+void* rt_device_accum(RtContext* ctx);
+void* rt_device_composite(RtContext* ctx);
+/* GPU time of the last rt_render_frame / rt_dispatch launch in ms (CUDA events
+ * on the context stream); <0 if none. */
+float rt_last_kernel_ms(RtContext* ctx);
+/* number of kernels this library has launched on ctx since creation */
+uint64_t rt_launch_count(const RtContext* ctx);
+/* which traversal the last launch used (RT_TRAVERSAL_LITERAL / _ORDERED) */
+int rt_last_traversal(const RtContext* ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
