@@ -1,0 +1,189 @@
+"""Python mirror of the reference's dispatch surface over the C ABI:
+`BufferManager` (src/buffers.rs) and `ComputeRenderer` (src/compute.rs).
+Every method is one call into librtb200.so; nothing is computed in Python."""
+import ctypes as C
+
+import numpy as np
+
+from . import abi
+from .native import load
+
+
+class RtError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"librtb200 error {code}: {msg}")
+        self.code = code
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None and a.size else None
+
+
+class Context:
+    """RenderState.device/queue + output textures (src/renderer.rs:93-246, 452-475)."""
+
+    def __init__(self, device=0, width=None, height=None):
+        self.lib = load()
+        h = C.c_void_p()
+        rc = self.lib.rt_create(device, C.byref(h))
+        if rc != 0:
+            raise RtError(rc, self.lib.rt_last_error(None).decode())
+        self.handle = h
+        self.width = self.height = 0
+        if width:
+            self.resize(width, height)
+
+    def _ck(self, rc):
+        if rc < 0:
+            raise RtError(rc, self.lib.rt_last_error(self.handle).decode())
+        return rc
+
+    def close(self):
+        if getattr(self, "handle", None):
+            self.lib.rt_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def resize(self, width, height):
+        self._ck(self.lib.rt_resize(self.handle, width, height))
+        self.width, self.height = width, height
+
+    def synchronize(self):
+        self._ck(self.lib.rt_synchronize(self.handle))
+
+    # ---- read-back
+    def read_channel(self, ch):
+        out = np.empty((self.height, self.width, 4), np.uint8)
+        self._ck(self.lib.rt_read_channel_rgba8(self.handle, ch, _p(out)))
+        return out
+
+    def read_composite(self, out=None):
+        if out is None:
+            out = np.empty((self.height, self.width, 4), np.uint8)
+        self._ck(self.lib.rt_read_composite_rgba8(self.handle, _p(out)))
+        return out
+
+    def read_accum(self):
+        out = np.empty((self.height, self.width, 4), np.float32)
+        self._ck(self.lib.rt_read_accum_f32(self.handle, _p(out)))
+        return out
+
+    def write_accum(self, a):
+        a = np.ascontiguousarray(a, np.float32)
+        assert a.shape == (self.height, self.width, 4)
+        self._ck(self.lib.rt_write_accum_f32(self.handle, _p(a)))
+
+    def read_hits(self):
+        out = np.empty((self.height, self.width), abi.HitRecord)
+        self._ck(self.lib.rt_read_hit_records(self.handle, _p(out)))
+        return out
+
+    @property
+    def last_kernel_ms(self):
+        return float(self.lib.rt_last_kernel_ms(self.handle))
+
+    @property
+    def launch_count(self):
+        return int(self.lib.rt_launch_count(self.handle))
+
+    @property
+    def last_traversal(self):
+        return int(self.lib.rt_last_traversal(self.handle))
+
+
+class BufferManager:
+    """src/buffers.rs — same method names, same return values (`resized` bools)."""
+
+    def __init__(self, ctx):
+        self.ctx = ctx
+        self.triangles_per_buffer = int(ctx.lib.rt_triangles_per_buffer(ctx.handle))
+
+    def update_scene_metadata(self, spheres, lights, bvh_nodes, triangle_indices, vertices):
+        c = self.ctx
+        arrs = [np.ascontiguousarray(spheres, abi.Sphere), np.ascontiguousarray(lights, abi.Light),
+                np.ascontiguousarray(bvh_nodes, abi.BvhNode), np.ascontiguousarray(triangle_indices, np.uint32),
+                np.ascontiguousarray(vertices, abi.Vertex)]
+        off = np.zeros((), abi.SceneMetadataOffsets)
+        rc = c._ck(c.lib.rt_update_scene_metadata(c.handle, _p(arrs[0]), len(arrs[0]), _p(arrs[1]), len(arrs[1]),
+                                                  _p(arrs[2]), len(arrs[2]), _p(arrs[3]), len(arrs[3]), _p(arrs[4]),
+                                                  len(arrs[4]), off.ctypes.data_as(C.c_void_p)))
+        return bool(rc), off
+
+    def update_triangles(self, triangles):
+        t = np.ascontiguousarray(triangles, abi.Triangle)
+        return bool(self.ctx._ck(self.ctx.lib.rt_update_triangles(self.ctx.handle, _p(t), len(t))))
+
+    def update_materials(self, materials):
+        m = np.ascontiguousarray(materials, abi.Material)
+        return bool(self.ctx._ck(self.ctx.lib.rt_update_materials(self.ctx.handle, _p(m), len(m))))
+
+    def update_textures(self, textures):
+        t = np.ascontiguousarray(textures, abi.TextureInfo)
+        return bool(self.ctx._ck(self.ctx.lib.rt_update_textures(self.ctx.handle, _p(t), len(t))))
+
+    def update_texture_data(self, data):
+        d = np.ascontiguousarray(data, np.uint8)
+        return bool(self.ctx._ck(self.ctx.lib.rt_update_texture_data(self.ctx.handle, _p(d), d.size)))
+
+    def mark_scene_metadata_dirty(self):
+        self.ctx.lib.rt_mark_scene_metadata_dirty(self.ctx.handle)
+
+    def mark_triangles_dirty(self):
+        self.ctx.lib.rt_mark_triangles_dirty(self.ctx.handle)
+
+    def mark_materials_dirty(self):
+        self.ctx.lib.rt_mark_materials_dirty(self.ctx.handle)
+
+    def mark_textures_dirty(self):
+        self.ctx.lib.rt_mark_textures_dirty(self.ctx.handle)
+
+    def mark_texture_data_dirty(self):
+        self.ctx.lib.rt_mark_texture_data_dirty(self.ctx.handle)
+
+    def mark_all_dirty(self):
+        self.ctx.lib.rt_mark_all_dirty(self.ctx.handle)
+
+    def needs_update(self):
+        return bool(self.ctx.lib.rt_needs_update(self.ctx.handle))
+
+    def upload_scene(self, scene):
+        """ComputeRenderer::update_buffers_and_bind_groups (src/compute.rs:109-134)."""
+        _, off = self.update_scene_metadata(scene.spheres, scene.lights, scene.bvh_nodes, scene.triangle_indices,
+                                            scene.vertices)
+        self.update_triangles(scene.triangles)
+        self.update_materials(scene.materials)
+        self.update_textures(scene.textures)
+        self.update_texture_data(scene.texture_data)
+        return off
+
+
+class ComputeRenderer:
+    """src/compute.rs — run_compute (progressive), one literal dispatch, and the fused frame."""
+
+    def __init__(self, ctx):
+        self.ctx = ctx
+
+    def dispatch(self, push_constants):
+        pc = np.ascontiguousarray(push_constants, abi.PushConstants)
+        self.ctx._ck(self.ctx.lib.rt_dispatch(self.ctx.handle, pc.ctypes.data_as(C.c_void_p)))
+
+    def run_compute(self, camera, needs_recompute=False):
+        cam = np.ascontiguousarray(camera, abi.Camera)
+        return self.ctx._ck(self.ctx.lib.rt_run_compute(self.ctx.handle, cam.ctypes.data_as(C.c_void_p),
+                                                        int(needs_recompute)))
+
+    def render_frame(self, camera, mode=abi.MODE_LEGACY, outputs=abi.OUT_ACCUM | abi.OUT_COMPOSITE, spp=1,
+                     first_sample=0, max_depth=0, base_seed=1, reset_accum=True, tile_stride=0, tile_phase=0,
+                     traversal=abi.TRAVERSAL_AUTO):
+        cam = np.ascontiguousarray(camera, abi.Camera)
+        fp = np.zeros((), abi.FrameParams)
+        fp["mode"], fp["outputs"], fp["spp"], fp["first_sample"] = mode, outputs, spp, first_sample
+        fp["max_depth"], fp["base_seed"], fp["reset_accum"] = max_depth, base_seed, int(reset_accum)
+        fp["tile_stride"], fp["tile_phase"], fp["traversal"] = tile_stride, tile_phase, traversal
+        self.ctx._ck(self.ctx.lib.rt_render_frame(self.ctx.handle, cam.ctypes.data_as(C.c_void_p),
+                                                  fp.ctypes.data_as(C.c_void_p)))

@@ -1,0 +1,115 @@
+"""TEST INFRASTRUCTURE: ctypes binding of oracle/librt_oracle.so (the CPU
+restatement of the reference shader).  Only tests/, __graft_entry__.smoke() and
+bench.py's cpu_baseline / --impl reference legs import this."""
+import ctypes as C
+import os
+
+import numpy as np
+
+from gpu_raytracer_b200 import abi
+from gpu_raytracer_b200.host import pack_scene_metadata, push_constants_new
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+_lib = None
+
+
+class OrcBindings(C.Structure):
+    _fields_ = [("scene_metadata", C.c_void_p), ("scene_metadata_len", C.c_uint64),
+                ("triangles", C.c_void_p * 3), ("triangles_len", C.c_uint64 * 3),
+                ("materials", C.c_void_p), ("materials_len", C.c_uint64)]
+
+
+class OrcCounters(C.Structure):
+    _fields_ = [("aabb_tests", C.c_uint64), ("tri_tests", C.c_uint64), ("sphere_tests", C.c_uint64),
+                ("rays", C.c_uint64)]
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        path = os.path.join(ROOT, "oracle", "librt_oracle.so")
+        _lib = C.CDLL(path)
+        _lib.orc_dispatch.restype = C.c_int
+        _lib.orc_dispatch.argtypes = [C.POINTER(OrcBindings), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int,
+                                      C.POINTER(OrcCounters)]
+        _lib.orc_composite.restype = None
+        _lib.orc_composite.argtypes = [C.c_void_p] * 4 + [C.c_uint64]
+        _lib.orc_hardware_threads.restype = C.c_int
+        _lib.orc_f32_to_f16.restype = C.c_uint16
+        _lib.orc_f32_to_f16.argtypes = [C.c_float]
+        _lib.orc_f16_to_f32.restype = C.c_float
+        _lib.orc_f16_to_f32.argtypes = [C.c_uint16]
+    return _lib
+
+
+def hardware_threads():
+    return int(lib().orc_hardware_threads())
+
+
+class BoundScene:
+    """The reference's bound buffers for one scene (bindings 1-5), split over <=3
+    triangle buffers like BufferManager::update_triangles (src/buffers.rs:311-325)."""
+
+    def __init__(self, scene, triangles_per_buffer=abi.MAX_TRIANGLES_PER_BUFFER):
+        self.scene = scene
+        self.meta, self.offsets = pack_scene_metadata(scene)
+        self.tpb = triangles_per_buffer
+        tris = np.ascontiguousarray(scene.triangles, abi.Triangle)
+        self.tri_parts = [np.ascontiguousarray(tris[i * self.tpb:(i + 1) * self.tpb]) for i in range(3)]
+        self.materials = np.ascontiguousarray(scene.materials, abi.Material)
+        b = OrcBindings()
+        b.scene_metadata = self.meta.ctypes.data
+        b.scene_metadata_len = self.meta.size
+        for i in range(3):
+            b.triangles[i] = self.tri_parts[i].ctypes.data if len(self.tri_parts[i]) else None
+            b.triangles_len[i] = len(self.tri_parts[i])
+        b.materials = self.materials.ctypes.data if len(self.materials) else None
+        b.materials_len = len(self.materials)
+        self.bindings = b
+
+
+def dispatch(bound, pc, image, radiance=None, hits=None, threads=None, counters=None):
+    """One reference dispatch (src/compute.rs:245-250) on the CPU."""
+    threads = threads or hardware_threads()
+    pc = np.ascontiguousarray(pc, abi.PushConstants)
+    rc = lib().orc_dispatch(C.byref(bound.bindings), pc.ctypes.data, image.ctypes.data if image is not None else None,
+                            radiance.ctypes.data if radiance is not None else None,
+                            hits.ctypes.data if hits is not None else None, threads,
+                            C.byref(counters) if counters is not None else None)
+    assert rc == 0
+    return rc
+
+
+def tile_rects(width, height, tile=abi.TILE_SIZE):
+    """calculate_tile_dimensions over all tiles (src/compute.rs:194-209)."""
+    tx, ty = (width + tile - 1) // tile, (height + tile - 1) // tile
+    for i in range(tx * ty):
+        ox, oy = (i % tx) * tile, (i // tx) * tile
+        yield ox, oy, min(tile, width - ox), min(tile, height - oy), (tx, ty)
+
+
+def render(scene, width, height, wavefront=None, threads=None, camera=None, channels=(0, 1, 2), rows=None):
+    """The reference's whole progressive render on the CPU: every tile x 3 colour
+    channels (src/compute.rs:157-191) then the main_fs composite.  `rows=(y0,y1)`
+    restricts to the tiles intersecting those rows (bounded cpu_baseline samples).
+    Returns dict(channels[3] HxWx4 u8, composite, radiance HxWx3 f32, hits, counters)."""
+    bound = scene if isinstance(scene, BoundScene) else BoundScene(scene)
+    sc = bound.scene
+    cam = sc.camera if camera is None else camera
+    chans = [np.zeros((height, width, 4), np.uint8) for _ in range(3)]
+    radiance = np.zeros((height, width, 3), np.float32)
+    hits = np.zeros((height, width), abi.HitRecord)
+    counters = OrcCounters()
+    for ox, oy, tw, th, tt in tile_rects(width, height):
+        if rows is not None and (oy + th <= rows[0] or oy >= rows[1]):
+            continue
+        for ch in channels:
+            pc = push_constants_new([width, height], cam, len(sc.triangles), len(sc.materials), [ox, oy], [tw, th], tt,
+                                    bound.tpb, bound.offsets, ch, wavefront=wavefront)
+            dispatch(bound, pc, chans[ch], radiance, hits, threads, counters)
+    comp = np.zeros((height, width, 4), np.uint8)
+    lib().orc_composite(chans[0].ctypes.data, chans[1].ctypes.data, chans[2].ctypes.data, comp.ctypes.data,
+                        width * height)
+    return dict(channels=chans, composite=comp, radiance=radiance, hits=hits,
+                counters=dict(aabb_tests=counters.aabb_tests, tri_tests=counters.tri_tests,
+                              sphere_tests=counters.sphere_tests, rays=counters.rays))
