@@ -1,0 +1,328 @@
+#!/usr/bin/env python
+"""bench.py — measures BASELINE.json's metric (Mrays/s on the 1M-triangle scene at
+1080p) for the B200 path, with the roofline of the trace kernel and the CPU
+baseline beside it.  One JSON line on stdout (rank 0).
+
+  python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path
+  python bench.py --impl reference --gpus N --steps K ...  # reference CPU arm (oracle port)
+
+Step = one frame of the workload through the hot path.  `value`: scene resident
+in HBM, CUDA-event time of the K frames (L2 flushed between frames), max over
+ranks.  `e2e`: the same frames through the C ABI with HOST buffers — scene
+upload from pinned host memory + render + composite read-back, wall clock.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: (terrain nx, nz, width, height, bvh strategy name, description)
+    "c3-primary": dict(nx=1000, nz=500, w=1920, h=1080, bvh="auto",
+                       desc="C3 scene: procedural 1M-triangle terrain, 1920x1080, primary rays + direct shading "
+                            "(reference semantics), reference chunked BVH (100 tris/leaf)"),
+    "c2": dict(nx=250, nz=200, w=1920, h=1080, bvh="auto",
+               desc="C2: procedural 100K-triangle terrain, 1920x1080, primary rays + direct shading, "
+                    "standard-format BVH (1 tri/leaf)"),
+    "c3-primary-smallleaf": dict(nx=1000, nz=500, w=1920, h=1080, bvh="small_leaf",
+                                 desc="C3 scene, primary rays + direct shading, small-leaf BVH (<=4 tris/leaf) in "
+                                      "the reference node format"),
+}
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="c3-primary", choices=sorted(WORKLOADS))
+    ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU work for the cpu_baseline sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+class ClockSampler:
+    """nvidia-smi clocks/throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        self.thread.join(timeout=2)
+        sm = [float(r[0]) for r in self.rows if len(r) >= 7 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 7 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) >= 7 and r[3 + i].lower() == "active" for r in self.rows)]
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def build_scene(wl):
+    import gpu_raytracer_b200 as g
+    from gpu_raytracer_b200 import abi
+    strat = {"auto": abi.BVH_AUTO, "small_leaf": abi.BVH_SMALL_LEAF, "standard": abi.BVH_STANDARD}[wl["bvh"]]
+    return g.terrain_scene(wl["nx"], wl["nz"], seed=1, strategy=strat)
+
+
+def measured_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def cpu_baseline_sample(scene, wl, target_seconds):
+    """Times the oracle (reference policy: literal traversal, 3 channel passes per
+    tile) on a bounded band of tile rows of the same frame, all host threads."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_binding as ob
+    bound = ob.BoundScene(scene)
+    w, h = wl["w"], wl["h"]
+    threads = ob.hardware_threads()
+    # probe: one 128-row band centred vertically, one channel, to size the sample
+    mid = (h // 2) // 128 * 128
+    t0 = time.perf_counter()
+    ob.render(bound, w, h, channels=(0,), rows=(mid, mid + 1), threads=threads)
+    probe = time.perf_counter() - t0  # one band, one channel
+    band_cost = probe * 3.0
+    n_bands_total = (h + 127) // 128
+    n_bands = int(max(1, min(n_bands_total, target_seconds // max(band_cost, 1e-3))))
+    first = max(0, (n_bands_total - n_bands) // 2)
+    rows = (first * 128, min(h, (first + n_bands) * 128))
+    t0 = time.perf_counter()
+    r = ob.render(bound, w, h, rows=rows, threads=threads)
+    dt = time.perf_counter() - t0
+    pixels = (rows[1] - rows[0]) * w
+    # the reference traces every pixel three times (one dispatch per colour channel);
+    # the metric counts one camera ray per pixel, like the GPU arm
+    return {"value": pixels / dt / 1e6, "unit": "Mrays/s", "cores": threads, "kind": "port",
+            "sample": "rows %d-%d of the %dx%d frame (%d of %d tile bands), 3 channel passes, literal traversal, %.1f s"
+                      % (rows[0], rows[1], w, h, n_bands, n_bands_total, dt),
+            "traced_rays_per_s_M": r["counters"]["rays"] / dt / 1e6, "seconds": dt}
+
+
+def dist_setup(args):
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1 and args.impl != "reference":  # the reference arm is rank-0-only CPU work
+        import torch
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        backend = "gloo" if args.impl == "reference" else "nccl"
+        if backend == "nccl":
+            torch.cuda.set_device(local)
+        dist.init_process_group(backend=backend, rank=rank, world_size=world)
+    return world, rank, local
+
+
+def max_over_ranks(x, world):
+    if world == 1:
+        return x
+    import torch
+    import torch.distributed as dist
+    t = torch.tensor([x], dtype=torch.float64, device="cuda" if dist.get_backend() == "nccl" else "cpu")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def barrier(world):
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+
+
+def run_reference(args, wl, world, rank):
+    """Reference arm: the reference's CPU implementation of the path.  The Rust crate
+    cannot be built here (no rustc; rust-gpu nightly + crates.io), so this is the
+    oracle port — literal traversal, three channel passes per tile — on all host
+    threads.  Each step is a bounded sample of the frame.  Rank 0 only."""
+    if rank != 0:
+        return
+    scene = build_scene(wl)
+    per_step = max(2.0, min(args.cpu_seconds, 120.0 / max(1, args.steps + args.warmup)))
+    vals, last = [], None
+    for i in range(args.warmup + args.steps):
+        last = cpu_baseline_sample(scene, wl, per_step)
+        if i >= args.warmup:
+            vals.append(last)
+    v = float(np.mean([x["value"] for x in vals]))
+    secs = float(np.mean([x["seconds"] for x in vals]))
+    line = {"impl": "reference", "metric": "Mrays/s", "value": v, "unit": "Mrays/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": secs * 1e3, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": wl["desc"], "width": wl["w"], "height": wl["h"]},
+            "cpu_baseline": {"value": v, "unit": "Mrays/s", "cores": last["cores"], "kind": "port",
+                             "sample": last["sample"]},
+            "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def run_b200(args, wl, world, rank, local):
+    import torch
+    import gpu_raytracer_b200 as g
+    from gpu_raytracer_b200 import abi
+
+    torch.cuda.set_device(local)
+    scene = build_scene(wl)
+    w, h = wl["w"], wl["h"]
+    ctx = g.Context(local, w, h)
+    bm, cr = g.BufferManager(ctx), g.ComputeRenderer(ctx)
+    # host inputs in pinned memory (the e2e leg copies from these every step)
+    pinned = {}
+    for name in ("spheres", "lights", "bvh_nodes", "triangle_indices", "vertices", "triangles", "materials"):
+        a = np.ascontiguousarray(getattr(scene, name))
+        t = torch.from_numpy(a.view(np.uint8).reshape(-1).copy()).pin_memory() if a.size else None
+        pinned[name] = t.numpy().view(a.dtype) if t is not None else a
+        pinned["_keep_" + name] = t
+    ps = g.Scene(scene.camera, pinned["spheres"], pinned["triangles"], pinned["vertices"], pinned["materials"],
+                 pinned["lights"], pinned["bvh_nodes"], pinned["triangle_indices"])
+    h2d_bytes = sum(int(np.asarray(getattr(ps, n)).nbytes) for n in
+                    ("spheres", "lights", "bvh_nodes", "triangle_indices", "vertices", "triangles", "materials"))
+    bm.upload_scene(ps)
+    stride, phase = (world, rank) if world > 1 else (0, 0)
+    outputs = abi.OUT_ACCUM | abi.OUT_COMPOSITE
+    tiles_total = ((w + 127) // 128) * ((h + 127) // 128)
+    my_tiles = len(range(rank, tiles_total, world))
+    # rays this rank traces per frame (edge tiles are clipped to the image)
+    my_pixels = 0
+    tx = (w + 127) // 128
+    for t in range(rank, tiles_total, world):
+        ox, oy = (t % tx) * 128, (t // tx) * 128
+        my_pixels += min(128, w - ox) * min(128, h - oy)
+
+    flush = torch.empty(512 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
+
+    def frame():
+        cr.render_frame(ps.camera, outputs=outputs, tile_stride=stride, tile_phase=phase)
+
+    for _ in range(max(args.warmup, 3)):
+        frame()
+    ctx.synchronize()
+
+    # instrumented launch (untimed): algorithmic work per ray for the roofline
+    ctx.count_next_launch()
+    frame()
+    cnt = ctx.read_counters()
+
+    # ---- timed: K frames, CUDA events on the launching stream, L2 flushed between frames
+    clocks = ClockSampler(local)
+    barrier(world)
+    torch.cuda.synchronize()
+    ctx.synchronize()
+    clocks.start()
+    launches0 = ctx.launch_count
+    kernel_ms = []
+    for _ in range(args.steps):
+        flush.zero_()
+        torch.cuda.synchronize()
+        frame()
+        kernel_ms.append(ctx.last_kernel_ms)  # waits for the frame's end event
+    ctx.synchronize()
+    launches = ctx.launch_count - launches0
+    clk = clocks.stop()
+    barrier(world)
+    total_ms = max_over_ranks(float(np.sum(kernel_ms)), world)
+    total_pixels = w * h
+    value = total_pixels * args.steps / (total_ms * 1e-3) / 1e6
+
+    # ---- e2e: host buffers -> C ABI -> host image, wall clock, every step
+    host_img = torch.empty((h, w, 4), dtype=torch.uint8).pin_memory().numpy()
+    e2e_ms = []
+    barrier(world)
+    for i in range(args.warmup + args.steps):
+        t0 = time.perf_counter()
+        bm.mark_all_dirty()
+        bm.upload_scene(ps)          # H2D of every scene buffer + device re-layout
+        frame()
+        ctx.read_composite(host_img)  # D2H of the frame (this rank's tiles)
+        dt = (time.perf_counter() - t0) * 1e3
+        if i >= args.warmup:
+            e2e_ms.append(dt)
+    e2e_total = max_over_ranks(float(np.sum(e2e_ms)), world)
+    e2e_value = total_pixels * args.steps / (e2e_total * 1e-3) / 1e6
+
+    if rank != 0:
+        return
+    # ---- roofline of rt_trace_shade: algorithmic bytes per launch / mean launch time
+    n_lights = len(scene.lights)
+    seg = max(cnt["segments"], 1)
+    V, T, H = cnt["box_tests"] / seg, cnt["tri_tests"] / seg, cnt["shaded"] / seg
+    out_bytes = 16 + 4  # float4 accumulation store + rgba8 composite store per pixel
+    bytes_per_ray = 48 * V + 56 * T + 20 * len(scene.spheres) + 128 * H + 52 * n_lights * H + out_bytes
+    peak, peak_src = measured_peaks()
+    mean_ms = float(np.mean(kernel_ms))
+    achieved = bytes_per_ray * my_pixels / (mean_ms * 1e-3) / 1e9
+    line = {
+        "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps,
+        "warmup": max(args.warmup, 3), "ms_per_step": total_ms / args.steps, "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": wl["desc"], "width": w, "height": h, "triangles": int(len(scene.triangles)),
+                   "bvh_nodes": int(len(scene.bvh_nodes)), "spp": 1, "max_depth": 0,
+                   "traversal": "ordered" if ctx.last_traversal == abi.TRAVERSAL_ORDERED else "literal",
+                   "l2": "flushed between timed frames (512 MiB memset)", "tiles_per_rank": my_tiles,
+                   "parallelism": "tile-split x%d, scene replicated" % world},
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "traffic": None, "kernel": "rt_trace_shade", "peak_source": peak_src,
+                     "bytes_per_ray": bytes_per_ray, "box_tests_per_ray": V, "tri_tests_per_ray": T,
+                     "kernel_ms": mean_ms,
+                     "note": "algorithmic reference-layout bytes (48 V + 56 T + 128 H + 52 L H + out); the scene "
+                             "fits the 126 MB L2, so achieved can exceed the HBM copy peak"},
+        "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": h2d_bytes,
+                "d2h_bytes_per_step": int(host_img.nbytes), "ms_per_step": e2e_total / args.steps},
+        "gpu_launches": int(launches), "clocks": clk,
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        line["cpu_baseline"] = {k: v for k, v in cpu_baseline_sample(scene, wl, args.cpu_seconds).items()
+                                if k in ("value", "unit", "cores", "kind", "sample")}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    args = parse_args()
+    wl = WORKLOADS[args.workload]
+    world, rank, local = dist_setup(args)
+    if args.impl == "reference":
+        run_reference(args, wl, world, rank)
+    else:
+        run_b200(args, wl, world, rank, local)
+    if world > 1 and args.impl != "reference":
+        import torch.distributed as dist
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -82,6 +82,8 @@ struct RtContext {
     DevBuf<float4> wtris;
     DevBuf<uint2> wleaves;
     DevBuf<uint32_t> dflag;
+    DevBuf<unsigned long long> dcounters;
+    bool count_next = false; // next launch is instrumented
     bool relayout_dirty = true;
     bool relayout_ok = false;
 
@@ -264,7 +266,7 @@ int rt_create(int device, RtContext** out) {
                                        1024 * sizeof(uint32_t) + 1024 * sizeof(RtVertex);
     if (c->meta.reserve(c->scene_metadata_capacity_bytes / 4) < 0 || c->mats.reserve(c->mats_capacity) < 0 ||
         c->textures.reserve(c->textures_capacity) < 0 || c->texdata.reserve(c->texdata_capacity) < 0 ||
-        c->tris.reserve(64) < 0 || c->dflag.reserve(1) < 0) {
+        c->tris.reserve(64) < 0 || c->dflag.reserve(1) < 0 || c->dcounters.reserve(8) < 0) {
         fail(nullptr, RT_ERR_CUDA, "rt_create: cudaMalloc failed");
         delete c;
         return RT_ERR_CUDA;
@@ -512,6 +514,7 @@ void fill_scene(RtContext* c, KParams& k) {
     k.accum = c->accum.ptr; k.hits = c->hits.ptr;
     for (int i = 0; i < 3; i++) k.chan[i] = c->chan[i].ptr;
     k.composite = c->composite.ptr;
+    k.counters = c->count_next ? c->dcounters.ptr : nullptr;
 }
 
 void fill_camera(KParams& k, const RtCamera& cam) {
@@ -535,13 +538,19 @@ int launch(RtContext* c, const KParams& k, uint32_t blocks, uint32_t traversal) 
                         c->wide.why_not.empty() ? "push constants differ from the uploaded scene" : c->wide.why_not.c_str());
     }
     CK(c, cudaEventRecord(c->ev0, c->stream));
-    if (ordered) rt_trace_shade<true><<<blocks, 256, 0, c->stream>>>(k);
-    else rt_trace_shade<false><<<blocks, 256, 0, c->stream>>>(k);
+    if (k.counters) {
+        if (ordered) rt_trace_shade<true, true><<<blocks, 256, 0, c->stream>>>(k);
+        else rt_trace_shade<false, true><<<blocks, 256, 0, c->stream>>>(k);
+    } else {
+        if (ordered) rt_trace_shade<true, false><<<blocks, 256, 0, c->stream>>>(k);
+        else rt_trace_shade<false, false><<<blocks, 256, 0, c->stream>>>(k);
+    }
     CK(c, cudaGetLastError());
     CK(c, cudaEventRecord(c->ev1, c->stream));
     c->timed = true;
     c->launches++;
     c->last_traversal = ordered ? RT_TRAVERSAL_ORDERED : RT_TRAVERSAL_LITERAL;
+    c->count_next = false;
     return RT_OK;
 }
 
@@ -687,6 +696,24 @@ float rt_last_kernel_ms(RtContext* c) {
     float ms = -1.0f;
     if (cudaEventElapsedTime(&ms, c->ev0, c->ev1) != cudaSuccess) return -1.0f;
     return ms;
+}
+// Instrumentation: the next render/dispatch launch counts box tests, triangle tests,
+// ray segments and shaded hits (atomics; not for timing).  Read with rt_read_counters.
+int rt_count_next_launch(RtContext* c) {
+    if (!c) return RT_ERR_INVALID_ARGUMENT;
+    CK(c, cudaSetDevice(c->device));
+    CK(c, cudaMemsetAsync(c->dcounters.ptr, 0, 8 * sizeof(unsigned long long), c->stream));
+    c->count_next = true;
+    return RT_OK;
+}
+int rt_read_counters(RtContext* c, uint64_t out[4]) {
+    if (!c || !out) return RT_ERR_INVALID_ARGUMENT;
+    CK(c, cudaSetDevice(c->device));
+    unsigned long long h[4];
+    CK(c, cudaMemcpyAsync(h, c->dcounters.ptr, sizeof h, cudaMemcpyDeviceToHost, c->stream));
+    CK(c, cudaStreamSynchronize(c->stream));
+    for (int i = 0; i < 4; i++) out[i] = h[i];
+    return RT_OK;
 }
 uint64_t rt_launch_count(const RtContext* c) { return c ? c->launches : 0; }
 int rt_last_traversal(const RtContext* c) { return c ? c->last_traversal : 0; }

@@ -65,6 +65,8 @@ struct KParams {
     RtHitRecord* hits;
     uchar4* chan[3];
     uchar4* composite;
+    // instrumented launches only: [0] box tests, [1] triangle tests, [2] ray segments, [3] shaded hits
+    unsigned long long* counters;
 };
 
 struct Ray {
@@ -77,6 +79,7 @@ struct Hit {
     uint32_t prim;  // sphere index / triangle index
     uint32_t material_id;
     V3 point, normal;
+    uint32_t n_box, n_tri; // instrumentation
 };
 
 __device__ __forceinline__ uint32_t meta_at(const KParams& p, uint64_t i) {
@@ -184,12 +187,14 @@ struct TriBest {
     uint32_t mat;
     V3 v0, e1, e2; // winner's geometry (for point/normal)
     bool hit;
+    uint32_t n_box, n_tri; // instrumentation (dead code unless COUNT)
 };
 
 __device__ __forceinline__ void literal_test(const KParams& p, const Ray& ray, uint32_t tri_index, TriBest& b) {
     V3 v0, v1, v2;
     uint32_t mat;
     if (!fetch_triangle_ref(p, tri_index, &v0, &v1, &v2, &mat)) return;
+    b.n_tri++;
     V3 e1 = v1 - v0, e2 = v2 - v0;
     float t = triangle_t(ray, v0, e1, e2);
     if (t > 0.0f && t < b.t) {
@@ -199,7 +204,7 @@ __device__ __forceinline__ void literal_test(const KParams& p, const Ray& ray, u
 
 // shader/src/bvh.rs:18-133 (stack quirk included) / lib.rs:272-296 (brute force)
 __device__ void closest_triangle_literal(const KParams& p, const Ray& ray, float max_t, TriBest& b) {
-    b.t = max_t; b.hit = false; b.prim = 0xFFFFFFFFu; b.mat = 0xFFFFFFFFu;
+    b.t = max_t; b.hit = false; b.prim = 0xFFFFFFFFu; b.mat = 0xFFFFFFFFu; b.n_box = 0; b.n_tri = 0;
     uint32_t node_count = p.off.bvh_nodes_count;
     if (node_count == 0u) {
         for (uint32_t i = 0; i < p.triangle_count; i++) literal_test(p, ray, i, b);
@@ -216,6 +221,7 @@ __device__ void closest_triangle_literal(const KParams& p, const Ray& ray, float
         V3 bmin = mk(meta_f(p, no), meta_f(p, no + 1), meta_f(p, no + 2));
         V3 bmax = mk(meta_f(p, no + 4), meta_f(p, no + 5), meta_f(p, no + 6));
         float entry;
+        b.n_box++;
         if (!slab(ray.o, inv, bmin, bmax, &entry)) continue;
         uint32_t left = meta_at(p, no + 8), right = meta_at(p, no + 9);
         if (left == 0xFFFFFFFFu) {
@@ -247,6 +253,7 @@ __device__ __forceinline__ void ordered_leaf(const KParams& p, const Ray& ray, u
         float4 a = __ldg(tp), c = __ldg(tp + 1), d = __ldg(tp + 2);
         V3 v0 = mk(a.x, a.y, a.z), e1 = mk(a.w, c.x, c.y), e2 = mk(c.z, c.w, d.x);
         float t = triangle_t(ray, v0, e1, e2);
+        b.n_tri++;
         // reference: strict `t < closest` in visit order; with re-ordered visits the
         // equal-t winner is the smaller position in triangle_indices.
         if (t > 0.0f && (t < b.t || (t == b.t && b.hit && pos < best_pos))) {
@@ -261,7 +268,7 @@ __device__ __forceinline__ void ordered_leaf(const KParams& p, const Ray& ray, u
 }
 
 __device__ void closest_triangle_ordered(const KParams& p, const Ray& ray, float max_t, TriBest& b) {
-    b.t = max_t; b.hit = false; b.prim = 0xFFFFFFFFu; b.mat = 0xFFFFFFFFu;
+    b.t = max_t; b.hit = false; b.prim = 0xFFFFFFFFu; b.mat = 0xFFFFFFFFu; b.n_box = 1; b.n_tri = 0;
     uint32_t best_pos = 0u;
     uint32_t cur = p.root_ref;
     if (cur == RT_CHILD_ABSENT) return;
@@ -280,6 +287,7 @@ __device__ void closest_triangle_ordered(const KParams& p, const Ray& ray, float
             float4 q0 = __ldg(np), q1 = __ldg(np + 1), q2 = __ldg(np + 2), q3 = __ldg(np + 3);
             uint32_t lref = __float_as_uint(q3.x), rref = __float_as_uint(q3.y);
             float el, er;
+            b.n_box += 2;
             bool hl = slab(ray.o, inv, mk(q0.x, q0.y, q0.z), mk(q0.w, q1.x, q1.y), &el);
             bool hr = slab(ray.o, inv, mk(q1.z, q1.w, q2.x), mk(q2.y, q2.z, q2.w), &er);
             float limit = b.t * RT_PRUNE_SCALE + RT_PRUNE_ABS;
@@ -320,6 +328,7 @@ __device__ __forceinline__ Hit find_closest(const KParams& p, const Ray& ray) {
     TriBest b;
     if (ORDERED) closest_triangle_ordered(p, ray, closest, b);
     else closest_triangle_literal(p, ray, closest, b);
+    h.n_box = b.n_box; h.n_tri = b.n_tri;
     if (b.hit) { // b.t < sphere t by construction
         h.t = b.t; h.kind = 2u; h.prim = b.prim; h.material_id = b.mat;
         h.point = ray.o + ray.d * b.t;
@@ -442,23 +451,26 @@ __device__ __forceinline__ bool pixel_of_thread(const KParams& p, uint32_t* px, 
     return lx < w && ly < h && *px < p.width && *py < p.height;
 }
 
-template <bool ORDERED>
+template <bool ORDERED, bool COUNT>
 __global__ void __launch_bounds__(256) rt_trace_shade(const __grid_constant__ KParams p) {
     uint32_t px, py;
     if (!pixel_of_thread(p, &px, &py)) return;
+    uint32_t n_seg = 0;
     const bool wavefront = p.mode == RT_MODE_WAVEFRONT0;
     const bool fused = p.use_tiles != 0u;
     const uint32_t channel = fused ? 0xFFu : p.channel;
     V3 color = mk(0.0f, 0.0f, 0.0f);
     Hit h;
-    h.t = FLT_MAX; h.kind = 0u; h.prim = 0xFFFFFFFFu; h.material_id = 0xFFFFFFFFu;
+    h.t = FLT_MAX; h.kind = 0u; h.prim = 0xFFFFFFFFu; h.material_id = 0xFFFFFFFFu; h.n_box = 0; h.n_tri = 0;
     if (!wavefront) {
         Ray ray = camera_ray(p, px, py, 0.5f, 0.5f, false);
+        n_seg = 1;
         h = find_closest<ORDERED>(p, ray);
         if (h.kind != 0u) color = shade_hit(p, h, channel); // miss: (0,0,0), lib.rs:77
     } else if (p.cur_depth <= p.max_depth) {
         // run_wavefront_raytracing, lib.rs:92-149: throughput (1,1,1); sky on miss
         Ray ray = camera_ray(p, px, py, 0.5f, 0.5f, true);
+        n_seg = 1;
         h = find_closest<ORDERED>(p, ray);
         V3 tp = mk(1.0f, 1.0f, 1.0f);
         V3 c = (h.kind != 0u) ? shade_hit(p, h, channel) * tp : mk(0.1f, 0.2f, 0.3f) * tp;
@@ -499,5 +511,11 @@ __global__ void __launch_bounds__(256) rt_trace_shade(const __grid_constant__ KP
     if (p.outputs & RT_OUT_HITS) {
         uint4 rec = make_uint4(h.kind, h.prim, __float_as_uint(h.t), h.material_id);
         reinterpret_cast<uint4*>(p.hits)[pix] = rec;
+    }
+    if (COUNT) {
+        atomicAdd(p.counters + 0, (unsigned long long)h.n_box);
+        atomicAdd(p.counters + 1, (unsigned long long)h.n_tri);
+        atomicAdd(p.counters + 2, (unsigned long long)n_seg);
+        atomicAdd(p.counters + 3, (unsigned long long)(h.kind != 0u ? 1u : 0u));
     }
 }

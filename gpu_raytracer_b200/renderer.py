@@ -83,6 +83,14 @@ class Context:
         self._ck(self.lib.rt_read_hit_records(self.handle, _p(out)))
         return out
 
+    def count_next_launch(self):
+        self._ck(self.lib.rt_count_next_launch(self.handle))
+
+    def read_counters(self):
+        out = np.zeros(4, np.uint64)
+        self._ck(self.lib.rt_read_counters(self.handle, _p(out)))
+        return dict(box_tests=int(out[0]), tri_tests=int(out[1]), segments=int(out[2]), shaded=int(out[3]))
+
     @property
     def last_kernel_ms(self):
         return float(self.lib.rt_last_kernel_ms(self.handle))

@@ -136,6 +136,10 @@ void* rt_device_composite(RtContext* ctx);
 /* GPU time of the last rt_render_frame / rt_dispatch launch in ms (CUDA events
  * on the context stream); <0 if none. */
 float rt_last_kernel_ms(RtContext* ctx);
+/* Instrumentation (not for timing): make the next launch count [0] box tests,
+ * [1] triangle tests, [2] ray segments, [3] shaded hits; read them back. */
+int rt_count_next_launch(RtContext* ctx);
+int rt_read_counters(RtContext* ctx, uint64_t out[4]);
 /* number of kernels this library has launched on ctx since creation */
 uint64_t rt_launch_count(const RtContext* ctx);
 /* which traversal the last launch used (RT_TRAVERSAL_LITERAL / _ORDERED) */
