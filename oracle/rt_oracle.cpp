@@ -249,6 +249,82 @@ static Hit traverse(const Ray& ray, const Bind& b, float max_t, Counters& c) {
     return result;
 }
 
+/* NOT in the reference: the CUDA kernel's declared ORDERED policy (near-first,
+ * conservatively t-pruned, equal-t ties to the smaller triangle_indices position),
+ * restated on the reference node layout.  Used (a) to count the box / triangle
+ * tests of that policy for the roofline's bytes-per-ray and (b) to check on the
+ * CPU that the policy returns exactly the literal policy's hits.  Only valid on
+ * BVHs the product's upload validation accepts (tree, depth < 60, leaves in
+ * increasing triangle_start order). */
+static const float PRUNE_SCALE = 1.001f, PRUNE_ABS = 1.0e-4f;
+static inline bool slab_entry(V3 o, V3 inv, V3 bmin, V3 bmax, float* entry) {
+    V3 t1 = (bmin - o) * inv, t2 = (bmax - o) * inv;
+    V3 tmin = vmin(t1, t2), tmax = vmax(t1, t2);
+    float tmin_max = fmaxf(fmaxf(tmin.x, tmin.y), tmin.z);
+    float tmax_min = fminf(fminf(tmax.x, tmax.y), tmax.z);
+    *entry = tmin_max;
+    return tmax_min >= 0.0f && tmin_max <= tmax_min;
+}
+static Hit traverse_ordered(const Ray& ray, const Bind& b, float max_t, Counters& c) {
+    uint32_t node_count = b.pc->metadata_offsets.bvh_nodes_count;
+    uint32_t n_idx = b.pc->metadata_offsets.triangle_indices_count;
+    Hit result = miss();
+    if (node_count == 0) return result;
+    float closest = max_t;
+    uint32_t best_pos = 0;
+    V3 inv = v3(1.0f / ray.direction.x, 1.0f / ray.direction.y, 1.0f / ray.direction.z);
+    auto box_of = [&](uint32_t n, V3* mn, V3* mx) {
+        uint64_t no = node_off(b, n);
+        *mn = v3(meta_f(b, no), meta_f(b, no + 1), meta_f(b, no + 2));
+        *mx = v3(meta_f(b, no + 4), meta_f(b, no + 5), meta_f(b, no + 6));
+    };
+    V3 mn, mx;
+    float e;
+    box_of(0, &mn, &mx);
+    c.aabb_tests++;
+    if (!slab_entry(ray.origin, inv, mn, mx, &e)) return result;
+    uint32_t stack[64];
+    int sp = 0;
+    uint32_t cur = 0;
+    for (;;) {
+        uint64_t no = node_off(b, cur);
+        uint32_t left = meta_at(b, no + 8), right = meta_at(b, no + 9);
+        if (left == 0xFFFFFFFFu) {
+            uint32_t start = meta_at(b, no + 10), count = meta_at(b, no + 11);
+            for (uint32_t i = 0; i < count && start + i < n_idx; i++) {
+                uint32_t pos = start + i;
+                uint32_t ti = meta_at(b, (uint64_t)b.pc->metadata_offsets.triangle_indices_offset + pos);
+                V3 v0, v1, v2;
+                uint32_t mat;
+                if (!fetch_triangle(b, ti, &v0, &v1, &v2, &mat)) continue;
+                c.tri_tests++;
+                Hit h = test_triangle(ray, v0, v1, v2, mat, FLT_MAX, ti); /* any t > eps */
+                if (h.hit && h.t < max_t &&
+                    (h.t < closest || (h.t == closest && result.hit && pos < best_pos))) {
+                    closest = h.t; result = h; best_pos = pos;
+                }
+            }
+        } else {
+            bool lv = left < node_count, rv = right != 0xFFFFFFFFu && right < node_count;
+            float el = 0, er = 0;
+            bool hl = false, hr = false;
+            float limit = closest * PRUNE_SCALE + PRUNE_ABS;
+            if (lv) { box_of(left, &mn, &mx); c.aabb_tests++; hl = slab_entry(ray.origin, inv, mn, mx, &el) && el <= limit; }
+            if (rv) { box_of(right, &mn, &mx); c.aabb_tests++; hr = slab_entry(ray.origin, inv, mn, mx, &er) && er <= limit; }
+            if (hl && hr) {
+                bool right_first = er < el;
+                stack[sp++] = right_first ? left : right;
+                cur = right_first ? right : left;
+                continue;
+            } else if (hl) { cur = left; continue; }
+            else if (hr) { cur = right; continue; }
+        }
+        if (sp == 0) break;
+        cur = stack[--sp];
+    }
+    return result;
+}
+
 /* shader/src/lib.rs:272-296 */
 static Hit brute_force(const Ray& ray, const Bind& b, float max_t, Counters& c) {
     Hit result = miss();
@@ -266,6 +342,7 @@ static Hit brute_force(const Ray& ray, const Bind& b, float max_t, Counters& c) 
 }
 
 /* shader/src/lib.rs:174-249 (twin: wavefront.rs:214-289) */
+static thread_local int g_policy = 0; /* 0 literal (reference), 1 ordered (kernel's policy) */
 static Hit find_closest(const Ray& ray, const Bind& b, Counters& c) {
     float closest = FLT_MAX - 2.0f;
     /* lib.rs:252-269 */
@@ -279,7 +356,7 @@ static Hit find_closest(const Ray& ray, const Bind& b, Counters& c) {
         }
     }
     if (sphere.hit) closest = sphere.t;
-    Hit tri = b.pc->metadata_offsets.bvh_nodes_count > 0 ? traverse(ray, b, closest, c)
+    Hit tri = b.pc->metadata_offsets.bvh_nodes_count > 0 ? (g_policy == 1 ? traverse_ordered(ray, b, closest, c) : traverse(ray, b, closest, c))
                                                          : brute_force(ray, b, closest, c);
     /* branchless select, lib.rs:216-248 */
     uint32_t sphere_closer = sphere.t < tri.t ? 1u : 0u;
@@ -472,6 +549,12 @@ int orc_hardware_threads(void) {
  * channel<3), `hits` (W*H records). */
 int orc_dispatch(const OrcBindings* ob, const RtPushConstants* pc, uint8_t* image, float* radiance,
                  OrcHit* hits, int threads, OrcCounters* counters) {
+    return orc_dispatch_policy(ob, pc, image, radiance, hits, threads, counters, 0);
+}
+
+/* policy 0: the reference's literal traversal; 1: the kernel's ORDERED policy. */
+int orc_dispatch_policy(const OrcBindings* ob, const RtPushConstants* pc, uint8_t* image, float* radiance,
+                        OrcHit* hits, int threads, OrcCounters* counters, int policy) {
     if (!ob || !pc) return -1;
     Bind b = make_bind(ob, pc);
     uint32_t width = (uint32_t)pc->resolution[0], height = (uint32_t)pc->resolution[1];
@@ -483,6 +566,7 @@ int orc_dispatch(const OrcBindings* ob, const RtPushConstants* pc, uint8_t* imag
     std::vector<Counters> cs((size_t)threads);
     parallel_rows(gh, threads, [&](uint32_t iy, int tid) {
         Counters& c = cs[(size_t)tid];
+        g_policy = policy;
         for (uint32_t ix = 0; ix < gw; ix++) {
             uint32_t px = pc->tile_offset[0] + ix, py = pc->tile_offset[1] + iy;
             if (!(ix < tw && iy < th && px < width && py < height)) continue; /* lib.rs:152-163 */

@@ -36,6 +36,8 @@ typedef struct OrcCounters {
 int orc_hardware_threads(void);
 int orc_dispatch(const OrcBindings* ob, const RtPushConstants* pc, uint8_t* image, float* radiance,
                  OrcHit* hits, int threads, OrcCounters* counters);
+int orc_dispatch_policy(const OrcBindings* ob, const RtPushConstants* pc, uint8_t* image, float* radiance,
+                        OrcHit* hits, int threads, OrcCounters* counters, int policy);
 void orc_composite(const uint8_t* r, const uint8_t* g, const uint8_t* b, uint8_t* out, uint64_t pixels);
 uint16_t orc_f32_to_f16(float f);
 float orc_f16_to_f32(uint16_t h);

@@ -32,6 +32,8 @@ def lib():
         _lib.orc_dispatch.restype = C.c_int
         _lib.orc_dispatch.argtypes = [C.POINTER(OrcBindings), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int,
                                       C.POINTER(OrcCounters)]
+        _lib.orc_dispatch_policy.restype = C.c_int
+        _lib.orc_dispatch_policy.argtypes = _lib.orc_dispatch.argtypes + [C.c_int]
         _lib.orc_composite.restype = None
         _lib.orc_composite.argtypes = [C.c_void_p] * 4 + [C.c_uint64]
         _lib.orc_hardware_threads.restype = C.c_int
@@ -68,14 +70,15 @@ class BoundScene:
         self.bindings = b
 
 
-def dispatch(bound, pc, image, radiance=None, hits=None, threads=None, counters=None):
+def dispatch(bound, pc, image, radiance=None, hits=None, threads=None, counters=None, policy=0):
     """One reference dispatch (src/compute.rs:245-250) on the CPU."""
     threads = threads or hardware_threads()
     pc = np.ascontiguousarray(pc, abi.PushConstants)
-    rc = lib().orc_dispatch(C.byref(bound.bindings), pc.ctypes.data, image.ctypes.data if image is not None else None,
-                            radiance.ctypes.data if radiance is not None else None,
-                            hits.ctypes.data if hits is not None else None, threads,
-                            C.byref(counters) if counters is not None else None)
+    rc = lib().orc_dispatch_policy(C.byref(bound.bindings), pc.ctypes.data,
+                                   image.ctypes.data if image is not None else None,
+                                   radiance.ctypes.data if radiance is not None else None,
+                                   hits.ctypes.data if hits is not None else None, threads,
+                                   C.byref(counters) if counters is not None else None, policy)
     assert rc == 0
     return rc
 
@@ -88,7 +91,7 @@ def tile_rects(width, height, tile=abi.TILE_SIZE):
         yield ox, oy, min(tile, width - ox), min(tile, height - oy), (tx, ty)
 
 
-def render(scene, width, height, wavefront=None, threads=None, camera=None, channels=(0, 1, 2), rows=None):
+def render(scene, width, height, wavefront=None, threads=None, camera=None, channels=(0, 1, 2), rows=None, policy=0):
     """The reference's whole progressive render on the CPU: every tile x 3 colour
     channels (src/compute.rs:157-191) then the main_fs composite.  `rows=(y0,y1)`
     restricts to the tiles intersecting those rows (bounded cpu_baseline samples).
@@ -106,7 +109,7 @@ def render(scene, width, height, wavefront=None, threads=None, camera=None, chan
         for ch in channels:
             pc = push_constants_new([width, height], cam, len(sc.triangles), len(sc.materials), [ox, oy], [tw, th], tt,
                                     bound.tpb, bound.offsets, ch, wavefront=wavefront)
-            dispatch(bound, pc, chans[ch], radiance, hits, threads, counters)
+            dispatch(bound, pc, chans[ch], radiance, hits, threads, counters, policy)
     comp = np.zeros((height, width, 4), np.uint8)
     lib().orc_composite(chans[0].ctypes.data, chans[1].ctypes.data, chans[2].ctypes.data, comp.ctypes.data,
                         width * height)
