@@ -47,6 +47,7 @@ def parse_args():
     ap.add_argument("--workload", default="c3-primary", choices=sorted(WORKLOADS))
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU work for the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--traversal", default="auto", choices=["auto", "literal", "ordered", "rebuilt"])
     return ap.parse_args()
 
 
@@ -225,8 +226,11 @@ def run_b200(args, wl, world, rank, local):
 
     flush = torch.empty(512 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
 
+    trav = {"auto": abi.TRAVERSAL_AUTO, "literal": abi.TRAVERSAL_LITERAL, "ordered": abi.TRAVERSAL_ORDERED,
+            "rebuilt": abi.TRAVERSAL_REBUILT}[args.traversal]
+
     def frame():
-        cr.render_frame(ps.camera, outputs=outputs, tile_stride=stride, tile_phase=phase)
+        cr.render_frame(ps.camera, outputs=outputs, tile_stride=stride, tile_phase=phase, traversal=trav)
 
     for _ in range(max(args.warmup, 3)):
         frame()
@@ -291,7 +295,10 @@ def run_b200(args, wl, world, rank, local):
         "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": wl["desc"], "width": w, "height": h, "triangles": int(len(scene.triangles)),
                    "bvh_nodes": int(len(scene.bvh_nodes)), "spp": 1, "max_depth": 0,
-                   "traversal": "ordered" if ctx.last_traversal == abi.TRAVERSAL_ORDERED else "literal",
+                   "traversal": {abi.TRAVERSAL_LITERAL: "literal", abi.TRAVERSAL_ORDERED: "ordered (uploaded tree)",
+                                 abi.TRAVERSAL_REBUILT: "rebuilt (internal LBVH, winners certified against the "
+                                                        "uploaded tree)"}[ctx.last_traversal],
+                   "literal_fallback_rays": cnt["literal_fallbacks"], "upload_relayout_build_ms": ctx.last_build_ms,
                    "l2": "flushed between timed frames (512 MiB memset)", "tiles_per_rank": my_tiles,
                    "parallelism": "tile-split x%d, scene replicated" % world},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,

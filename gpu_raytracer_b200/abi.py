@@ -56,5 +56,5 @@ INVALID_INDEX = 0xFFFFFFFF
 
 OUT_ACCUM, OUT_HITS, OUT_CHANNELS, OUT_COMPOSITE = 1, 2, 4, 8
 MODE_LEGACY, MODE_WAVEFRONT0, MODE_PATH = 0, 1, 2
-TRAVERSAL_AUTO, TRAVERSAL_LITERAL, TRAVERSAL_ORDERED = 0, 1, 2
+TRAVERSAL_AUTO, TRAVERSAL_LITERAL, TRAVERSAL_ORDERED, TRAVERSAL_REBUILT = 0, 1, 2, 3
 BVH_AUTO, BVH_STANDARD, BVH_CHUNKED, BVH_SMALL_LEAF = 0, 1, 2, 3

@@ -14,6 +14,7 @@
 #include <vector>
 
 #include "rt_kernels.cuh"
+#include "rt_lbvh.cuh"
 
 namespace {
 
@@ -41,6 +42,9 @@ struct WideBvh { // host-side result of validation + node re-layout
     std::string why_not;
     std::vector<float4> nodes;      // 4 per internal node
     std::vector<uint2> leaves;      // (start, effective count) of every reachable non-empty leaf
+    std::vector<uint32_t> leaf_nodes; // uploaded node index of each entry of `leaves`
+    bool nested_ok = false;         // every child box inside its parent's box, no NaN (REBUILT policy needs it)
+    uint32_t max_leaf = 0;          // largest effective leaf
     uint32_t root_ref = RT_CHILD_ABSENT;
     float root_min[3] = {0, 0, 0}, root_max[3] = {0, 0, 0};
     uint32_t max_depth = 0;
@@ -86,6 +90,16 @@ struct RtContext {
     bool count_next = false; // next launch is instrumented
     bool relayout_dirty = true;
     bool relayout_ok = false;
+    // internally rebuilt LBVH (REBUILT policy)
+    DevBuf<uint32_t> wleaf_nodes, leaf_of_pos, lb_vals, lb_vals_sorted, lb_parent_i, lb_parent_l, lb_visits, lb_bounds;
+    DevBuf<unsigned long long> lb_keys, lb_keys_sorted;
+    DevBuf<unsigned char> lb_temp;
+    DevBuf<uint2> lb_children, lb_range;
+    DevBuf<float4> pbox, lb_nbox, bnodes, btris;
+    bool rebuilt_ok = false;
+    uint32_t broot_ref = RT_CHILD_ABSENT;
+    float broot_min[3] = {0, 0, 0}, broot_max[3] = {0, 0, 0};
+    float last_build_ms = -1.0f;
 
     // outputs (src/renderer.rs:452-475) + progressive state (src/renderer.rs:821-855)
     uint32_t width = 0, height = 0;
@@ -138,6 +152,15 @@ void build_wide(const RtBvhNode* nodes, uint32_t n_nodes, uint32_t n_indices, Wi
     stack.push_back({0u, 0u});
     uint64_t prev_end = 0;
     uint32_t n_internal = 0;
+    bool nested = true;
+    auto box_ok = [](const RtAabb& a) {
+        for (int k = 0; k < 3; k++) if (a.min[k] != a.min[k] || a.max[k] != a.max[k]) return false;
+        return true;
+    };
+    auto inside = [](const RtAabb& c, const RtAabb& p) {
+        for (int k = 0; k < 3; k++) if (!(c.min[k] >= p.min[k] && c.max[k] <= p.max[k])) return false;
+        return true;
+    };
     // pass 1: DFS in reference order; number internal nodes; check leaves
     while (!stack.empty()) {
         Item it = stack.back();
@@ -147,6 +170,7 @@ void build_wide(const RtBvhNode* nodes, uint32_t n_nodes, uint32_t n_indices, Wi
         seen[it.node] = 1;
         if (it.depth > w.max_depth) w.max_depth = it.depth;
         if (it.depth >= 60) { w.why_not = "BVH deeper than 60 levels"; return; }
+        nested = nested && box_ok(nd.bounds);
         if (is_leaf(nd)) {
             uint32_t cnt = eff_count(nd);
             if (cnt) {
@@ -154,11 +178,13 @@ void build_wide(const RtBvhNode* nodes, uint32_t n_nodes, uint32_t n_indices, Wi
                 prev_end = (uint64_t)nd.triangle_start + cnt;
                 if (nd.triangle_start & RT_LEAF_FLAG) { w.why_not = "triangle_start >= 2^31"; return; }
                 w.leaves.push_back(make_uint2(nd.triangle_start, cnt));
+                w.leaf_nodes.push_back(it.node);
+                if (cnt > w.max_leaf) w.max_leaf = cnt;
             }
         } else {
             wide_index[it.node] = n_internal++;
-            if (valid_child(nd.right_child)) stack.push_back({nd.right_child, it.depth + 1});
-            if (valid_child(nd.left_child)) stack.push_back({nd.left_child, it.depth + 1});
+            if (valid_child(nd.right_child)) { stack.push_back({nd.right_child, it.depth + 1}); nested = nested && inside(nodes[nd.right_child].bounds, nd.bounds); }
+            if (valid_child(nd.left_child)) { stack.push_back({nd.left_child, it.depth + 1}); nested = nested && inside(nodes[nd.left_child].bounds, nd.bounds); }
         }
     }
     auto ref_of = [&](uint32_t c) -> uint32_t {
@@ -190,6 +216,7 @@ void build_wide(const RtBvhNode* nodes, uint32_t n_nodes, uint32_t n_indices, Wi
     if (is_leaf(root)) w.root_ref = eff_count(root) ? (RT_LEAF_FLAG | root.triangle_start) : RT_CHILD_ABSENT;
     else w.root_ref = wide_index[0];
     w.ordered_ok = true;
+    w.nested_ok = nested;
 }
 
 // ---- device re-layout kernels -------------------------------------------------
@@ -198,11 +225,12 @@ void build_wide(const RtBvhNode* nodes, uint32_t n_nodes, uint32_t n_indices, Wi
 // IEEE subtractions intersection.rs:102-103 performs per test, hoisted to upload.
 __global__ void relayout_triangles(const uint32_t* __restrict__ meta, RtSceneMetadataOffsets off,
                                    const RtTriangle* __restrict__ tris, uint64_t n_tris, uint32_t tpb,
-                                   float4* __restrict__ out, uint32_t* __restrict__ flag) {
+                                   float4* __restrict__ out, float4* __restrict__ pbox, uint32_t* __restrict__ flag) {
     uint32_t pos = blockIdx.x * blockDim.x + threadIdx.x;
     if (pos >= off.triangle_indices_count) return;
     uint32_t ti = meta[(uint64_t)off.triangle_indices_offset + pos];
     float4 a = make_float4(0, 0, 0, 0), b = a, c = a;
+    float4 blo = a, bhi = a;
     c.z = __uint_as_float(ti);
     // triangle_access.rs:26-48: valid iff it falls inside one of the <=3 bound buffers
     bool valid = ti < n_tris && (ti / tpb) <= 2u;
@@ -222,20 +250,27 @@ __global__ void relayout_triangles(const uint32_t* __restrict__ meta, RtSceneMet
             b = make_float4(v1y - v0y, v1z - v0z, v2x - v0x, v2y - v0y);
             c.x = v2z - v0z;
             c.y = __uint_as_float(t.material_id);
+            blo = make_float4(fminf(fminf(v0x, v1x), v2x), fminf(fminf(v0y, v1y), v2y), fminf(fminf(v0z, v1z), v2z), 0.0f);
+            bhi = make_float4(fmaxf(fmaxf(v0x, v1x), v2x), fmaxf(fmaxf(v0y, v1y), v2y), fmaxf(fmaxf(v0z, v1z), v2z), 0.0f);
         }
     }
     c.w = __uint_as_float(1u); // `remaining`, fixed up per leaf below
     out[(uint64_t)pos * 3] = a;
     out[(uint64_t)pos * 3 + 1] = b;
     out[(uint64_t)pos * 3 + 2] = c;
+    if (pbox) { pbox[(uint64_t)pos * 2] = blo; pbox[(uint64_t)pos * 2 + 1] = bhi; }
 }
 // One warp per leaf: remaining[start + i] = count - i.
-__global__ void relayout_leaf_counts(const uint2* __restrict__ leaves, uint32_t n_leaves, float4* __restrict__ out) {
+__global__ void relayout_leaf_counts(const uint2* __restrict__ leaves, const uint32_t* __restrict__ leaf_nodes,
+                                     uint32_t n_leaves, float4* __restrict__ out, uint32_t* __restrict__ leaf_of_pos) {
     uint32_t leaf = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31u;
     if (leaf >= n_leaves) return;
     uint2 l = leaves[leaf];
-    for (uint32_t i = lane; i < l.y; i += 32u)
+    uint32_t node = leaf_nodes[leaf];
+    for (uint32_t i = lane; i < l.y; i += 32u) {
         reinterpret_cast<uint32_t*>(out + (uint64_t)(l.x + i) * 3 + 2)[3] = l.y - i;
+        leaf_of_pos[l.x + i] = node;
+    }
 }
 
 } // namespace
@@ -348,14 +383,18 @@ int rt_update_scene_metadata(RtContext* c, const RtSphere* spheres, uint32_t ns,
         // validation + node re-layout while the host arrays are still borrowed
         build_wide(nodes, nn, ni, c->wide);
         if (c->wide.ordered_ok) {
-            if (c->wnodes.reserve(c->wide.nodes.size()) < 0 || c->wleaves.reserve(c->wide.leaves.size()) < 0)
+            if (c->wnodes.reserve(c->wide.nodes.size()) < 0 || c->wleaves.reserve(c->wide.leaves.size()) < 0 ||
+                c->wleaf_nodes.reserve(c->wide.leaf_nodes.size()) < 0)
                 return fail(c, RT_ERR_CUDA, "wide BVH cudaMalloc failed");
             if (!c->wide.nodes.empty())
                 CK(c, cudaMemcpyAsync(c->wnodes.ptr, c->wide.nodes.data(), c->wide.nodes.size() * sizeof(float4),
                                       cudaMemcpyHostToDevice, c->stream));
-            if (!c->wide.leaves.empty())
+            if (!c->wide.leaves.empty()) {
                 CK(c, cudaMemcpyAsync(c->wleaves.ptr, c->wide.leaves.data(), c->wide.leaves.size() * sizeof(uint2),
                                       cudaMemcpyHostToDevice, c->stream));
+                CK(c, cudaMemcpyAsync(c->wleaf_nodes.ptr, c->wide.leaf_nodes.data(), c->wide.leaf_nodes.size() * 4,
+                                      cudaMemcpyHostToDevice, c->stream));
+            }
         }
         // pageable host memory: the copies above are staged before return, but the
         // std::vectors must outlive the DMA -> wait here (upload is not the hot path)
@@ -474,21 +513,82 @@ int rt_get_metadata_offsets(const RtContext* c, RtSceneMetadataOffsets* out) {
 
 namespace {
 
-// Bring the ORDERED-policy buffers up to date (GPU gather of triangles).
+// Builds the internal small-leaf LBVH over the n triangle positions (rt_lbvh.cuh).
+int build_rebuilt(RtContext* c, uint32_t n) {
+    c->rebuilt_ok = false;
+    if (n == 0 || n >= RT_LBVH_MAX_PRIMS) return RT_OK;
+    size_t temp_bytes = 0;
+    cub::DeviceRadixSort::SortPairs(nullptr, temp_bytes, (unsigned long long*)nullptr, (unsigned long long*)nullptr,
+                                    (uint32_t*)nullptr, (uint32_t*)nullptr, (int)n, 0, 63, c->stream);
+    if (c->lb_keys.reserve(n) < 0 || c->lb_keys_sorted.reserve(n) < 0 || c->lb_vals.reserve(n) < 0 ||
+        c->lb_vals_sorted.reserve(n) < 0 || c->lb_temp.reserve(temp_bytes) < 0 || c->lb_children.reserve(n) < 0 ||
+        c->lb_range.reserve(n) < 0 || c->lb_parent_i.reserve(n) < 0 || c->lb_parent_l.reserve(n) < 0 ||
+        c->lb_visits.reserve(n) < 0 || c->lb_bounds.reserve(8) < 0 || c->lb_nbox.reserve((size_t)n * 2) < 0 ||
+        c->bnodes.reserve((size_t)n * 4) < 0 || c->btris.reserve((size_t)n * 3) < 0)
+        return fail(c, RT_ERR_CUDA, "LBVH cudaMalloc failed for %u triangles", n);
+    const uint32_t g = (n + 255) / 256;
+    const unsigned int init_bounds[6] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0u, 0u, 0u};
+    CK(c, cudaMemcpyAsync(c->lb_bounds.ptr, init_bounds, sizeof init_bounds, cudaMemcpyHostToDevice, c->stream));
+    CK(c, cudaStreamSynchronize(c->stream)); // init_bounds is a stack array
+    lbvh::centroid_bounds<<<g, 256, 0, c->stream>>>(c->pbox.ptr, n, c->lb_bounds.ptr);
+    lbvh::morton_keys<<<g, 256, 0, c->stream>>>(c->pbox.ptr, n, c->lb_bounds.ptr, c->lb_keys.ptr, c->lb_vals.ptr);
+    c->launches += 2;
+    if (cub::DeviceRadixSort::SortPairs(c->lb_temp.ptr, temp_bytes, c->lb_keys.ptr, c->lb_keys_sorted.ptr, c->lb_vals.ptr,
+                                        c->lb_vals_sorted.ptr, (int)n, 0, 63, c->stream) != cudaSuccess)
+        return fail(c, RT_ERR_CUDA, "LBVH radix sort failed");
+    if (n >= 2) {
+        CK(c, cudaMemsetAsync(c->lb_visits.ptr, 0, (size_t)n * 4, c->stream));
+        lbvh::build_radix_tree<<<g, 256, 0, c->stream>>>(c->lb_keys_sorted.ptr, n, c->lb_children.ptr, c->lb_range.ptr,
+                                                         c->lb_parent_i.ptr, c->lb_parent_l.ptr);
+        lbvh::fit_boxes<<<g, 256, 0, c->stream>>>(c->pbox.ptr, c->lb_vals_sorted.ptr, n, c->lb_children.ptr,
+                                                  c->lb_parent_i.ptr, c->lb_parent_l.ptr, c->lb_nbox.ptr, c->lb_visits.ptr);
+        lbvh::emit_wide<<<g, 256, 0, c->stream>>>(c->pbox.ptr, c->lb_vals_sorted.ptr, n, c->lb_children.ptr, c->lb_range.ptr,
+                                                  c->lb_nbox.ptr, c->bnodes.ptr);
+        c->launches += 3;
+    }
+    lbvh::gather_sorted<<<g, 256, 0, c->stream>>>(c->wtris.ptr, c->lb_vals_sorted.ptr, n, c->leaf_of_pos.ptr, c->btris.ptr);
+    c->launches++;
+    // root: the whole tree collapses into one leaf when n <= RT_LBVH_LEAF
+    float4 rb[2];
+    if (n >= 2) CK(c, cudaMemcpyAsync(rb, c->lb_nbox.ptr, sizeof rb, cudaMemcpyDeviceToHost, c->stream));
+    else CK(c, cudaMemcpyAsync(rb, c->pbox.ptr, sizeof rb, cudaMemcpyDeviceToHost, c->stream));
+    CK(c, cudaStreamSynchronize(c->stream));
+    CK(c, cudaGetLastError());
+    float m = 0.0f;
+    const float v[6] = {rb[0].x, rb[0].y, rb[0].z, rb[1].x, rb[1].y, rb[1].z};
+    for (float x : v) m = fmaxf(m, fabsf(x));
+    float pad = m * 1.52587890625e-05f + 1e-30f; // same inflation as lbvh::inflate
+    for (int k = 0; k < 3; k++) { c->broot_min[k] = v[k] - pad; c->broot_max[k] = v[3 + k] + pad; }
+    c->broot_ref = n <= RT_LBVH_LEAF ? (RT_LEAF_FLAG | ((n - 1u) << 28)) : 0u;
+    c->rebuilt_ok = true;
+    return RT_OK;
+}
+
+// Bring the ORDERED / REBUILT policy buffers up to date (all on the GPU).
 int prepare_relayout(RtContext* c) {
     if (!c->relayout_dirty) return RT_OK;
     c->relayout_ok = false;
+    c->rebuilt_ok = false;
     if (c->have_meta && c->wide.ordered_ok) {
         uint32_t ni = c->offsets.triangle_indices_count;
-        if (c->wtris.reserve((size_t)ni * 3 + 3) < 0) return fail(c, RT_ERR_CUDA, "wtris cudaMalloc failed");
+        // REBUILT is worth it (and certifiable) only for big-leaf, properly nested trees
+        bool want_rebuilt = c->wide.nested_ok && c->wide.max_leaf > 2 * RT_LBVH_LEAF && ni < RT_LBVH_MAX_PRIMS;
+        cudaEvent_t e0 = c->ev0, e1 = c->ev1;
+        CK(c, cudaEventRecord(e0, c->stream));
+        if (c->wtris.reserve((size_t)ni * 3 + 3) < 0 || c->leaf_of_pos.reserve((size_t)ni + 1) < 0 ||
+            (want_rebuilt && c->pbox.reserve((size_t)ni * 2 + 2) < 0))
+            return fail(c, RT_ERR_CUDA, "relayout cudaMalloc failed");
         CK(c, cudaMemsetAsync(c->dflag.ptr, 0, 4, c->stream));
+        CK(c, cudaMemsetAsync(c->leaf_of_pos.ptr, 0xFF, ((size_t)ni + 1) * 4, c->stream));
         if (ni) {
             relayout_triangles<<<(ni + 255) / 256, 256, 0, c->stream>>>(c->meta.ptr, c->offsets, c->tris.ptr, c->n_tris,
-                                                                        RT_MAX_TRIANGLES_PER_BUFFER, c->wtris.ptr, c->dflag.ptr);
+                                                                        RT_MAX_TRIANGLES_PER_BUFFER, c->wtris.ptr,
+                                                                        want_rebuilt ? c->pbox.ptr : nullptr, c->dflag.ptr);
             c->launches++;
             uint32_t nl = (uint32_t)c->wide.leaves.size();
             if (nl) {
-                relayout_leaf_counts<<<(nl * 32 + 255) / 256, 256, 0, c->stream>>>(c->wleaves.ptr, nl, c->wtris.ptr);
+                relayout_leaf_counts<<<(nl * 32 + 255) / 256, 256, 0, c->stream>>>(c->wleaves.ptr, c->wleaf_nodes.ptr, nl,
+                                                                                   c->wtris.ptr, c->leaf_of_pos.ptr);
                 c->launches++;
             }
         }
@@ -498,6 +598,13 @@ int prepare_relayout(RtContext* c) {
         CK(c, cudaGetLastError());
         if (flag & 1u) return fail(c, RT_ERR_INVALID_SCENE, "a triangle references a vertex index >= vertices_count");
         c->relayout_ok = true;
+        if (want_rebuilt) {
+            int r = build_rebuilt(c, ni);
+            if (r != RT_OK) return r;
+        }
+        CK(c, cudaEventRecord(e1, c->stream));
+        CK(c, cudaEventSynchronize(e1));
+        cudaEventElapsedTime(&c->last_build_ms, e0, e1);
     }
     c->relayout_dirty = false;
     return RT_OK;
@@ -511,6 +618,9 @@ void fill_scene(RtContext* c, KParams& k) {
     k.wnodes = c->wnodes.ptr; k.wtris = c->wtris.ptr;
     k.root_ref = c->wide.root_ref;
     memcpy(k.root_min, c->wide.root_min, 12); memcpy(k.root_max, c->wide.root_max, 12);
+    k.bnodes = c->bnodes.ptr; k.btris = c->btris.ptr; k.leaf_of_pos = c->leaf_of_pos.ptr;
+    k.broot_ref = c->broot_ref;
+    memcpy(k.broot_min, c->broot_min, 12); memcpy(k.broot_max, c->broot_max, 12);
     k.accum = c->accum.ptr; k.hits = c->hits.ptr;
     for (int i = 0; i < 3; i++) k.chan[i] = c->chan[i].ptr;
     k.composite = c->composite.ptr;
@@ -524,32 +634,37 @@ void fill_camera(KParams& k, const RtCamera& cam) {
     k.fov_scale = tanf(cam.fov * 0.5f * 3.14159265358979323846f / 180.0f);
 }
 
+template <int POLICY>
+void launch_policy(RtContext* c, const KParams& k, uint32_t blocks) {
+    if (k.counters) rt_trace_shade<POLICY, true><<<blocks, 256, 0, c->stream>>>(k);
+    else rt_trace_shade<POLICY, false><<<blocks, 256, 0, c->stream>>>(k);
+}
+
 int launch(RtContext* c, const KParams& k, uint32_t blocks, uint32_t traversal) {
     if (blocks == 0) return RT_OK;
-    bool ordered;
-    if (traversal == RT_TRAVERSAL_LITERAL) ordered = false;
-    else {
-        // the ORDERED layout bakes in the context's buffer split; a dispatch whose
-        // push constants carry another triangles_per_buffer takes the literal path
-        ordered = c->relayout_ok && k.off.bvh_nodes_count > 0 && k.triangles_per_buffer == RT_MAX_TRIANGLES_PER_BUFFER &&
-                  memcmp(&k.off, &c->offsets, sizeof(RtSceneMetadataOffsets)) == 0;
-        if (!ordered && traversal == RT_TRAVERSAL_ORDERED)
-            return fail(c, RT_ERR_INVALID_SCENE, "ordered traversal unavailable: %s",
-                        c->wide.why_not.empty() ? "push constants differ from the uploaded scene" : c->wide.why_not.c_str());
-    }
+    // the re-laid-out buffers bake in the uploaded offsets and the context's buffer
+    // split; a dispatch whose push constants differ from them takes the literal path
+    bool same_scene = k.off.bvh_nodes_count > 0 && k.triangles_per_buffer == RT_MAX_TRIANGLES_PER_BUFFER &&
+                      memcmp(&k.off, &c->offsets, sizeof(RtSceneMetadataOffsets)) == 0;
+    bool can_ordered = c->relayout_ok && same_scene, can_rebuilt = c->rebuilt_ok && same_scene;
+    int policy;
+    if (traversal == RT_TRAVERSAL_LITERAL) policy = 0;
+    else if (traversal == RT_TRAVERSAL_ORDERED) policy = can_ordered ? 1 : -1;
+    else if (traversal == RT_TRAVERSAL_REBUILT) policy = can_rebuilt ? 2 : -1;
+    else policy = can_rebuilt ? 2 : (can_ordered ? 1 : 0);
+    if (policy < 0)
+        return fail(c, RT_ERR_INVALID_SCENE, "requested traversal unavailable: %s",
+                    !same_scene ? "push constants differ from the uploaded scene"
+                                : (c->wide.why_not.empty() ? "BVH not eligible (small leaves, not nested, or too large)" : c->wide.why_not.c_str()));
     CK(c, cudaEventRecord(c->ev0, c->stream));
-    if (k.counters) {
-        if (ordered) rt_trace_shade<true, true><<<blocks, 256, 0, c->stream>>>(k);
-        else rt_trace_shade<false, true><<<blocks, 256, 0, c->stream>>>(k);
-    } else {
-        if (ordered) rt_trace_shade<true, false><<<blocks, 256, 0, c->stream>>>(k);
-        else rt_trace_shade<false, false><<<blocks, 256, 0, c->stream>>>(k);
-    }
+    if (policy == 2) launch_policy<2>(c, k, blocks);
+    else if (policy == 1) launch_policy<1>(c, k, blocks);
+    else launch_policy<0>(c, k, blocks);
     CK(c, cudaGetLastError());
     CK(c, cudaEventRecord(c->ev1, c->stream));
     c->timed = true;
     c->launches++;
-    c->last_traversal = ordered ? RT_TRAVERSAL_ORDERED : RT_TRAVERSAL_LITERAL;
+    c->last_traversal = policy == 2 ? RT_TRAVERSAL_REBUILT : (policy == 1 ? RT_TRAVERSAL_ORDERED : RT_TRAVERSAL_LITERAL);
     c->count_next = false;
     return RT_OK;
 }
@@ -706,16 +821,17 @@ int rt_count_next_launch(RtContext* c) {
     c->count_next = true;
     return RT_OK;
 }
-int rt_read_counters(RtContext* c, uint64_t out[4]) {
+int rt_read_counters(RtContext* c, uint64_t out[5]) {
     if (!c || !out) return RT_ERR_INVALID_ARGUMENT;
     CK(c, cudaSetDevice(c->device));
-    unsigned long long h[4];
+    unsigned long long h[5];
     CK(c, cudaMemcpyAsync(h, c->dcounters.ptr, sizeof h, cudaMemcpyDeviceToHost, c->stream));
     CK(c, cudaStreamSynchronize(c->stream));
-    for (int i = 0; i < 4; i++) out[i] = h[i];
+    for (int i = 0; i < 5; i++) out[i] = h[i];
     return RT_OK;
 }
 uint64_t rt_launch_count(const RtContext* c) { return c ? c->launches : 0; }
 int rt_last_traversal(const RtContext* c) { return c ? c->last_traversal : 0; }
+float rt_last_build_ms(const RtContext* c) { return c ? c->last_build_ms : -1.0f; }
 
 } // extern "C"

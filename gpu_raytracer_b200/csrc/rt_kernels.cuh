@@ -60,12 +60,19 @@ struct KParams {
     const float4* wtris;   // 3 x float4 per triangle position
     uint32_t root_ref;     // internal index, or RT_LEAF_FLAG|start, or RT_CHILD_ABSENT
     float root_min[3], root_max[3];
+    // internally rebuilt small-leaf LBVH (REBUILT policy, rt_lbvh.cuh)
+    const float4* bnodes;          // 4 x float4 per radix-tree node
+    const float4* btris;           // 3 x float4 per sorted slot; last word = triangle_indices position
+    const uint32_t* leaf_of_pos;   // uploaded leaf node of every triangle_indices position
+    uint32_t broot_ref;
+    float broot_min[3], broot_max[3];
     // outputs
     float4* accum;
     RtHitRecord* hits;
     uchar4* chan[3];
     uchar4* composite;
-    // instrumented launches only: [0] box tests, [1] triangle tests, [2] ray segments, [3] shaded hits
+    // instrumented launches only: [0] box tests, [1] triangle tests, [2] ray segments, [3] shaded hits,
+    // [4] rays that re-ran the literal policy (REBUILT certification failed)
     unsigned long long* counters;
 };
 
@@ -79,7 +86,7 @@ struct Hit {
     uint32_t prim;  // sphere index / triangle index
     uint32_t material_id;
     V3 point, normal;
-    uint32_t n_box, n_tri; // instrumentation
+    uint32_t n_box, n_tri, n_fallback; // instrumentation
 };
 
 __device__ __forceinline__ uint32_t meta_at(const KParams& p, uint64_t i) {
@@ -187,7 +194,7 @@ struct TriBest {
     uint32_t mat;
     V3 v0, e1, e2; // winner's geometry (for point/normal)
     bool hit;
-    uint32_t n_box, n_tri; // instrumentation (dead code unless COUNT)
+    uint32_t n_box, n_tri, n_fallback; // instrumentation (dead code unless COUNT)
 };
 
 __device__ __forceinline__ void literal_test(const KParams& p, const Ray& ray, uint32_t tri_index, TriBest& b) {
@@ -308,10 +315,91 @@ __device__ void closest_triangle_ordered(const KParams& p, const Ray& ray, float
     }
 }
 
+// ------------------------------------------------- REBUILT closest-hit policy
+// Traverses the internal LBVH (conservatively inflated boxes, leaves of <= 4
+// triangles), then certifies the winner W against the reference traversal:
+//   * reference result = first-in-DFS-order minimum-t hit among the positions whose
+//     uploaded leaf and all its ancestors pass the reference slab test (no pruning in
+//     the reference, so that set does not depend on the search order);
+//   * W is the minimum over ALL positions the Möller–Trumbore test accepts (ties to
+//     the smaller position == earlier in DFS order), so if W's own chain passes, W is
+//     the reference result;
+//   * upload validated that every ancestor box contains the leaf box component-wise;
+//     (b - o) * inv is monotone in b under IEEE rounding, so for rays without zero
+//     direction components "leaf box passes" implies "every ancestor passes".
+// Hence one exact slab test on W's uploaded leaf box certifies W.  Rays that fail it
+// (or have a zero direction component) re-run the literal policy.
+__device__ void closest_triangle_rebuilt(const KParams& p, const Ray& ray, float max_t, TriBest& b) {
+    if (ray.d.x == 0.0f || ray.d.y == 0.0f || ray.d.z == 0.0f) { closest_triangle_literal(p, ray, max_t, b); b.n_fallback = 1; return; }
+    b.t = max_t; b.hit = false; b.prim = 0xFFFFFFFFu; b.mat = 0xFFFFFFFFu; b.n_box = 1; b.n_tri = 0;
+    uint32_t best_pos = 0u;
+    uint32_t cur = p.broot_ref;
+    if (cur == RT_CHILD_ABSENT) return;
+    V3 inv = mk(1.0f / ray.d.x, 1.0f / ray.d.y, 1.0f / ray.d.z);
+    {
+        float entry;
+        if (!slab(ray.o, inv, mka(p.broot_min), mka(p.broot_max), &entry)) return;
+    }
+    uint32_t stack[64];
+    int sp = 0;
+    for (;;) {
+        if (cur & RT_LEAF_FLAG) {
+            uint32_t slot = cur & 0x0FFFFFFFu, cnt = ((cur >> 28) & 7u) + 1u;
+            for (uint32_t i = 0; i < cnt; i++, slot++) {
+                const float4* tp = p.btris + (uint64_t)slot * 3;
+                float4 a = __ldg(tp), c = __ldg(tp + 1), d = __ldg(tp + 2);
+                V3 v0 = mk(a.x, a.y, a.z), e1 = mk(a.w, c.x, c.y), e2 = mk(c.z, c.w, d.x);
+                float t = triangle_t(ray, v0, e1, e2);
+                b.n_tri++;
+                uint32_t pos = __float_as_uint(d.w);
+                if (t > 0.0f && (t < b.t || (t == b.t && b.hit && pos < best_pos))) {
+                    b.t = t; b.hit = true; best_pos = pos;
+                    b.mat = __float_as_uint(d.y); b.prim = __float_as_uint(d.z);
+                    b.v0 = v0; b.e1 = e1; b.e2 = e2;
+                }
+            }
+        } else {
+            const float4* np = p.bnodes + (uint64_t)cur * 4;
+            float4 q0 = __ldg(np), q1 = __ldg(np + 1), q2 = __ldg(np + 2), q3 = __ldg(np + 3);
+            uint32_t lref = __float_as_uint(q3.x), rref = __float_as_uint(q3.y);
+            float el, er;
+            b.n_box += 2;
+            bool hl = slab(ray.o, inv, mk(q0.x, q0.y, q0.z), mk(q0.w, q1.x, q1.y), &el);
+            bool hr = slab(ray.o, inv, mk(q1.z, q1.w, q2.x), mk(q2.y, q2.z, q2.w), &er);
+            float limit = b.t * RT_PRUNE_SCALE + RT_PRUNE_ABS;
+            hl = hl && (el <= limit);
+            hr = hr && (er <= limit);
+            if (hl && hr) {
+                bool right_first = er < el;
+                stack[sp++] = right_first ? lref : rref;
+                cur = right_first ? rref : lref;
+                continue;
+            } else if (hl) { cur = lref; continue; }
+            else if (hr) { cur = rref; continue; }
+        }
+        if (sp == 0) break;
+        cur = stack[--sp];
+    }
+    if (b.hit) {
+        uint32_t leaf = __ldg(p.leaf_of_pos + best_pos);
+        uint64_t no = (uint64_t)p.off.bvh_nodes_offset + (uint64_t)leaf * 12;
+        float entry;
+        b.n_box++;
+        bool ok = slab(ray.o, inv, mk(meta_f(p, no), meta_f(p, no + 1), meta_f(p, no + 2)),
+                       mk(meta_f(p, no + 4), meta_f(p, no + 5), meta_f(p, no + 6)), &entry);
+        if (!ok) {
+            uint32_t nb = b.n_box, nt = b.n_tri;
+            closest_triangle_literal(p, ray, max_t, b);
+            b.n_box += nb; b.n_tri += nt; b.n_fallback = 1;
+        }
+    }
+}
+
 // ---------------------------------------------------------------- closest hit
 // shader/src/lib.rs:174-269: spheres first (brute force), then triangles seeded
 // with the sphere t; the triangle wins only if strictly closer.
-template <bool ORDERED>
+// POLICY: 0 literal, 1 ordered (uploaded tree), 2 rebuilt (internal LBVH)
+template <int POLICY>
 __device__ __forceinline__ Hit find_closest(const KParams& p, const Ray& ray) {
     Hit h;
     h.t = FLT_MAX; h.kind = 0u; h.prim = 0xFFFFFFFFu; h.material_id = 0xFFFFFFFFu;
@@ -326,9 +414,11 @@ __device__ __forceinline__ Hit find_closest(const KParams& p, const Ray& ray) {
         }
     }
     TriBest b;
-    if (ORDERED) closest_triangle_ordered(p, ray, closest, b);
+    b.n_fallback = 0;
+    if (POLICY == 2) closest_triangle_rebuilt(p, ray, closest, b);
+    else if (POLICY == 1) closest_triangle_ordered(p, ray, closest, b);
     else closest_triangle_literal(p, ray, closest, b);
-    h.n_box = b.n_box; h.n_tri = b.n_tri;
+    h.n_box = b.n_box; h.n_tri = b.n_tri; h.n_fallback = b.n_fallback;
     if (b.hit) { // b.t < sphere t by construction
         h.t = b.t; h.kind = 2u; h.prim = b.prim; h.material_id = b.mat;
         h.point = ray.o + ray.d * b.t;
@@ -451,7 +541,7 @@ __device__ __forceinline__ bool pixel_of_thread(const KParams& p, uint32_t* px, 
     return lx < w && ly < h && *px < p.width && *py < p.height;
 }
 
-template <bool ORDERED, bool COUNT>
+template <int POLICY, bool COUNT>
 __global__ void __launch_bounds__(256) rt_trace_shade(const __grid_constant__ KParams p) {
     uint32_t px, py;
     if (!pixel_of_thread(p, &px, &py)) return;
@@ -461,17 +551,17 @@ __global__ void __launch_bounds__(256) rt_trace_shade(const __grid_constant__ KP
     const uint32_t channel = fused ? 0xFFu : p.channel;
     V3 color = mk(0.0f, 0.0f, 0.0f);
     Hit h;
-    h.t = FLT_MAX; h.kind = 0u; h.prim = 0xFFFFFFFFu; h.material_id = 0xFFFFFFFFu; h.n_box = 0; h.n_tri = 0;
+    h.t = FLT_MAX; h.kind = 0u; h.prim = 0xFFFFFFFFu; h.material_id = 0xFFFFFFFFu; h.n_box = 0; h.n_tri = 0; h.n_fallback = 0;
     if (!wavefront) {
         Ray ray = camera_ray(p, px, py, 0.5f, 0.5f, false);
         n_seg = 1;
-        h = find_closest<ORDERED>(p, ray);
+        h = find_closest<POLICY>(p, ray);
         if (h.kind != 0u) color = shade_hit(p, h, channel); // miss: (0,0,0), lib.rs:77
     } else if (p.cur_depth <= p.max_depth) {
         // run_wavefront_raytracing, lib.rs:92-149: throughput (1,1,1); sky on miss
         Ray ray = camera_ray(p, px, py, 0.5f, 0.5f, true);
         n_seg = 1;
-        h = find_closest<ORDERED>(p, ray);
+        h = find_closest<POLICY>(p, ray);
         V3 tp = mk(1.0f, 1.0f, 1.0f);
         V3 c = (h.kind != 0u) ? shade_hit(p, h, channel) * tp : mk(0.1f, 0.2f, 0.3f) * tp;
         color = color + c;
@@ -517,5 +607,6 @@ __global__ void __launch_bounds__(256) rt_trace_shade(const __grid_constant__ KP
         atomicAdd(p.counters + 1, (unsigned long long)h.n_tri);
         atomicAdd(p.counters + 2, (unsigned long long)n_seg);
         atomicAdd(p.counters + 3, (unsigned long long)(h.kind != 0u ? 1u : 0u));
+        if (h.n_fallback) atomicAdd(p.counters + 4, 1ull);
     }
 }

@@ -1,0 +1,196 @@
+// rt_lbvh.cuh — on-device rebuild of a small-leaf BVH over the uploaded triangle
+// positions (REBUILT traversal policy).
+//
+// Why: the reference's builder for > 100 000 triangles (src/bvh.rs:154-247) emits
+// leaves of 100-1000 consecutive input triangles; traversing that tree costs
+// hundreds of triangle tests per ray.  A drop-in caller still uploads that tree,
+// so at upload this file builds an internal LBVH (Morton order + Karras radix
+// tree, leaves of <= RT_LBVH_LEAF triangles) over the same triangle positions.
+// The kernel traverses the internal tree and then proves the winner is one the
+// reference traversal would also have tested (see closest_triangle_rebuilt in
+// rt_kernels.cuh); otherwise that ray re-runs the literal policy.
+#pragma once
+#include <cub/device/device_radix_sort.cuh>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#define RT_LBVH_LEAF 4u
+// REBUILT leaf ref: bit31 | (count-1) << 28 | first sorted slot (28 bits)
+#define RT_LBVH_MAX_PRIMS (1u << 28)
+
+namespace lbvh {
+
+__device__ __forceinline__ unsigned int f2ord(float f) { // order-preserving float -> uint
+    unsigned int u = __float_as_uint(f);
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ float ord2f(unsigned int u) {
+    return __uint_as_float((u & 0x80000000u) ? (u & 0x7FFFFFFFu) : ~u);
+}
+__device__ __forceinline__ unsigned long long expand21(unsigned long long v) { // 21 bits -> every third bit
+    v &= 0x1FFFFFull;
+    v = (v | v << 32) & 0x1F00000000FFFFull;
+    v = (v | v << 16) & 0x1F0000FF0000FFull;
+    v = (v | v << 8) & 0x100F00F00F00F00Full;
+    v = (v | v << 4) & 0x10C30C30C30C30C3ull;
+    v = (v | v << 2) & 0x1249249249249249ull;
+    return v;
+}
+
+// bounds[0..2] = ordered min of centroids, bounds[3..5] = ordered max
+__global__ void centroid_bounds(const float4* __restrict__ pbox, uint32_t n, unsigned int* __restrict__ bounds) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    float c[3] = {0, 0, 0};
+    bool ok = i < n;
+    if (ok) {
+        float4 lo = pbox[(size_t)i * 2], hi = pbox[(size_t)i * 2 + 1];
+        c[0] = 0.5f * (lo.x + hi.x); c[1] = 0.5f * (lo.y + hi.y); c[2] = 0.5f * (lo.z + hi.z);
+    }
+    for (int k = 0; k < 3; k++) {
+        unsigned int mn = ok ? f2ord(c[k]) : 0xFFFFFFFFu, mx = ok ? f2ord(c[k]) : 0u;
+        for (int o = 16; o; o >>= 1) {
+            mn = min(mn, __shfl_xor_sync(0xFFFFFFFFu, mn, o));
+            mx = max(mx, __shfl_xor_sync(0xFFFFFFFFu, mx, o));
+        }
+        if ((threadIdx.x & 31u) == 0) { atomicMin(bounds + k, mn); atomicMax(bounds + 3 + k, mx); }
+    }
+}
+
+__global__ void morton_keys(const float4* __restrict__ pbox, uint32_t n, const unsigned int* __restrict__ bounds,
+                            unsigned long long* __restrict__ keys, uint32_t* __restrict__ vals) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float4 lo = pbox[(size_t)i * 2], hi = pbox[(size_t)i * 2 + 1];
+    float c[3] = {0.5f * (lo.x + hi.x), 0.5f * (lo.y + hi.y), 0.5f * (lo.z + hi.z)};
+    unsigned long long q[3];
+    for (int k = 0; k < 3; k++) {
+        float mn = ord2f(bounds[k]), mx = ord2f(bounds[3 + k]);
+        float ext = mx - mn;
+        float u = ext > 0.0f ? (c[k] - mn) / ext : 0.0f;
+        u = fminf(fmaxf(u, 0.0f), 1.0f);
+        q[k] = (unsigned long long)min(2097151.0f, u * 2097152.0f);
+    }
+    keys[i] = expand21(q[0]) << 2 | expand21(q[1]) << 1 | expand21(q[2]);
+    vals[i] = i;
+}
+
+// Karras 2012 radix tree over sorted keys; equal keys are split by index.
+__device__ __forceinline__ int delta(const unsigned long long* __restrict__ k, int n, int i, int j) {
+    if (j < 0 || j >= n) return -1;
+    unsigned long long a = k[i], b = k[j];
+    if (a == b) return 64 + __clz((unsigned int)i ^ (unsigned int)j);
+    return __clzll((long long)(a ^ b));
+}
+// child encoding inside the builder: bit31 set = Karras leaf (sorted slot), else internal index
+__global__ void build_radix_tree(const unsigned long long* __restrict__ keys, uint32_t n, uint2* __restrict__ children,
+                                 uint2* __restrict__ range, uint32_t* __restrict__ parent_internal,
+                                 uint32_t* __restrict__ parent_leaf) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    int ni = (int)n - 1;
+    if (i >= ni) return;
+    int d = (delta(keys, n, i, i + 1) - delta(keys, n, i, i - 1)) >= 0 ? 1 : -1;
+    int dmin = delta(keys, n, i, i - d);
+    int lmax = 2;
+    while (delta(keys, n, i, i + lmax * d) > dmin) lmax <<= 1;
+    int l = 0;
+    for (int t = lmax >> 1; t >= 1; t >>= 1)
+        if (delta(keys, n, i, i + (l + t) * d) > dmin) l += t;
+    int j = i + l * d;
+    int dnode = delta(keys, n, i, j);
+    int s = 0, t = l;
+    do {
+        t = (t + 1) >> 1;
+        if (delta(keys, n, i, i + (s + t) * d) > dnode) s += t;
+    } while (t > 1);
+    int gamma = i + s * d + min(d, 0);
+    int lo = min(i, j), hi = max(i, j);
+    uint32_t left = (lo == gamma) ? (0x80000000u | (uint32_t)gamma) : (uint32_t)gamma;
+    uint32_t right = (hi == gamma + 1) ? (0x80000000u | (uint32_t)(gamma + 1)) : (uint32_t)(gamma + 1);
+    children[i] = make_uint2(left, right);
+    range[i] = make_uint2((uint32_t)lo, (uint32_t)hi);
+    if (left & 0x80000000u) parent_leaf[gamma] = (uint32_t)i; else parent_internal[gamma] = (uint32_t)i;
+    if (right & 0x80000000u) parent_leaf[gamma + 1] = (uint32_t)i; else parent_internal[gamma + 1] = (uint32_t)i;
+    if (i == 0) parent_internal[0] = 0xFFFFFFFFu;
+}
+
+// bottom-up fit: the second thread to reach a node computes its box
+__global__ void fit_boxes(const float4* __restrict__ pbox, const uint32_t* __restrict__ sorted_pos, uint32_t n,
+                          const uint2* __restrict__ children, const uint32_t* __restrict__ parent_internal,
+                          const uint32_t* __restrict__ parent_leaf, float4* __restrict__ nbox,
+                          unsigned int* __restrict__ visits) {
+    uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n || n < 2) return;
+    uint32_t node = parent_leaf[k];
+    while (node != 0xFFFFFFFFu) {
+        __threadfence();
+        if (atomicAdd(visits + node, 1u) == 0u) return; // first arrival waits for the sibling
+        uint2 ch = children[node];
+        float4 lo, hi;
+        {
+            const float4* a = (ch.x & 0x80000000u) ? pbox + (size_t)sorted_pos[ch.x & 0x7FFFFFFFu] * 2 : nbox + (size_t)ch.x * 2;
+            const float4* b = (ch.y & 0x80000000u) ? pbox + (size_t)sorted_pos[ch.y & 0x7FFFFFFFu] * 2 : nbox + (size_t)ch.y * 2;
+            // plain (non-__ldg) loads: nbox entries were written by other threads in this launch
+            float4 alo = __ldcg(a), ahi = __ldcg(a + 1), blo = __ldcg(b), bhi = __ldcg(b + 1);
+            lo = make_float4(fminf(alo.x, blo.x), fminf(alo.y, blo.y), fminf(alo.z, blo.z), 0.0f);
+            hi = make_float4(fmaxf(ahi.x, bhi.x), fmaxf(ahi.y, bhi.y), fmaxf(ahi.z, bhi.z), 0.0f);
+        }
+        __stcg(nbox + (size_t)node * 2, lo);
+        __stcg(nbox + (size_t)node * 2 + 1, hi);
+        node = parent_internal[node];
+    }
+}
+
+__device__ __forceinline__ void inflate(float4& lo, float4& hi) {
+    // conservative boxes: a Möller–Trumbore hit implies the true ray passes within a few
+    // ulps (relative to coordinate magnitude) of the triangle; 2^-16 relative is ~100x that
+    float m = fmaxf(fmaxf(fmaxf(fabsf(lo.x), fabsf(hi.x)), fmaxf(fabsf(lo.y), fabsf(hi.y))), fmaxf(fabsf(lo.z), fabsf(hi.z)));
+    float pad = m * 1.52587890625e-05f + 1e-30f;
+    lo.x -= pad; lo.y -= pad; lo.z -= pad; hi.x += pad; hi.y += pad; hi.z += pad;
+}
+
+__device__ __forceinline__ uint32_t emit_ref(uint32_t child, const uint2* __restrict__ range) {
+    if (child & 0x80000000u) return 0x80000000u | (child & 0x7FFFFFFFu); // single triangle: count-1 = 0
+    uint2 r = range[child];
+    uint32_t cnt = r.y - r.x + 1u;
+    if (cnt <= RT_LBVH_LEAF) return 0x80000000u | ((cnt - 1u) << 28) | r.x; // collapsed subtree
+    return child;
+}
+
+// two-child 64-byte nodes in the layout rt_kernels.cuh traverses
+__global__ void emit_wide(const float4* __restrict__ pbox, const uint32_t* __restrict__ sorted_pos, uint32_t n,
+                          const uint2* __restrict__ children, const uint2* __restrict__ range,
+                          const float4* __restrict__ nbox, float4* __restrict__ wnodes) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n < 2 || i >= n - 1) return;
+    uint2 r = range[i];
+    if (r.y - r.x + 1u <= RT_LBVH_LEAF) return; // inside / is a collapsed leaf: never visited
+    uint2 ch = children[i];
+    float4 lo[2], hi[2];
+    uint32_t c[2] = {ch.x, ch.y};
+    for (int k = 0; k < 2; k++) {
+        const float4* s = (c[k] & 0x80000000u) ? pbox + (size_t)sorted_pos[c[k] & 0x7FFFFFFFu] * 2 : nbox + (size_t)c[k] * 2;
+        lo[k] = s[0]; hi[k] = s[1];
+        inflate(lo[k], hi[k]);
+    }
+    float4* q = wnodes + (size_t)i * 4;
+    q[0] = make_float4(lo[0].x, lo[0].y, lo[0].z, hi[0].x);
+    q[1] = make_float4(hi[0].y, hi[0].z, lo[1].x, lo[1].y);
+    q[2] = make_float4(lo[1].z, hi[1].x, hi[1].y, hi[1].z);
+    q[3] = make_float4(__uint_as_float(emit_ref(ch.x, range)), __uint_as_float(emit_ref(ch.y, range)), 0.0f, 0.0f);
+}
+
+// triangle records in sorted order; the last word carries the triangle_indices position
+__global__ void gather_sorted(const float4* __restrict__ wtris, const uint32_t* __restrict__ sorted_pos, uint32_t n,
+                              const uint32_t* __restrict__ leaf_of_pos, float4* __restrict__ out) {
+    uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    uint32_t pos = sorted_pos[k];
+    float4 a = wtris[(size_t)pos * 3], b = wtris[(size_t)pos * 3 + 1], c = wtris[(size_t)pos * 3 + 2];
+    c.w = __uint_as_float(pos);
+    if (leaf_of_pos[pos] == 0xFFFFFFFFu) { // not in any reachable leaf: the reference never tests it
+        a.w = 0.0f; b = make_float4(0.0f, 0.0f, 0.0f, 0.0f); c.x = 0.0f;
+    }
+    out[(size_t)k * 3] = a; out[(size_t)k * 3 + 1] = b; out[(size_t)k * 3 + 2] = c;
+}
+
+} // namespace lbvh

@@ -87,9 +87,10 @@ class Context:
         self._ck(self.lib.rt_count_next_launch(self.handle))
 
     def read_counters(self):
-        out = np.zeros(4, np.uint64)
+        out = np.zeros(5, np.uint64)
         self._ck(self.lib.rt_read_counters(self.handle, _p(out)))
-        return dict(box_tests=int(out[0]), tri_tests=int(out[1]), segments=int(out[2]), shaded=int(out[3]))
+        return dict(box_tests=int(out[0]), tri_tests=int(out[1]), segments=int(out[2]), shaded=int(out[3]),
+                    literal_fallbacks=int(out[4]))
 
     @property
     def last_kernel_ms(self):
@@ -98,6 +99,10 @@ class Context:
     @property
     def launch_count(self):
         return int(self.lib.rt_launch_count(self.handle))
+
+    @property
+    def last_build_ms(self):
+        return float(self.lib.rt_last_build_ms(self.handle))
 
     @property
     def last_traversal(self):

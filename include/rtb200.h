@@ -52,7 +52,11 @@ enum {
     RT_MODE_WAVEFRONT0 = 1,/* main_cs wavefront branch at depth 0, lib.rs:92-149 */
     RT_MODE_PATH = 2       /* EXTENSION (reference stubs it): bounces + spp, SPEC.md */
 };
-enum { RT_TRAVERSAL_AUTO = 0, RT_TRAVERSAL_LITERAL = 1, RT_TRAVERSAL_ORDERED = 2 };
+/* LITERAL: the reference's own DFS.  ORDERED: near-first + t-pruned over the uploaded
+ * tree.  REBUILT: an internal small-leaf LBVH built on the GPU at upload, each winner
+ * certified against the uploaded tree.  All three return identical hit records.
+ * AUTO picks REBUILT for big-leaf trees, else ORDERED, else LITERAL. */
+enum { RT_TRAVERSAL_AUTO = 0, RT_TRAVERSAL_LITERAL = 1, RT_TRAVERSAL_ORDERED = 2, RT_TRAVERSAL_REBUILT = 3 };
 
 /* Whole-frame parameters of the fused path (no reference analogue: replaces the
  * per-tile x per-channel loop of src/compute.rs:157-191 by one launch). */
@@ -137,13 +141,16 @@ void* rt_device_composite(RtContext* ctx);
  * on the context stream); <0 if none. */
 float rt_last_kernel_ms(RtContext* ctx);
 /* Instrumentation (not for timing): make the next launch count [0] box tests,
- * [1] triangle tests, [2] ray segments, [3] shaded hits; read them back. */
+ * [1] triangle tests, [2] ray segments, [3] shaded hits, [4] rays whose REBUILT winner
+ * failed certification and re-ran the literal policy; read them back. */
 int rt_count_next_launch(RtContext* ctx);
-int rt_read_counters(RtContext* ctx, uint64_t out[4]);
+int rt_read_counters(RtContext* ctx, uint64_t out[5]);
 /* number of kernels this library has launched on ctx since creation */
 uint64_t rt_launch_count(const RtContext* ctx);
-/* which traversal the last launch used (RT_TRAVERSAL_LITERAL / _ORDERED) */
+/* which traversal the last launch used (RT_TRAVERSAL_LITERAL / _ORDERED / _REBUILT) */
 int rt_last_traversal(const RtContext* ctx);
+/* GPU time of the last upload-time re-layout + LBVH build, ms (<0 if none) */
+float rt_last_build_ms(const RtContext* ctx);
 
 #ifdef __cplusplus
 }

@@ -103,12 +103,69 @@ def test_c2_terrain_100k_1080p(traversal):
     assert (ref["hits"]["kind"] == 2).mean() > 0.9
 
 
-def test_c3_terrain_1m_chunked_bvh():
-    """1M-triangle terrain on the reference's chunked BVH (100 triangles per leaf)."""
+@pytest.fixture(scope="module")
+def c3_scene_and_ref():
     s = g.terrain_scene(1000, 500)
     assert len(s.triangles) == 1000000 and len(s.bvh_nodes) == 20005
-    w, h = 480, 270
-    ref = ob.render(s, w, h)
-    gpu = render_gpu_fused(s, w, h)
-    assert gpu["traversal"] == abi.TRAVERSAL_ORDERED
+    return s, ob.render(s, 480, 270)
+
+
+@pytest.mark.parametrize("traversal", [abi.TRAVERSAL_LITERAL, abi.TRAVERSAL_ORDERED, abi.TRAVERSAL_REBUILT,
+                                       abi.TRAVERSAL_AUTO])
+def test_c3_terrain_1m_chunked_bvh(c3_scene_and_ref, traversal):
+    """1M-triangle terrain on the reference's chunked BVH (100 triangles per leaf): every
+    traversal policy returns the oracle's hit records bit for bit."""
+    s, ref = c3_scene_and_ref
+    gpu = render_gpu_fused(s, 480, 270, traversal=traversal)
+    assert gpu["traversal"] == (abi.TRAVERSAL_REBUILT if traversal == abi.TRAVERSAL_AUTO else traversal)
     compare(gpu, ref)
+
+
+def test_c3_full_size_policies_agree_1080p():
+    """At BASELINE.json's full size the oracle is too slow for a unit test; the
+    size-independent property is that the three policies agree with each other
+    (ORDERED and LITERAL are pinned to the oracle above)."""
+    s = g.terrain_scene(1000, 500)
+    outs = [render_gpu_fused(s, 1920, 1080, traversal=t) for t in (abi.TRAVERSAL_ORDERED, abi.TRAVERSAL_REBUILT)]
+    check_hits(outs[1]["hits"], outs[0]["hits"])
+    assert np.array_equal(outs[1]["composite"], outs[0]["composite"])
+    assert np.array_equal(outs[1]["accum"].view(np.uint32), outs[0]["accum"].view(np.uint32))
+    assert (outs[0]["hits"]["kind"] == 2).mean() > 0.9
+
+
+def test_rebuilt_policy_grazing_and_inside_cameras():
+    """Cameras that stress the certification step: grazing view along the terrain,
+    a camera inside the terrain bounds, an axis-aligned view (zero direction
+    components -> literal fallback rays), and a random soup on a chunked BVH."""
+    s = g.terrain_scene(400, 300, strategy=abi.BVH_CHUNKED)
+    cams = []
+    for pos, d in (([0, 4.5, 40], [0, -0.05, -1]), ([3, 1.0, 2], [0.6, -0.1, -0.79]), ([0, 30, 0], [0, -1, 0]),
+                   ([-60, 6, 0], [1, -0.08, 0.02])):
+        cam = s.camera.copy()
+        d = np.array(d, np.float32)
+        d /= np.linalg.norm(d)
+        cam["position"], cam["direction"] = pos, d
+        if abs(d[1]) > 0.99:
+            cam["up"] = [0, 0, -1]
+        cams.append(cam)
+    ctx = g.Context(0, 640, 360)
+    g.BufferManager(ctx).upload_scene(s)
+    cr = g.ComputeRenderer(ctx)
+    bound = ob.BoundScene(s)
+    for cam in cams:
+        ref = ob.render(bound, 640, 360, camera=cam, channels=(0,))
+        cr.render_frame(cam, traversal=abi.TRAVERSAL_REBUILT, outputs=abi.OUT_HITS | abi.OUT_ACCUM)
+        assert ctx.last_traversal == abi.TRAVERSAL_REBUILT
+        check_hits(ctx.read_hits(), ref["hits"])
+        assert np.array_equal(ctx.read_accum()[..., 0].view(np.uint32), ref["radiance"][..., 0].view(np.uint32))
+    ctx.close()
+
+
+def test_random_soup_all_policies():
+    import test_oracle
+    s = test_oracle.random_soup(3000, 5).rebuild_bvh(abi.BVH_CHUNKED)
+    ref = ob.render(s, 512, 384)
+    for t in (abi.TRAVERSAL_LITERAL, abi.TRAVERSAL_ORDERED, abi.TRAVERSAL_REBUILT):
+        gpu = render_gpu_fused(s, 512, 384, traversal=t)
+        assert gpu["traversal"] == t
+        compare(gpu, ref)
