@@ -669,6 +669,41 @@ int launch(RtContext* c, const KParams& k, uint32_t blocks, uint32_t traversal) 
     return RT_OK;
 }
 
+int pick_policy(RtContext* c, const KParams& k, uint32_t traversal) {
+    bool same_scene = k.off.bvh_nodes_count > 0 && k.triangles_per_buffer == RT_MAX_TRIANGLES_PER_BUFFER &&
+                      memcmp(&k.off, &c->offsets, sizeof(RtSceneMetadataOffsets)) == 0;
+    bool can_ordered = c->relayout_ok && same_scene, can_rebuilt = c->rebuilt_ok && same_scene;
+    if (traversal == RT_TRAVERSAL_LITERAL) return 0;
+    if (traversal == RT_TRAVERSAL_ORDERED) return can_ordered ? 1 : -1;
+    if (traversal == RT_TRAVERSAL_REBUILT) return can_rebuilt ? 2 : -1;
+    return can_rebuilt ? 2 : (can_ordered ? 1 : 0);
+}
+
+// EXTENSION path tracing: persistent grid, one resident wave of 256-thread blocks
+int launch_path(RtContext* c, const KParams& k, uint32_t traversal) {
+    if (k.n_work == 0) return RT_OK;
+    int policy = pick_policy(c, k, traversal);
+    if (policy < 0) return fail(c, RT_ERR_INVALID_SCENE, "requested traversal unavailable for this scene");
+    const void* fn = policy == 2 ? (const void*)rt_path_trace<2> : policy == 1 ? (const void*)rt_path_trace<1> : (const void*)rt_path_trace<0>;
+    int per_sm = 0, sms = 0;
+    CK(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, 256, 0));
+    CK(c, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device));
+    uint32_t blocks = (uint32_t)(per_sm > 0 ? per_sm : 1) * (uint32_t)sms;
+    uint32_t need = (k.n_work + 255u) / 256u;
+    if (blocks > need) blocks = need;
+    CK(c, cudaEventRecord(c->ev0, c->stream));
+    if (policy == 2) rt_path_trace<2><<<blocks, 256, 0, c->stream>>>(k);
+    else if (policy == 1) rt_path_trace<1><<<blocks, 256, 0, c->stream>>>(k);
+    else rt_path_trace<0><<<blocks, 256, 0, c->stream>>>(k);
+    CK(c, cudaGetLastError());
+    CK(c, cudaEventRecord(c->ev1, c->stream));
+    c->timed = true;
+    c->launches++;
+    c->last_traversal = policy == 2 ? RT_TRAVERSAL_REBUILT : (policy == 1 ? RT_TRAVERSAL_ORDERED : RT_TRAVERSAL_LITERAL);
+    c->count_next = false;
+    return RT_OK;
+}
+
 int check_ready(RtContext* c) {
     if (!c) return RT_ERR_INVALID_ARGUMENT;
     if (c->width == 0) return fail(c, RT_ERR_NOT_READY, "rt_resize has not been called");
@@ -717,8 +752,9 @@ int rt_render_frame(RtContext* c, const RtCamera* cam, const RtFrameParams* fp) 
     int r = check_ready(c);
     if (r) return r;
     if (!cam || !fp) return fail(c, RT_ERR_INVALID_ARGUMENT, "rt_render_frame: NULL argument");
-    if (fp->mode != RT_MODE_LEGACY && fp->mode != RT_MODE_WAVEFRONT0)
-        return fail(c, RT_ERR_INVALID_ARGUMENT, "rt_render_frame: mode %u not available", fp->mode);
+    if (fp->mode > RT_MODE_PATH) return fail(c, RT_ERR_INVALID_ARGUMENT, "rt_render_frame: mode %u unknown", fp->mode);
+    if (fp->mode == RT_MODE_PATH && (fp->spp == 0 || fp->max_depth > 255))
+        return fail(c, RT_ERR_INVALID_ARGUMENT, "rt_render_frame: path mode needs spp >= 1 and max_depth <= 255");
     CK(c, cudaSetDevice(c->device));
     if ((r = prepare_relayout(c)) != RT_OK) return r;
     KParams k;
@@ -737,6 +773,14 @@ int rt_render_frame(RtContext* c, const RtCamera* cam, const RtFrameParams* fp) 
     k.triangles_per_buffer = RT_MAX_TRIANGLES_PER_BUFFER;
     k.triangle_count = (uint32_t)c->n_tris;
     uint32_t my_tiles = k.n_tiles_total > k.tile_phase ? (k.n_tiles_total - k.tile_phase + k.tile_stride - 1) / k.tile_stride : 0;
+    if (fp->mode == RT_MODE_PATH) {
+        k.spp = fp->spp; k.first_sample = fp->first_sample; k.path_max_depth = fp->max_depth; k.base_seed = fp->base_seed;
+        k.n_work = my_tiles * 16384u;
+        k.seg_counter = c->dcounters.ptr + 6;
+        k.work_counter = reinterpret_cast<unsigned int*>(c->dcounters.ptr + 7);
+        CK(c, cudaMemsetAsync(c->dcounters.ptr + 6, 0, 2 * sizeof(unsigned long long), c->stream));
+        return launch_path(c, k, fp->traversal);
+    }
     return launch(c, k, my_tiles * 64u, fp->traversal);
 }
 
@@ -832,6 +876,16 @@ int rt_read_counters(RtContext* c, uint64_t out[5]) {
 }
 uint64_t rt_launch_count(const RtContext* c) { return c ? c->launches : 0; }
 int rt_last_traversal(const RtContext* c) { return c ? c->last_traversal : 0; }
+// ray segments traced by the last RT_MODE_PATH launch (waits for it)
+int rt_last_segments(RtContext* c, uint64_t* out) {
+    if (!c || !out) return RT_ERR_INVALID_ARGUMENT;
+    CK(c, cudaSetDevice(c->device));
+    unsigned long long h = 0;
+    CK(c, cudaMemcpyAsync(&h, c->dcounters.ptr + 6, sizeof h, cudaMemcpyDeviceToHost, c->stream));
+    CK(c, cudaStreamSynchronize(c->stream));
+    *out = h;
+    return RT_OK;
+}
 float rt_last_build_ms(const RtContext* c) { return c ? c->last_build_ms : -1.0f; }
 
 } // extern "C"

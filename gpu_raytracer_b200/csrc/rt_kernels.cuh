@@ -74,6 +74,11 @@ struct KParams {
     // instrumented launches only: [0] box tests, [1] triangle tests, [2] ray segments, [3] shaded hits,
     // [4] rays that re-ran the literal policy (REBUILT certification failed)
     unsigned long long* counters;
+    // RT_MODE_PATH (EXTENSION, SPEC.md)
+    uint32_t spp, first_sample, path_max_depth, base_seed;
+    uint32_t n_work;                 // pixels in this launch's work list (16384 per assigned tile)
+    unsigned int* work_counter;      // persistent-thread work fetch
+    unsigned long long* seg_counter; // ray segments traced (the Mrays/s numerator)
 };
 
 struct Ray {
@@ -492,9 +497,13 @@ __device__ __forceinline__ V3 calculate_lighting(const KParams& p, const Hit& h,
 // enters through ior_for_channel(c) and the final component select, and every
 // Vec3 op is component-wise, so out.c equals pass c's value bit for bit.
 // `channel` < 3 evaluates that single pass; >= 3 the fused triple.
+__device__ __forceinline__ V3 shade_hit_m(const KParams& p, const Hit& h, const MatEval& m, uint32_t channel);
 __device__ __forceinline__ V3 shade_hit(const KParams& p, const Hit& h, uint32_t channel) {
     if (h.material_id >= p.n_mats) return mk(1.0f, 0.0f, 1.0f);
     MatEval m = load_material(p, h.material_id);
+    return shade_hit_m(p, h, m, channel);
+}
+__device__ __forceinline__ V3 shade_hit_m(const KParams& p, const Hit& h, const MatEval& m, uint32_t channel) {
     V3 lighting = calculate_lighting(p, h, m);
     float T = fminf(fmaxf(m.transmission, 0.0f), 1.0f);
     if (!(T > 0.0f)) return lighting;
@@ -609,4 +618,145 @@ __global__ void __launch_bounds__(256) rt_trace_shade(const __grid_constant__ KP
         atomicAdd(p.counters + 3, (unsigned long long)(h.kind != 0u ? 1u : 0u));
         if (h.n_fallback) atomicAdd(p.counters + 4, 1ull);
     }
+}
+
+// ------------------------------------------------ EXTENSION: path tracing kernel
+// SPEC.md.  Persistent threads: the grid is sized to fill the machine once; every lane
+// owns one pixel at a time, runs that pixel's samples in order (so the fp32
+// accumulation order is fixed and the result is bit-reproducible) and, when the pixel
+// is finished, fetches the next one from a global counter with one warp-aggregated
+// atomicAdd (ballot + popc).  Lanes at different bounce depths share the same
+// traversal loop, so a finished path is replaced immediately instead of idling until
+// the slowest path of the warp ends (path regeneration).
+struct SimpleRng { // shader/src/wavefront.rs:46-72
+    uint32_t seed;
+    __device__ __forceinline__ uint32_t next_u32() { seed = seed * 1664525u + 1013904223u; return seed; }
+    __device__ __forceinline__ float next_f32() { return (float)(next_u32() >> 8) / 16777216.0f; }
+    __device__ __forceinline__ float next_f32_signed() { return next_f32() * 2.0f - 1.0f; }
+};
+
+__device__ __forceinline__ bool work_to_pixel(const KParams& p, uint32_t idx, uint32_t* px, uint32_t* py) {
+    uint32_t tile_local = idx >> 14, within = idx & 16383u;
+    uint32_t tile = p.tile_phase + tile_local * p.tile_stride;
+    uint32_t tx = tile % p.tiles_x, ty = tile / p.tiles_x;
+    uint32_t sub = within >> 5, l = within & 31u; // 8x4 pixel groups, 16 across x 32 down per tile
+    *px = tx * RT_TILE_SIZE + (sub & 15u) * 8u + (l & 7u);
+    *py = ty * RT_TILE_SIZE + (sub >> 4) * 4u + (l >> 3);
+    return *px < p.width && *py < p.height;
+}
+
+template <int POLICY>
+__global__ void __launch_bounds__(256) rt_path_trace(const __grid_constant__ KParams p) {
+    const uint32_t lane = threadIdx.x & 31u;
+    const unsigned full = 0xFFFFFFFFu;
+    bool have = false, exhausted = false, new_sample = false;
+    uint32_t px = 0, py = 0, s = 0, depth = 0, n_seg = 0;
+    const uint32_t s_end = p.first_sample + p.spp;
+    SimpleRng rng; rng.seed = 0;
+    Ray ray; ray.o = mk(0, 0, 0); ray.d = mk(0, 0, 1);
+    V3 tp = mk(1, 1, 1), L = mk(0, 0, 0), sum = mk(0, 0, 0);
+    float wsum = 0.0f;
+    for (;;) {
+        unsigned idle = __ballot_sync(full, !have && !exhausted);
+        if (idle) {
+            uint32_t base = 0;
+            int leader = __ffs(idle) - 1;
+            if ((int)lane == leader) base = atomicAdd(p.work_counter, (unsigned int)__popc(idle));
+            base = __shfl_sync(full, base, leader);
+            if (!have && !exhausted) {
+                uint32_t idx = base + __popc(idle & ((1u << lane) - 1u));
+                if (idx >= p.n_work) exhausted = true;
+                else if (work_to_pixel(p, idx, &px, &py)) {
+                    have = true; new_sample = true; s = p.first_sample;
+                    sum = mk(0, 0, 0); wsum = 0.0f;
+                    if (!p.reset_accum) {
+                        float4 old = p.accum[(size_t)py * p.width + px];
+                        sum = mk(old.x, old.y, old.z); wsum = old.w;
+                    }
+                }
+            }
+        }
+        if (__all_sync(full, !have)) {
+            if (__all_sync(full, exhausted)) break;
+            continue;
+        }
+        if (!have) continue;
+        if (new_sample) { // SPEC.md steps 1-2
+            rng.seed = p.base_seed + s + px + py * p.width;
+            float jx = 0.5f, jy = 0.5f;
+            if (s != 0u) { jx = rng.next_f32(); jy = rng.next_f32(); }
+            ray = camera_ray(p, px, py, jx, jy, true);
+            tp = mk(1.0f, 1.0f, 1.0f); L = mk(0.0f, 0.0f, 0.0f); depth = 0; new_sample = false;
+        }
+        Hit h = find_closest<POLICY>(p, ray); // step 3.1
+        n_seg++;
+        if (depth == 0u && s == 0u && (p.outputs & RT_OUT_HITS))
+            reinterpret_cast<uint4*>(p.hits)[(size_t)py * p.width + px] =
+                make_uint4(h.kind, h.prim, __float_as_uint(h.t), h.material_id);
+        bool end = false;
+        if (h.kind == 0u) { L = L + mk(0.1f, 0.2f, 0.3f) * tp; end = true; }
+        else if (h.material_id >= p.n_mats) { L = L + mk(1.0f, 0.0f, 1.0f) * tp; end = true; }
+        else {
+            MatEval m = load_material(p, h.material_id);
+            L = L + shade_hit_m(p, h, m, 0xFFu) * tp;
+            if (depth == p.path_max_depth) end = true;
+            if (!end && depth >= 3u) { // Russian roulette
+                float pr = fminf(fmaxf(fmaxf(fmaxf(tp.x, tp.y), tp.z), 0.05f), 1.0f);
+                float r = rng.next_f32();
+                if (r > pr) end = true;
+                else tp = mk(tp.x / pr, tp.y / pr, tp.z / pr);
+            }
+            if (!end) {
+                float r0 = rng.next_f32();
+                V3 u = mk(0.0f, 0.0f, 0.0f);
+                for (int k = 0; k < 8; k++) {
+                    float a = rng.next_f32_signed(), bb = rng.next_f32_signed(), cc = rng.next_f32_signed();
+                    float q = a * a + bb * bb + cc * cc;
+                    if (q > 1e-6f && q <= 1.0f) { u = mk(a, bb, cc) * (1.0f / sqrtf(q)); break; }
+                }
+                V3 d = ray.d, n = h.normal;
+                float cosi = dot3(n, d);
+                V3 nf = cosi < 0.0f ? n : -n;
+                V3 w = nf + u;
+                if (dot3(w, w) < 1e-8f) w = nf;
+                w = normalize3(w);
+                float T = fminf(fmaxf(m.transmission, 0.0f), 1.0f);
+                V3 dir;
+                float side = 1.0f;
+                if (T > 0.0f && r0 < T) {
+                    float eta = cosi < 0.0f ? 1.0f / m.ior : m.ior;
+                    float c1 = -dot3(d, nf);
+                    float k = 1.0f - eta * eta * (1.0f - c1 * c1);
+                    if (k < 0.0f) dir = d - nf * (2.0f * dot3(d, nf));
+                    else { dir = d * eta + nf * (eta * c1 - sqrtf(k)); side = -1.0f; }
+                    dir = normalize3(dir);
+                } else if (m.metallic > 0.5f) {
+                    V3 mr = d - nf * (2.0f * dot3(d, nf));
+                    dir = mr * (1.0f - m.roughness) + w * m.roughness;
+                    if (dot3(dir, dir) < 1e-8f || dot3(dir, nf) <= 0.0f) dir = w;
+                    dir = normalize3(dir);
+                } else {
+                    dir = w;
+                }
+                tp = tp * m.albedo;
+                ray.o = h.point + nf * (side * 1e-3f);
+                ray.d = dir;
+                depth++;
+            }
+        }
+        if (end) { // step 4
+            sum = sum + L; wsum = wsum + 1.0f; s++;
+            if (s == s_end) {
+                const size_t pix = (size_t)py * p.width + px;
+                if (p.outputs & RT_OUT_ACCUM) p.accum[pix] = make_float4(sum.x, sum.y, sum.z, wsum);
+                if (p.outputs & RT_OUT_COMPOSITE)
+                    p.composite[pix] = make_uchar4((unsigned char)unorm8(sum.x / wsum), (unsigned char)unorm8(sum.y / wsum),
+                                                   (unsigned char)unorm8(sum.z / wsum), 255);
+                have = false;
+            } else new_sample = true;
+        }
+    }
+    // one atomic per warp for the segment count
+    for (int o = 16; o; o >>= 1) n_seg += __shfl_xor_sync(full, n_seg, o);
+    if (lane == 0u && n_seg) atomicAdd(p.seg_counter, (unsigned long long)n_seg);
 }

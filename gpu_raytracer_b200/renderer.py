@@ -101,6 +101,12 @@ class Context:
         return int(self.lib.rt_launch_count(self.handle))
 
     @property
+    def last_segments(self):
+        out = C.c_uint64(0)
+        self._ck(self.lib.rt_last_segments(self.handle, C.byref(out)))
+        return int(out.value)
+
+    @property
     def last_build_ms(self):
         return float(self.lib.rt_last_build_ms(self.handle))
 

@@ -149,6 +149,8 @@ int rt_read_counters(RtContext* ctx, uint64_t out[5]);
 uint64_t rt_launch_count(const RtContext* ctx);
 /* which traversal the last launch used (RT_TRAVERSAL_LITERAL / _ORDERED / _REBUILT) */
 int rt_last_traversal(const RtContext* ctx);
+/* EXTENSION: ray segments traced by the last RT_MODE_PATH launch (SPEC.md) */
+int rt_last_segments(RtContext* ctx, uint64_t* out);
 /* GPU time of the last upload-time re-layout + LBVH build, ms (<0 if none) */
 float rt_last_build_ms(const RtContext* ctx);
 

@@ -502,6 +502,97 @@ static V3 shade_pixel(const Bind& b, uint32_t px, uint32_t py, Hit* out_hit, Cou
     return h.hit ? calculate_shading(b, h, channel, nullptr) : v3(0, 0, 0);
 }
 
+/* ---- EXTENSION (not in the reference; SPEC.md) ------------------------------ */
+/* shader/src/wavefront.rs:46-72 */
+struct SimpleRng {
+    uint32_t seed;
+    uint32_t next_u32() { seed = seed * 1664525u + 1013904223u; return seed; }
+    float next_f32() { return (float)(next_u32() >> 8) / 16777216.0f; }
+    float next_f32_signed() { return next_f32() * 2.0f - 1.0f; }
+};
+
+struct PathParams {
+    uint32_t spp, first_sample, max_depth, base_seed;
+};
+
+/* SPEC.md steps 1-3 for one sample; returns L, counts segments; optionally the primary hit. */
+static V3 path_sample(const Bind& b, uint32_t px, uint32_t py, uint32_t s, const PathParams& pp, Counters& c,
+                      Hit* primary) {
+    const RtPushConstants& pc = *b.pc;
+    uint32_t W = (uint32_t)pc.resolution[0];
+    SimpleRng rng{pp.base_seed + s + px + py * W};
+    float jx = 0.5f, jy = 0.5f;
+    if (s != 0) { jx = rng.next_f32(); jy = rng.next_f32(); }
+    Ray ray;
+    { /* generate_camera_ray with the sub-pixel offset, wavefront.rs:75-112 */
+        float u = ((float)px + jx) / pc.resolution[0];
+        float v = ((float)py + jy) / pc.resolution[1];
+        float aspect = pc.resolution[0] / pc.resolution[1];
+        float fov_scale = tanf(pc.camera.fov * 0.5f * 3.14159265358979323846f / 180.0f);
+        float cx = (u * 2.0f - 1.0f) * aspect * fov_scale;
+        float cy = (1.0f - v * 2.0f) * fov_scale;
+        V3 forward = v3a(pc.camera.direction), up = v3a(pc.camera.up);
+        V3 right = cross(forward, up);
+        V3 true_up = cross(right, forward);
+        ray = Ray{v3a(pc.camera.position), normalize(forward + right * cx + true_up * cy)};
+    }
+    V3 tp = v3(1.0f, 1.0f, 1.0f), L = v3(0, 0, 0);
+    uint32_t depth = 0;
+    for (;;) {
+        c.rays++;
+        Hit h = find_closest(ray, b, c);
+        if (depth == 0 && primary) *primary = h;
+        if (!h.hit) { L = L + v3(0.1f, 0.2f, 0.3f) * tp; break; }
+        if ((uint64_t)h.material_id >= b.materials_len) { L = L + v3(1.0f, 0.0f, 1.0f) * tp; break; }
+        V3 C = v3(calculate_shading(b, h, 0, nullptr).x, calculate_shading(b, h, 1, nullptr).y,
+                  calculate_shading(b, h, 2, nullptr).z);
+        L = L + C * tp;
+        if (depth == pp.max_depth) break;
+        if (depth >= 3) {
+            float p = fminf(fmaxf(fmaxf(fmaxf(tp.x, tp.y), tp.z), 0.05f), 1.0f);
+            float r = rng.next_f32();
+            if (r > p) break;
+            tp = v3(tp.x / p, tp.y / p, tp.z / p);
+        }
+        float r0 = rng.next_f32();
+        V3 u = v3(0, 0, 0);
+        for (int k = 0; k < 8; k++) {
+            float a = rng.next_f32_signed(), bb = rng.next_f32_signed(), cc = rng.next_f32_signed();
+            float q = a * a + bb * bb + cc * cc;
+            if (q > 1e-6f && q <= 1.0f) { u = v3(a, bb, cc) * (1.0f / sqrtf(q)); break; }
+        }
+        Mat m = mat_eval(b.materials[h.material_id]);
+        V3 d = ray.direction, n = h.normal;
+        float cosi = dot(n, d);
+        V3 nf = cosi < 0.0f ? n : -n;
+        V3 w = nf + u;
+        if (dot(w, w) < 1e-8f) w = nf;
+        w = normalize(w);
+        float T = fminf(fmaxf(m.transmission, 0.0f), 1.0f);
+        V3 dir;
+        float side = 1.0f;
+        if (T > 0.0f && r0 < T) {
+            float eta = cosi < 0.0f ? 1.0f / m.ior : m.ior;
+            float c1 = -dot(d, nf);
+            float k = 1.0f - eta * eta * (1.0f - c1 * c1);
+            if (k < 0.0f) dir = d - nf * (2.0f * dot(d, nf));
+            else { dir = d * eta + nf * (eta * c1 - sqrtf(k)); side = -1.0f; }
+            dir = normalize(dir);
+        } else if (m.metallic > 0.5f) {
+            V3 mr = d - nf * (2.0f * dot(d, nf));
+            dir = mr * (1.0f - m.roughness) + w * m.roughness;
+            if (dot(dir, dir) < 1e-8f || dot(dir, nf) <= 0.0f) dir = w;
+            dir = normalize(dir);
+        } else {
+            dir = w;
+        }
+        tp = tp * m.albedo;
+        ray = Ray{h.point + nf * (side * 1e-3f), dir};
+        depth++;
+    }
+    return L;
+}
+
 template <class F>
 static void parallel_rows(uint32_t rows, int threads, F fn) {
     if (threads <= 1 || rows <= 1) {
@@ -602,6 +693,58 @@ int orc_dispatch_policy(const OrcBindings* ob, const RtPushConstants* pc, uint8_
         }
     }
     return 0;
+}
+
+/* EXTENSION (SPEC.md): path tracing with spp / bounces / accumulation over rows
+ * [y0, y1) of the frame.  `pc` supplies resolution, camera, counts and offsets (tile
+ * fields and flags are ignored).  accum: W*H float4 (rgb sum, sample count), updated in
+ * sample order; reset != 0 starts from zero.  hits: primary hit of sample 0 (optional). */
+int orc_render_path(const OrcBindings* ob, const RtPushConstants* pc, uint32_t spp, uint32_t first_sample,
+                    uint32_t max_depth, uint32_t base_seed, int reset, uint32_t y0, uint32_t y1, float* accum,
+                    OrcHit* hits, int threads, OrcCounters* counters, int policy) {
+    if (!ob || !pc || !accum) return -1;
+    Bind b = make_bind(ob, pc);
+    uint32_t width = (uint32_t)pc->resolution[0], height = (uint32_t)pc->resolution[1];
+    if (y1 > height) y1 = height;
+    if (y0 >= y1) return 0;
+    if (threads < 1) threads = 1;
+    PathParams pp{spp, first_sample, max_depth, base_seed};
+    std::vector<Counters> cs((size_t)threads);
+    parallel_rows(y1 - y0, threads, [&](uint32_t iy, int tid) {
+        Counters& c = cs[(size_t)tid];
+        g_policy = policy;
+        uint32_t py = y0 + iy;
+        for (uint32_t px = 0; px < width; px++) {
+            size_t p = (size_t)py * width + px;
+            float* a = accum + p * 4;
+            if (reset) a[0] = a[1] = a[2] = a[3] = 0.0f;
+            for (uint32_t s = first_sample; s < first_sample + spp; s++) {
+                Hit h;
+                V3 L = path_sample(b, px, py, s, pp, c, (s == 0 && hits) ? &h : nullptr);
+                a[0] = a[0] + L.x; a[1] = a[1] + L.y; a[2] = a[2] + L.z; a[3] = a[3] + 1.0f;
+                if (s == 0 && hits) {
+                    hits[p].kind = h.kind; hits[p].prim = h.prim; hits[p].t_bits = f2u(h.t); hits[p].material_id = h.material_id;
+                }
+            }
+        }
+    });
+    if (counters)
+        for (auto& c : cs) {
+            counters->aabb_tests += c.aabb_tests; counters->tri_tests += c.tri_tests;
+            counters->sphere_tests += c.sphere_tests; counters->rays += c.rays;
+        }
+    return 0;
+}
+
+/* resolve: rgb / w -> Rgba8Unorm (SPEC.md step 4) */
+void orc_resolve(const float* accum, uint8_t* out, uint64_t pixels) {
+    for (uint64_t i = 0; i < pixels; i++) {
+        float w = accum[i * 4 + 3];
+        out[i * 4 + 0] = unorm8(accum[i * 4 + 0] / w);
+        out[i * 4 + 1] = unorm8(accum[i * 4 + 1] / w);
+        out[i * 4 + 2] = unorm8(accum[i * 4 + 2] / w);
+        out[i * 4 + 3] = 255;
+    }
 }
 
 /* main_fs (lib.rs:368-391) at 1:1 sampling: out = (R.x, G.y, B.z, 1). */

@@ -34,6 +34,12 @@ def lib():
                                       C.POINTER(OrcCounters)]
         _lib.orc_dispatch_policy.restype = C.c_int
         _lib.orc_dispatch_policy.argtypes = _lib.orc_dispatch.argtypes + [C.c_int]
+        _lib.orc_render_path.restype = C.c_int
+        _lib.orc_render_path.argtypes = [C.POINTER(OrcBindings), C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32,
+                                         C.c_int, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p, C.c_int,
+                                         C.POINTER(OrcCounters), C.c_int]
+        _lib.orc_resolve.restype = None
+        _lib.orc_resolve.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64]
         _lib.orc_composite.restype = None
         _lib.orc_composite.argtypes = [C.c_void_p] * 4 + [C.c_uint64]
         _lib.orc_hardware_threads.restype = C.c_int
@@ -114,5 +120,33 @@ def render(scene, width, height, wavefront=None, threads=None, camera=None, chan
     lib().orc_composite(chans[0].ctypes.data, chans[1].ctypes.data, chans[2].ctypes.data, comp.ctypes.data,
                         width * height)
     return dict(channels=chans, composite=comp, radiance=radiance, hits=hits,
+                counters=dict(aabb_tests=counters.aabb_tests, tri_tests=counters.tri_tests,
+                              sphere_tests=counters.sphere_tests, rays=counters.rays))
+
+
+def render_path(scene, width, height, spp=1, max_depth=0, base_seed=1, first_sample=0, accum=None, rows=None,
+                threads=None, camera=None, policy=0, want_hits=True):
+    """EXTENSION (SPEC.md): path-traced accumulation on the CPU.  Returns dict(accum HxWx4 f32,
+    resolved HxWx4 u8, hits, counters)."""
+    bound = scene if isinstance(scene, BoundScene) else BoundScene(scene)
+    sc = bound.scene
+    cam = sc.camera if camera is None else camera
+    threads = threads or hardware_threads()
+    reset = accum is None
+    if accum is None:
+        accum = np.zeros((height, width, 4), np.float32)
+    hits = np.zeros((height, width), abi.HitRecord) if want_hits else None
+    y0, y1 = rows if rows is not None else (0, height)
+    pc = push_constants_new([width, height], cam, len(sc.triangles), len(sc.materials), [0, 0], [width, height], [1, 1],
+                            bound.tpb, bound.offsets, 0, wavefront=(0, max_depth, base_seed))
+    counters = OrcCounters()
+    rc = lib().orc_render_path(C.byref(bound.bindings), pc.ctypes.data, spp, first_sample, max_depth, base_seed,
+                               int(reset), y0, y1, accum.ctypes.data, hits.ctypes.data if want_hits else None, threads,
+                               C.byref(counters), policy)
+    assert rc == 0
+    resolved = np.zeros((height, width, 4), np.uint8)
+    with np.errstate(all="ignore"):
+        lib().orc_resolve(accum.ctypes.data, resolved.ctypes.data, width * height)
+    return dict(accum=accum, resolved=resolved, hits=hits,
                 counters=dict(aabb_tests=counters.aabb_tests, tri_tests=counters.tri_tests,
                               sphere_tests=counters.sphere_tests, rays=counters.rays))

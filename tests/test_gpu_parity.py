@@ -169,3 +169,66 @@ def test_random_soup_all_policies():
         gpu = render_gpu_fused(s, 512, 384, traversal=t)
         assert gpu["traversal"] == t
         compare(gpu, ref)
+
+
+# ---- EXTENSION (SPEC.md): path tracing, bit-exact vs the extension oracle ------
+def render_gpu_path(scene, w, h, spp, max_depth, base_seed=1, traversal=abi.TRAVERSAL_AUTO, chunks=None):
+    ctx = g.Context(0, w, h)
+    g.BufferManager(ctx).upload_scene(scene)
+    cr = g.ComputeRenderer(ctx)
+    segs, first = 0, 0
+    for n in (chunks or [spp]):
+        cr.render_frame(scene.camera, mode=abi.MODE_PATH, spp=n, first_sample=first, max_depth=max_depth,
+                        base_seed=base_seed, reset_accum=(first == 0), traversal=traversal,
+                        outputs=abi.OUT_ACCUM | abi.OUT_HITS | abi.OUT_COMPOSITE)
+        segs += ctx.last_segments
+        first += n
+    out = dict(accum=ctx.read_accum(), hits=ctx.read_hits(), composite=ctx.read_composite(), segments=segs,
+               traversal=ctx.last_traversal)
+    ctx.close()
+    return out
+
+
+def compare_path(gpu, ref):
+    check_hits(gpu["hits"], ref["hits"])
+    assert gpu["segments"] == ref["counters"]["rays"]
+    bad = gpu["accum"].view(np.uint32) != ref["accum"].view(np.uint32)
+    assert not bad.any(), (int(bad.sum()), np.argwhere(bad)[:4], gpu["accum"][bad][:4], ref["accum"][bad][:4])
+    assert np.array_equal(gpu["composite"], ref["resolved"])
+
+
+def test_path_spp1_depth0_is_reference_wavefront(default_ref):
+    s, _ = default_ref
+    wf = ob.render(s, 640, 360, wavefront=(0, 4, 5))
+    gpu = render_gpu_path(s, 640, 360, 1, 0, base_seed=5)
+    check_hits(gpu["hits"], wf["hits"])
+    assert np.array_equal(gpu["accum"][..., :3].view(np.uint32), wf["radiance"].view(np.uint32))
+    assert np.array_equal(gpu["composite"], wf["composite"])
+
+
+@pytest.mark.parametrize("traversal", [abi.TRAVERSAL_LITERAL, abi.TRAVERSAL_ORDERED])
+def test_c4_cornell_depth8(traversal):
+    """C4: Cornell box, diffuse bounces to depth 8 (incoherent rays; divergence stress)."""
+    s = g.cornell_scene()
+    ref = ob.render_path(s, 256, 256, spp=8, max_depth=8, base_seed=11)
+    gpu = render_gpu_path(s, 256, 256, 8, 8, base_seed=11, traversal=traversal)
+    compare_path(gpu, ref)
+    assert gpu["segments"] > 256 * 256 * 8 * 3
+
+
+def test_path_default_scene_glass_metal_and_resume(default_ref):
+    s, _ = default_ref
+    ref = ob.render_path(s, 320, 180, spp=6, max_depth=5, base_seed=2)
+    gpu = render_gpu_path(s, 320, 180, 6, 5, base_seed=2, chunks=[1, 2, 3])  # progressive in 3 calls
+    compare_path(gpu, ref)
+
+
+@pytest.mark.parametrize("traversal", [abi.TRAVERSAL_ORDERED, abi.TRAVERSAL_REBUILT])
+def test_c3_path_terrain_1m(c3_scene_and_ref, traversal):
+    """C3 semantics (4 bounces) on the 1M-triangle terrain at reduced size/spp so the oracle finishes."""
+    s, _ = c3_scene_and_ref
+    w, h = 240, 136
+    ref = ob.render_path(s, w, h, spp=2, max_depth=4, base_seed=1, policy=1)
+    gpu = render_gpu_path(s, w, h, 2, 4, base_seed=1, traversal=traversal)
+    assert gpu["traversal"] == traversal
+    compare_path(gpu, ref)

@@ -213,3 +213,39 @@ def test_ordered_policy_equals_literal_on_terrains():
         a, b = ob.render(sc, w, h, channels=(1,)), ob.render(sc, w, h, channels=(1,), policy=1)
         for f in ("kind", "prim", "t_bits", "material_id"):
             assert np.array_equal(a["hits"][f], b["hits"][f]), (sc.name, f)
+
+
+# ---- EXTENSION (SPEC.md): path tracing on the CPU oracle -----------------------
+def test_path_spp1_depth0_equals_wavefront_depth0():
+    s = g.default_scene()
+    wf = ob.render(s, 96, 54, wavefront=(0, 4, 9))
+    pt = ob.render_path(s, 96, 54, spp=1, max_depth=0, base_seed=9)
+    assert np.array_equal(pt["accum"][..., :3].view(np.uint32), wf["radiance"].view(np.uint32))
+    assert np.all(pt["accum"][..., 3] == 1.0)
+    assert np.array_equal(pt["resolved"], wf["composite"])
+    for f in ("kind", "prim", "t_bits", "material_id"):
+        assert np.array_equal(pt["hits"][f], wf["hits"][f])
+    assert pt["counters"]["rays"] == 96 * 54
+
+
+def test_path_progressive_accumulation_is_resumable_and_thread_independent():
+    s = g.cornell_scene()
+    full = ob.render_path(s, 48, 48, spp=6, max_depth=4, base_seed=3)
+    part = ob.render_path(s, 48, 48, spp=2, max_depth=4, base_seed=3, threads=1)
+    part = ob.render_path(s, 48, 48, spp=4, max_depth=4, base_seed=3, first_sample=2, accum=part["accum"], threads=3)
+    assert np.array_equal(full["accum"].view(np.uint32), part["accum"].view(np.uint32))
+    assert np.all(full["accum"][..., 3] == 6.0)
+    assert full["counters"]["rays"] > 48 * 48 * 6 * 2  # bounces happen
+    assert np.isfinite(full["accum"]).all() and full["accum"][..., :3].min() >= 0
+    # literal and ordered traversal policies agree on incoherent bounce rays too
+    o = ob.render_path(s, 48, 48, spp=6, max_depth=4, base_seed=3, policy=1)
+    assert np.array_equal(full["accum"].view(np.uint32), o["accum"].view(np.uint32))
+
+
+def test_path_depth_increases_radiance_and_segments_bounded():
+    s = g.cornell_scene()
+    d0 = ob.render_path(s, 32, 32, spp=4, max_depth=0, base_seed=1)
+    d8 = ob.render_path(s, 32, 32, spp=4, max_depth=8, base_seed=1)
+    assert d8["accum"][..., :3].sum() > d0["accum"][..., :3].sum()
+    assert d0["counters"]["rays"] == 32 * 32 * 4
+    assert 32 * 32 * 4 < d8["counters"]["rays"] <= 32 * 32 * 4 * 9
