@@ -25,16 +25,26 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 WORKLOADS = {
-    # name: (terrain nx, nz, width, height, bvh strategy name, description)
-    "c3-primary": dict(nx=1000, nz=500, w=1920, h=1080, bvh="auto",
+    # BASELINE.json configs[2] — the configuration the metric is quoted on ("1080p, 1M-tri scene")
+    "c3": dict(nx=1000, nz=500, w=1920, h=1080, bvh="auto", mode="path", spp=16, depth=4,
+               desc="C3: procedural 1M-triangle terrain, 1920x1080, 4 bounces, 16 spp progressive accumulation "
+                    "(EXTENSION semantics, SPEC.md: the reference stubs bounces/spp), scene uploaded with the "
+                    "reference's chunked BVH (100 tris/leaf)"),
+    "c3-primary": dict(nx=1000, nz=500, w=1920, h=1080, bvh="auto", mode="primary", spp=1, depth=0,
                        desc="C3 scene: procedural 1M-triangle terrain, 1920x1080, primary rays + direct shading "
                             "(reference semantics), reference chunked BVH (100 tris/leaf)"),
-    "c2": dict(nx=250, nz=200, w=1920, h=1080, bvh="auto",
+    "c2": dict(nx=250, nz=200, w=1920, h=1080, bvh="auto", mode="primary", spp=1, depth=0,
                desc="C2: procedural 100K-triangle terrain, 1920x1080, primary rays + direct shading, "
                     "standard-format BVH (1 tri/leaf)"),
-    "c3-primary-smallleaf": dict(nx=1000, nz=500, w=1920, h=1080, bvh="small_leaf",
+    "c3-primary-smallleaf": dict(nx=1000, nz=500, w=1920, h=1080, bvh="small_leaf", mode="primary", spp=1, depth=0,
                                  desc="C3 scene, primary rays + direct shading, small-leaf BVH (<=4 tris/leaf) in "
                                       "the reference node format"),
+    "c4": dict(scene="cornell", w=1024, h=1024, bvh="auto", mode="path", spp=64, depth=8,
+               desc="C4: Cornell box (36 triangles), 1024x1024, diffuse bounces to depth 8, 64 spp (EXTENSION "
+                    "semantics, SPEC.md) - divergence stress"),
+    "c5": dict(nx=2500, nz=2000, w=3840, h=2160, bvh="auto", mode="path", spp=1, depth=4,
+               desc="C5: procedural 10M-triangle terrain, 3840x2160, 4 bounces, 1 spp (EXTENSION semantics), "
+                    "reference chunked BVH (1000 tris/leaf)"),
 }
 
 
@@ -44,7 +54,7 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="c3-primary", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU work for the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--traversal", default="auto", choices=["auto", "literal", "ordered", "rebuilt"])
@@ -92,6 +102,8 @@ def build_scene(wl):
     import gpu_raytracer_b200 as g
     from gpu_raytracer_b200 import abi
     strat = {"auto": abi.BVH_AUTO, "small_leaf": abi.BVH_SMALL_LEAF, "standard": abi.BVH_STANDARD}[wl["bvh"]]
+    if wl.get("scene") == "cornell":
+        return g.cornell_scene(strat)
     return g.terrain_scene(wl["nx"], wl["nz"], seed=1, strategy=strat)
 
 
@@ -104,33 +116,47 @@ def measured_peaks():
 
 
 def cpu_baseline_sample(scene, wl, target_seconds):
-    """Times the oracle (reference policy: literal traversal, 3 channel passes per
-    tile) on a bounded band of tile rows of the same frame, all host threads."""
+    """Times the oracle on a bounded band of rows of the same frame, all host threads.
+    Primary workloads: the reference's own loop (literal traversal, 3 channel passes per
+    tile).  Path workloads: the extension oracle (SPEC.md) with the literal traversal."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import oracle_binding as ob
     bound = ob.BoundScene(scene)
     w, h = wl["w"], wl["h"]
     threads = ob.hardware_threads()
+    if wl["mode"] == "path":
+        spp, depth = wl["spp"], wl["depth"]
+        y = h // 2
+        t0 = time.perf_counter()
+        ob.render_path(bound, w, h, spp=1, max_depth=depth, rows=(y, y + 2), threads=threads, want_hits=False)
+        per_row_sample = max((time.perf_counter() - t0) / 2.0, 1e-4)  # one row, one sample
+        # prefer full spp on fewer rows so the sample is the workload's own mix of samples
+        nrows = int(max(2, min(h, target_seconds / (per_row_sample * spp))))
+        y0 = max(0, (h - nrows) // 2)
+        t0 = time.perf_counter()
+        r = ob.render_path(bound, w, h, spp=spp, max_depth=depth, rows=(y0, y0 + nrows), threads=threads, want_hits=False)
+        dt = time.perf_counter() - t0
+        return {"value": r["counters"]["rays"] / dt / 1e6, "unit": "Mrays/s", "cores": threads, "kind": "port",
+                "sample": "rows %d-%d of the %dx%d frame, %d spp, depth %d, literal traversal, %d ray segments, %.1f s"
+                          % (y0, y0 + nrows, w, h, spp, depth, r["counters"]["rays"], dt), "seconds": dt}
     # probe: one 128-row band centred vertically, one channel, to size the sample
     mid = (h // 2) // 128 * 128
     t0 = time.perf_counter()
     ob.render(bound, w, h, channels=(0,), rows=(mid, mid + 1), threads=threads)
-    probe = time.perf_counter() - t0  # one band, one channel
-    band_cost = probe * 3.0
+    band_cost = (time.perf_counter() - t0) * 3.0
     n_bands_total = (h + 127) // 128
     n_bands = int(max(1, min(n_bands_total, target_seconds // max(band_cost, 1e-3))))
     first = max(0, (n_bands_total - n_bands) // 2)
     rows = (first * 128, min(h, (first + n_bands) * 128))
     t0 = time.perf_counter()
-    r = ob.render(bound, w, h, rows=rows, threads=threads)
+    ob.render(bound, w, h, rows=rows, threads=threads)
     dt = time.perf_counter() - t0
     pixels = (rows[1] - rows[0]) * w
     # the reference traces every pixel three times (one dispatch per colour channel);
     # the metric counts one camera ray per pixel, like the GPU arm
     return {"value": pixels / dt / 1e6, "unit": "Mrays/s", "cores": threads, "kind": "port",
             "sample": "rows %d-%d of the %dx%d frame (%d of %d tile bands), 3 channel passes, literal traversal, %.1f s"
-                      % (rows[0], rows[1], w, h, n_bands, n_bands_total, dt),
-            "traced_rays_per_s_M": r["counters"]["rays"] / dt / 1e6, "seconds": dt}
+                      % (rows[0], rows[1], w, h, n_bands, n_bands_total, dt), "seconds": dt}
 
 
 def dist_setup(args):
@@ -182,8 +208,10 @@ def run_reference(args, wl, world, rank):
     secs = float(np.mean([x["seconds"] for x in vals]))
     line = {"impl": "reference", "metric": "Mrays/s", "value": v, "unit": "Mrays/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": secs * 1e3, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": wl["desc"], "width": wl["w"], "height": wl["h"]},
+            "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": wl["desc"], "width": wl["w"], "height": wl["h"], "spp": wl["spp"],
+                       "max_depth": wl["depth"],
+                       "semantics": "extension (SPEC.md)" if wl["mode"] == "path" else "reference"},
             "cpu_baseline": {"value": v, "unit": "Mrays/s", "cores": last["cores"], "kind": "port",
                              "sample": last["sample"]},
             "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -191,121 +219,168 @@ def run_reference(args, wl, world, rank):
     print(json.dumps(line), flush=True)
 
 
+
+
+def sum_over_ranks(x, world):
+    if world == 1:
+        return x
+    import torch
+    import torch.distributed as dist
+    t = torch.tensor([x], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    return float(t.item())
+
+
 def run_b200(args, wl, world, rank, local):
     import torch
+    import torch.distributed as dist
     import gpu_raytracer_b200 as g
-    from gpu_raytracer_b200 import abi
+    from gpu_raytracer_b200 import abi, tiles
 
     torch.cuda.set_device(local)
     scene = build_scene(wl)
     w, h = wl["w"], wl["h"]
+    path = wl["mode"] == "path"
     ctx = g.Context(local, w, h)
     bm, cr = g.BufferManager(ctx), g.ComputeRenderer(ctx)
+    stream = torch.cuda.ExternalStream(ctx.stream, device=local)  # the context's stream, for events + NCCL ordering
     # host inputs in pinned memory (the e2e leg copies from these every step)
-    pinned = {}
-    for name in ("spheres", "lights", "bvh_nodes", "triangle_indices", "vertices", "triangles", "materials"):
+    names = ("spheres", "lights", "bvh_nodes", "triangle_indices", "vertices", "triangles", "materials")
+    pinned, keep = {}, []
+    for name in names:
         a = np.ascontiguousarray(getattr(scene, name))
-        t = torch.from_numpy(a.view(np.uint8).reshape(-1).copy()).pin_memory() if a.size else None
-        pinned[name] = t.numpy().view(a.dtype) if t is not None else a
-        pinned["_keep_" + name] = t
+        if a.size:
+            t = torch.from_numpy(a.view(np.uint8).reshape(-1).copy()).pin_memory()
+            keep.append(t)
+            pinned[name] = t.numpy().view(a.dtype)
+        else:
+            pinned[name] = a
     ps = g.Scene(scene.camera, pinned["spheres"], pinned["triangles"], pinned["vertices"], pinned["materials"],
                  pinned["lights"], pinned["bvh_nodes"], pinned["triangle_indices"])
-    h2d_bytes = sum(int(np.asarray(getattr(ps, n)).nbytes) for n in
-                    ("spheres", "lights", "bvh_nodes", "triangle_indices", "vertices", "triangles", "materials"))
+    h2d_bytes = sum(int(pinned[n].nbytes) for n in names)
     bm.upload_scene(ps)
     stride, phase = (world, rank) if world > 1 else (0, 0)
     outputs = abi.OUT_ACCUM | abi.OUT_COMPOSITE
-    tiles_total = ((w + 127) // 128) * ((h + 127) // 128)
-    my_tiles = len(range(rank, tiles_total, world))
-    # rays this rank traces per frame (edge tiles are clipped to the image)
-    my_pixels = 0
-    tx = (w + 127) // 128
-    for t in range(rank, tiles_total, world):
-        ox, oy = (t % tx) * 128, (t // tx) * 128
-        my_pixels += min(128, w - ox) * min(128, h - oy)
-
-    flush = torch.empty(512 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
-
+    my_tiles = len(tiles.tiles_of_rank(w, h, world, rank))
+    my_pixels = tiles.pixels_of_rank(w, h, world, rank)
     trav = {"auto": abi.TRAVERSAL_AUTO, "literal": abi.TRAVERSAL_LITERAL, "ordered": abi.TRAVERSAL_ORDERED,
             "rebuilt": abi.TRAVERSAL_REBUILT}[args.traversal]
+    gather = tiles.TileGather(dist, torch, w, h, tiles.WHAT_COMPOSITE, "cuda") if world > 1 else None
+    flush = torch.empty(512 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
+
+    def render():
+        if path:
+            cr.render_frame(ps.camera, mode=abi.MODE_PATH, spp=wl["spp"], max_depth=wl["depth"], base_seed=1,
+                            outputs=outputs, tile_stride=stride, tile_phase=phase, traversal=trav)
+        else:
+            cr.render_frame(ps.camera, outputs=outputs, tile_stride=stride, tile_phase=phase, traversal=trav)
 
     def frame():
-        cr.render_frame(ps.camera, outputs=outputs, tile_stride=stride, tile_phase=phase, traversal=trav)
+        """One step: trace this rank's tiles, then (N > 1) gather the finished tiles to rank 0."""
+        render()
+        if gather is not None:
+            with torch.cuda.stream(stream):  # NCCL is ordered after the kernel on the context's stream
+                gather.run(lambda dst: ctx.pack_tiles(tiles.WHAT_COMPOSITE, world, rank, dst.data_ptr()),
+                           lambda src, r: ctx.unpack_tiles(tiles.WHAT_COMPOSITE, world, r, src.data_ptr()))
 
     for _ in range(max(args.warmup, 3)):
         frame()
     ctx.synchronize()
+    torch.cuda.synchronize()
 
-    # instrumented launch (untimed): algorithmic work per ray for the roofline
+    # instrumented launch (untimed): algorithmic work per ray segment for the roofline
     ctx.count_next_launch()
-    frame()
+    render()
     cnt = ctx.read_counters()
+    seg_per_frame_rank = ctx.last_segments if path else my_pixels
+    seg_per_frame = sum_over_ranks(float(seg_per_frame_rank), world)
 
-    # ---- timed: K frames, CUDA events on the launching stream, L2 flushed between frames
+    # ---- timed: K steps, CUDA events on the launching stream, L2 flushed between steps
     clocks = ClockSampler(local)
     barrier(world)
     torch.cuda.synchronize()
-    ctx.synchronize()
     clocks.start()
     launches0 = ctx.launch_count
-    kernel_ms = []
+    step_ms, kernel_ms = [], []
     for _ in range(args.steps):
-        flush.zero_()
-        torch.cuda.synchronize()
+        with torch.cuda.stream(stream):
+            flush.zero_()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
         frame()
-        kernel_ms.append(ctx.last_kernel_ms)  # waits for the frame's end event
-    ctx.synchronize()
+        e1.record(stream)
+        e1.synchronize()
+        torch.cuda.synchronize()
+        step_ms.append(e0.elapsed_time(e1))
+        kernel_ms.append(ctx.last_kernel_ms if gather is None else float("nan"))
     launches = ctx.launch_count - launches0
     clk = clocks.stop()
     barrier(world)
-    total_ms = max_over_ranks(float(np.sum(kernel_ms)), world)
-    total_pixels = w * h
-    value = total_pixels * args.steps / (total_ms * 1e-3) / 1e6
+    total_ms = max_over_ranks(float(np.sum(step_ms)), world)
+    value = seg_per_frame * args.steps / (total_ms * 1e-3) / 1e6
 
-    # ---- e2e: host buffers -> C ABI -> host image, wall clock, every step
+    # ---- e2e: host buffers -> C ABI -> host image on rank 0, wall clock, every step
     host_img = torch.empty((h, w, 4), dtype=torch.uint8).pin_memory().numpy()
     e2e_ms = []
     barrier(world)
     for i in range(args.warmup + args.steps):
+        torch.cuda.synchronize()
         t0 = time.perf_counter()
         bm.mark_all_dirty()
-        bm.upload_scene(ps)          # H2D of every scene buffer + device re-layout
+        bm.upload_scene(ps)           # H2D of every scene buffer + device re-layout / LBVH build
         frame()
-        ctx.read_composite(host_img)  # D2H of the frame (this rank's tiles)
+        if rank == 0:
+            ctx.read_composite(host_img)  # D2H of the gathered frame
+        else:
+            ctx.synchronize()
+        torch.cuda.synchronize()
         dt = (time.perf_counter() - t0) * 1e3
         if i >= args.warmup:
             e2e_ms.append(dt)
     e2e_total = max_over_ranks(float(np.sum(e2e_ms)), world)
-    e2e_value = total_pixels * args.steps / (e2e_total * 1e-3) / 1e6
+    e2e_value = seg_per_frame * args.steps / (e2e_total * 1e-3) / 1e6
 
     if rank != 0:
         return
-    # ---- roofline of rt_trace_shade: algorithmic bytes per launch / mean launch time
+    # ---- roofline of the trace kernel: algorithmic bytes per launch / mean launch time (rank 0)
     n_lights = len(scene.lights)
     seg = max(cnt["segments"], 1)
     V, T, H = cnt["box_tests"] / seg, cnt["tri_tests"] / seg, cnt["shaded"] / seg
-    out_bytes = 16 + 4  # float4 accumulation store + rgba8 composite store per pixel
-    bytes_per_ray = 48 * V + 56 * T + 20 * len(scene.spheres) + 128 * H + 52 * n_lights * H + out_bytes
+    out_bytes_per_pixel = 16 + 4  # float4 accumulation store + rgba8 composite store
+    bytes_per_ray = (48 * V + 56 * T + 20 * len(scene.spheres) + 128 * H + 52 * n_lights * H
+                     + out_bytes_per_pixel * my_pixels / seg)
     peak, peak_src = measured_peaks()
-    mean_ms = float(np.mean(kernel_ms))
-    achieved = bytes_per_ray * my_pixels / (mean_ms * 1e-3) / 1e9
+    # time the kernel alone once more for the roofline when the step also holds the gather
+    if gather is not None:
+        flush.zero_()
+        torch.cuda.synchronize()
+        render()
+        mean_ms = ctx.last_kernel_ms
+    else:
+        mean_ms = float(np.mean(kernel_ms))
+    achieved = bytes_per_ray * seg_per_frame_rank / (mean_ms * 1e-3) / 1e9
+    kernel = "rt_path_trace" if path else "rt_trace_shade"
+    trav_name = {abi.TRAVERSAL_LITERAL: "literal", abi.TRAVERSAL_ORDERED: "ordered (uploaded tree)",
+                 abi.TRAVERSAL_REBUILT: "rebuilt (internal LBVH, winners certified against the uploaded tree)"}
     line = {
         "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": total_ms / args.steps, "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": wl["desc"], "width": w, "height": h, "triangles": int(len(scene.triangles)),
-                   "bvh_nodes": int(len(scene.bvh_nodes)), "spp": 1, "max_depth": 0,
-                   "traversal": {abi.TRAVERSAL_LITERAL: "literal", abi.TRAVERSAL_ORDERED: "ordered (uploaded tree)",
-                                 abi.TRAVERSAL_REBUILT: "rebuilt (internal LBVH, winners certified against the "
-                                                        "uploaded tree)"}[ctx.last_traversal],
-                   "literal_fallback_rays": cnt["literal_fallbacks"], "upload_relayout_build_ms": ctx.last_build_ms,
-                   "l2": "flushed between timed frames (512 MiB memset)", "tiles_per_rank": my_tiles,
-                   "parallelism": "tile-split x%d, scene replicated" % world},
+                   "bvh_nodes": int(len(scene.bvh_nodes)), "spp": wl["spp"], "max_depth": wl["depth"],
+                   "ray_segments_per_frame": int(seg_per_frame),
+                   "semantics": "extension (SPEC.md; the reference stubs bounces/spp)" if path else "reference",
+                   "traversal": trav_name[ctx.last_traversal], "literal_fallback_rays": cnt["literal_fallbacks"],
+                   "upload_relayout_build_ms": ctx.last_build_ms,
+                   "l2": "flushed between timed steps (512 MiB memset)", "tiles_per_rank": my_tiles,
+                   "parallelism": "128x128 tile split x%d (tile i -> rank i %% N), scene replicated, NCCL gather of "
+                                  "the composite to rank 0 inside the timed step" % world if world > 1 else "single GPU"},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": None, "kernel": "rt_trace_shade", "peak_source": peak_src,
+                     "traffic": None, "kernel": kernel, "peak_source": peak_src,
                      "bytes_per_ray": bytes_per_ray, "box_tests_per_ray": V, "tri_tests_per_ray": T,
                      "kernel_ms": mean_ms,
-                     "note": "algorithmic reference-layout bytes (48 V + 56 T + 128 H + 52 L H + out); the scene "
+                     "note": "algorithmic reference-layout bytes per ray segment (48 V + 56 T + 128 H + 52 L H + "
+                             "output stores), V/T counted by an instrumented launch of the same kernel; the scene "
                              "fits the 126 MB L2, so achieved can exceed the HBM copy peak"},
         "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": h2d_bytes,
                 "d2h_bytes_per_step": int(host_img.nbytes), "ms_per_step": e2e_total / args.steps},

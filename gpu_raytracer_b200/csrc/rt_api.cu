@@ -273,6 +273,26 @@ __global__ void relayout_leaf_counts(const uint2* __restrict__ leaves, const uin
     }
 }
 
+// ---- multi-GPU tile gather helpers ---------------------------------------------
+// pack: this context's tiles (i % stride == phase) -> tile-major compact buffer
+// [local tile][128][128]; unpack: the inverse, into the full frame.  T = uchar4 / float4.
+template <class T, bool PACK>
+__global__ void tile_copy(T* __restrict__ frame, T* __restrict__ compact, uint32_t width, uint32_t height, uint32_t tiles_x,
+                          uint32_t n_tiles_total, uint32_t stride, uint32_t phase) {
+    uint32_t tile_local = blockIdx.y;
+    uint32_t tile = phase + tile_local * stride;
+    if (tile >= n_tiles_total) return;
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; // 0..16383
+    uint32_t x = (tile % tiles_x) * RT_TILE_SIZE + (i & 127u), y = (tile / tiles_x) * RT_TILE_SIZE + (i >> 7);
+    size_t ci = (size_t)tile_local * 16384u + i;
+    if (x < width && y < height) {
+        if (PACK) compact[ci] = frame[(size_t)y * width + x];
+        else frame[(size_t)y * width + x] = compact[ci];
+    } else if (PACK) {
+        T z; memset(&z, 0, sizeof z); compact[ci] = z;
+    }
+}
+
 } // namespace
 
 // =============================================================== C ABI ======
@@ -684,7 +704,7 @@ int launch_path(RtContext* c, const KParams& k, uint32_t traversal) {
     if (k.n_work == 0) return RT_OK;
     int policy = pick_policy(c, k, traversal);
     if (policy < 0) return fail(c, RT_ERR_INVALID_SCENE, "requested traversal unavailable for this scene");
-    const void* fn = policy == 2 ? (const void*)rt_path_trace<2> : policy == 1 ? (const void*)rt_path_trace<1> : (const void*)rt_path_trace<0>;
+    const void* fn = policy == 2 ? (const void*)rt_path_trace<2, false> : policy == 1 ? (const void*)rt_path_trace<1, false> : (const void*)rt_path_trace<0, false>;
     int per_sm = 0, sms = 0;
     CK(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, 256, 0));
     CK(c, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device));
@@ -692,9 +712,15 @@ int launch_path(RtContext* c, const KParams& k, uint32_t traversal) {
     uint32_t need = (k.n_work + 255u) / 256u;
     if (blocks > need) blocks = need;
     CK(c, cudaEventRecord(c->ev0, c->stream));
-    if (policy == 2) rt_path_trace<2><<<blocks, 256, 0, c->stream>>>(k);
-    else if (policy == 1) rt_path_trace<1><<<blocks, 256, 0, c->stream>>>(k);
-    else rt_path_trace<0><<<blocks, 256, 0, c->stream>>>(k);
+    if (k.counters) {
+        if (policy == 2) rt_path_trace<2, true><<<blocks, 256, 0, c->stream>>>(k);
+        else if (policy == 1) rt_path_trace<1, true><<<blocks, 256, 0, c->stream>>>(k);
+        else rt_path_trace<0, true><<<blocks, 256, 0, c->stream>>>(k);
+    } else {
+        if (policy == 2) rt_path_trace<2, false><<<blocks, 256, 0, c->stream>>>(k);
+        else if (policy == 1) rt_path_trace<1, false><<<blocks, 256, 0, c->stream>>>(k);
+        else rt_path_trace<0, false><<<blocks, 256, 0, c->stream>>>(k);
+    }
     CK(c, cudaGetLastError());
     CK(c, cudaEventRecord(c->ev1, c->stream));
     c->timed = true;
@@ -861,7 +887,7 @@ float rt_last_kernel_ms(RtContext* c) {
 int rt_count_next_launch(RtContext* c) {
     if (!c) return RT_ERR_INVALID_ARGUMENT;
     CK(c, cudaSetDevice(c->device));
-    CK(c, cudaMemsetAsync(c->dcounters.ptr, 0, 8 * sizeof(unsigned long long), c->stream));
+    CK(c, cudaMemsetAsync(c->dcounters.ptr, 0, 6 * sizeof(unsigned long long), c->stream));
     c->count_next = true;
     return RT_OK;
 }
@@ -876,6 +902,36 @@ int rt_read_counters(RtContext* c, uint64_t out[5]) {
 }
 uint64_t rt_launch_count(const RtContext* c) { return c ? c->launches : 0; }
 int rt_last_traversal(const RtContext* c) { return c ? c->last_traversal : 0; }
+void* rt_stream(RtContext* c) { return c ? (void*)c->stream : nullptr; }
+
+// what: 0 = composite rgba8 (4 B/px), 1 = accumulation float4 (16 B/px)
+static int tile_copy_launch(RtContext* c, uint32_t what, uint32_t stride, uint32_t phase, void* compact, bool pack) {
+    if (!c || !compact) return RT_ERR_INVALID_ARGUMENT;
+    if (c->width == 0) return fail(c, RT_ERR_NOT_READY, "rt_resize has not been called");
+    if (stride == 0 || phase >= stride || what > 1) return fail(c, RT_ERR_INVALID_ARGUMENT, "tile copy: bad stride/phase/what");
+    CK(c, cudaSetDevice(c->device));
+    uint32_t total = c->tiles_x * c->tiles_y;
+    uint32_t mine = total > phase ? (total - phase + stride - 1) / stride : 0;
+    if (!mine) return RT_OK;
+    dim3 grid(16384 / 256, mine);
+    if (what == 0) {
+        if (pack) tile_copy<uchar4, true><<<grid, 256, 0, c->stream>>>(c->composite.ptr, (uchar4*)compact, c->width, c->height, c->tiles_x, total, stride, phase);
+        else tile_copy<uchar4, false><<<grid, 256, 0, c->stream>>>(c->composite.ptr, (uchar4*)compact, c->width, c->height, c->tiles_x, total, stride, phase);
+    } else {
+        if (pack) tile_copy<float4, true><<<grid, 256, 0, c->stream>>>(c->accum.ptr, (float4*)compact, c->width, c->height, c->tiles_x, total, stride, phase);
+        else tile_copy<float4, false><<<grid, 256, 0, c->stream>>>(c->accum.ptr, (float4*)compact, c->width, c->height, c->tiles_x, total, stride, phase);
+    }
+    CK(c, cudaGetLastError());
+    c->launches++;
+    return RT_OK;
+}
+int rt_pack_tiles(RtContext* c, uint32_t what, uint32_t stride, uint32_t phase, void* dst_device) {
+    return tile_copy_launch(c, what, stride, phase, dst_device, true);
+}
+int rt_unpack_tiles(RtContext* c, uint32_t what, uint32_t stride, uint32_t phase, const void* src_device) {
+    return tile_copy_launch(c, what, stride, phase, const_cast<void*>(src_device), false);
+}
+
 // ray segments traced by the last RT_MODE_PATH launch (waits for it)
 int rt_last_segments(RtContext* c, uint64_t* out) {
     if (!c || !out) return RT_ERR_INVALID_ARGUMENT;

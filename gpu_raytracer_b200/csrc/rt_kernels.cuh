@@ -645,9 +645,10 @@ __device__ __forceinline__ bool work_to_pixel(const KParams& p, uint32_t idx, ui
     return *px < p.width && *py < p.height;
 }
 
-template <int POLICY>
+template <int POLICY, bool COUNT>
 __global__ void __launch_bounds__(256) rt_path_trace(const __grid_constant__ KParams p) {
     const uint32_t lane = threadIdx.x & 31u;
+    unsigned long long c_box = 0, c_tri = 0, c_shaded = 0, c_fb = 0;
     const unsigned full = 0xFFFFFFFFu;
     bool have = false, exhausted = false, new_sample = false;
     uint32_t px = 0, py = 0, s = 0, depth = 0, n_seg = 0;
@@ -690,6 +691,7 @@ __global__ void __launch_bounds__(256) rt_path_trace(const __grid_constant__ KPa
         }
         Hit h = find_closest<POLICY>(p, ray); // step 3.1
         n_seg++;
+        if (COUNT) { c_box += h.n_box; c_tri += h.n_tri; c_shaded += (h.kind != 0u); c_fb += h.n_fallback; }
         if (depth == 0u && s == 0u && (p.outputs & RT_OUT_HITS))
             reinterpret_cast<uint4*>(p.hits)[(size_t)py * p.width + px] =
                 make_uint4(h.kind, h.prim, __float_as_uint(h.t), h.material_id);
@@ -759,4 +761,15 @@ __global__ void __launch_bounds__(256) rt_path_trace(const __grid_constant__ KPa
     // one atomic per warp for the segment count
     for (int o = 16; o; o >>= 1) n_seg += __shfl_xor_sync(full, n_seg, o);
     if (lane == 0u && n_seg) atomicAdd(p.seg_counter, (unsigned long long)n_seg);
+    if (COUNT) {
+        for (int o = 16; o; o >>= 1) {
+            c_box += __shfl_xor_sync(full, c_box, o); c_tri += __shfl_xor_sync(full, c_tri, o);
+            c_shaded += __shfl_xor_sync(full, c_shaded, o); c_fb += __shfl_xor_sync(full, c_fb, o);
+        }
+        if (lane == 0u) {
+            atomicAdd(p.counters + 0, c_box); atomicAdd(p.counters + 1, c_tri);
+            atomicAdd(p.counters + 2, (unsigned long long)n_seg); atomicAdd(p.counters + 3, c_shaded);
+            atomicAdd(p.counters + 4, c_fb);
+        }
+    }
 }

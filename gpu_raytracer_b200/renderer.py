@@ -83,6 +83,16 @@ class Context:
         self._ck(self.lib.rt_read_hit_records(self.handle, _p(out)))
         return out
 
+    @property
+    def stream(self):
+        return int(self.lib.rt_stream(self.handle) or 0)
+
+    def pack_tiles(self, what, stride, phase, dst_device_ptr):
+        self._ck(self.lib.rt_pack_tiles(self.handle, what, stride, phase, C.c_void_p(dst_device_ptr)))
+
+    def unpack_tiles(self, what, stride, phase, src_device_ptr):
+        self._ck(self.lib.rt_unpack_tiles(self.handle, what, stride, phase, C.c_void_p(src_device_ptr)))
+
     def count_next_launch(self):
         self._ck(self.lib.rt_count_next_launch(self.handle))
 

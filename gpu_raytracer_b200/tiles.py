@@ -1,0 +1,83 @@
+"""Screen-space tile split across the GPUs of one box and the gather of the tiles
+to rank 0 (one process per GPU; torch.distributed is the plumbing).
+
+The reference is single-GPU but already iterates independent 128x128 tiles
+(src/compute.rs:157-162, 194-209); rank r of N renders the tiles i with
+i % N == r (RtFrameParams.tile_stride / tile_phase), the scene is replicated, and
+nothing is exchanged while tracing.  The only collective is the final gather of
+the finished tiles to rank 0: every rank packs its tiles into a tile-major compact
+buffer (CUDA kernel rt_pack_tiles), `dist.gather` moves the equal-sized buffers over
+NCCL/NVLink, rank 0 un-tiles them (rt_unpack_tiles).
+"""
+import numpy as np
+
+from . import abi
+
+TILE = abi.TILE_SIZE
+WHAT_COMPOSITE, WHAT_ACCUM = 0, 1
+BYTES_PER_PIXEL = {WHAT_COMPOSITE: 4, WHAT_ACCUM: 16}
+
+
+def tile_grid(width, height):
+    """TileHelper::calculate_tile_count (shared/src/lib.rs:1187-1191)."""
+    return (width + TILE - 1) // TILE, (height + TILE - 1) // TILE
+
+
+def tiles_of_rank(width, height, world, rank):
+    tx, ty = tile_grid(width, height)
+    return list(range(rank, tx * ty, world))
+
+
+def tiles_per_rank_padded(width, height, world):
+    tx, ty = tile_grid(width, height)
+    return (tx * ty + world - 1) // world
+
+
+def tile_rect(width, height, tile):
+    """calculate_tile_dimensions (src/compute.rs:194-209)."""
+    tx, _ = tile_grid(width, height)
+    ox, oy = (tile % tx) * TILE, (tile // tx) * TILE
+    return ox, oy, min(TILE, width - ox), min(TILE, height - oy)
+
+
+def pixels_of_rank(width, height, world, rank):
+    return sum(tile_rect(width, height, t)[2] * tile_rect(width, height, t)[3]
+               for t in tiles_of_rank(width, height, world, rank))
+
+
+def pack_tiles_host(frame, world, rank):
+    """numpy statement of rt_pack_tiles (used by the CPU/gloo tests of the gather logic)."""
+    h, w = frame.shape[:2]
+    out = np.zeros((tiles_per_rank_padded(w, h, world), TILE, TILE) + frame.shape[2:], frame.dtype)
+    for k, t in enumerate(tiles_of_rank(w, h, world, rank)):
+        ox, oy, tw, th = tile_rect(w, h, t)
+        out[k, :th, :tw] = frame[oy:oy + th, ox:ox + tw]
+    return out
+
+
+def unpack_tiles_host(frame, compact, world, rank):
+    h, w = frame.shape[:2]
+    for k, t in enumerate(tiles_of_rank(w, h, world, rank)):
+        ox, oy, tw, th = tile_rect(w, h, t)
+        frame[oy:oy + th, ox:ox + tw] = compact[k, :th, :tw]
+
+
+class TileGather:
+    """Gathers every rank's tiles to rank 0.  `pack(dst_tensor)` and
+    `unpack(src_tensor, src_rank)` are the device (or, in CPU tests, numpy) copies."""
+
+    def __init__(self, dist, torch, width, height, what, device):
+        self.dist, self.torch = dist, torch
+        self.world, self.rank = dist.get_world_size(), dist.get_rank()
+        self.width, self.height, self.what = width, height, what
+        n = tiles_per_rank_padded(width, height, self.world) * TILE * TILE * BYTES_PER_PIXEL[what]
+        self.bytes_per_rank = n
+        self.send = torch.zeros(n, dtype=torch.uint8, device=device)
+        self.recv = [torch.zeros(n, dtype=torch.uint8, device=device) for _ in range(self.world)] if self.rank == 0 else None
+
+    def run(self, pack, unpack):
+        pack(self.send)
+        self.dist.gather(self.send, self.recv, dst=0)
+        if self.rank == 0:
+            for r in range(1, self.world):  # rank 0's own tiles are already in its frame
+                unpack(self.recv[r], r)

@@ -149,6 +149,16 @@ int rt_read_counters(RtContext* ctx, uint64_t out[5]);
 uint64_t rt_launch_count(const RtContext* ctx);
 /* which traversal the last launch used (RT_TRAVERSAL_LITERAL / _ORDERED / _REBUILT) */
 int rt_last_traversal(const RtContext* ctx);
+/* ---- multi-GPU tile split (no reference analogue: the reference is single-GPU;
+ * it iterates the same independent 128x128 tiles, src/compute.rs:157-162, 194-209).
+ * Each context renders the tiles i % stride == phase (RtFrameParams); pack copies
+ * them into a tile-major compact device buffer [local tile][128][128] for a
+ * collective, unpack scatters such a buffer back into the full frame (rank 0).
+ * what: 0 = composite rgba8, 1 = accumulation float4.  Asynchronous on rt_stream(). */
+int rt_pack_tiles(RtContext* ctx, uint32_t what, uint32_t stride, uint32_t phase, void* dst_device);
+int rt_unpack_tiles(RtContext* ctx, uint32_t what, uint32_t stride, uint32_t phase, const void* src_device);
+/* the context's cudaStream_t, so callers can order their own work (NCCL) after it */
+void* rt_stream(RtContext* ctx);
 /* EXTENSION: ray segments traced by the last RT_MODE_PATH launch (SPEC.md) */
 int rt_last_segments(RtContext* ctx, uint64_t* out);
 /* GPU time of the last upload-time re-layout + LBVH build, ms (<0 if none) */
