@@ -232,3 +232,37 @@ def test_c3_path_terrain_1m(c3_scene_and_ref, traversal):
     gpu = render_gpu_path(s, w, h, 2, 4, base_seed=1, traversal=traversal)
     assert gpu["traversal"] == traversal
     compare_path(gpu, ref)
+
+
+# ---- multi-GPU tile split: N-rank output must be bit-identical to the 1-GPU output ----
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_tile_split_pack_unpack_bit_identical(world):
+    """Emulates N ranks on one GPU: each 'rank' context renders its tiles (i % N == r), packs
+    them (rt_pack_tiles); the 'rank 0' context unpacks every buffer (rt_unpack_tiles).  The
+    assembled frame must equal the single-context frame bit for bit."""
+    import torch
+    from gpu_raytracer_b200 import tiles
+    s = g.default_scene()
+    w, h = 1000, 600  # ragged edge tiles
+    kw = dict(mode=abi.MODE_PATH, spp=3, max_depth=3, base_seed=4, outputs=abi.OUT_ACCUM | abi.OUT_COMPOSITE)
+    one = g.Context(0, w, h)
+    g.BufferManager(one).upload_scene(s)
+    g.ComputeRenderer(one).render_frame(s.camera, **kw)
+    want_c, want_a = one.read_composite(), one.read_accum()
+    root = g.Context(0, w, h)  # plays rank 0's frame buffers
+    n_pad = tiles.tiles_per_rank_padded(w, h, world)
+    for r in range(world):
+        ctx = g.Context(0, w, h)
+        g.BufferManager(ctx).upload_scene(s)
+        g.ComputeRenderer(ctx).render_frame(s.camera, tile_stride=world, tile_phase=r, **kw)
+        for what, bpp in ((tiles.WHAT_COMPOSITE, 4), (tiles.WHAT_ACCUM, 16)):
+            buf = torch.zeros(n_pad * 128 * 128 * bpp, dtype=torch.uint8, device="cuda")
+            ctx.pack_tiles(what, world, r, buf.data_ptr())
+            ctx.synchronize()
+            root.unpack_tiles(what, world, r, buf.data_ptr())
+            root.synchronize()
+        ctx.close()
+    assert np.array_equal(root.read_composite(), want_c)
+    assert np.array_equal(root.read_accum().view(np.uint32), want_a.view(np.uint32))
+    one.close()
+    root.close()
