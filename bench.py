@@ -57,6 +57,7 @@ def parse_args():
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU work for the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--variant", type=int, default=0, help="path mode: 1 = first-generation kernel (A/B)")
     ap.add_argument("--traversal", default="auto", choices=["auto", "literal", "ordered", "rebuilt"])
     return ap.parse_args()
 
@@ -271,7 +272,7 @@ def run_b200(args, wl, world, rank, local):
     def render():
         if path:
             cr.render_frame(ps.camera, mode=abi.MODE_PATH, spp=wl["spp"], max_depth=wl["depth"], base_seed=1,
-                            outputs=outputs, tile_stride=stride, tile_phase=phase, traversal=trav)
+                            outputs=outputs, tile_stride=stride, tile_phase=phase, traversal=trav, variant=args.variant)
         else:
             cr.render_frame(ps.camera, outputs=outputs, tile_stride=stride, tile_phase=phase, traversal=trav)
 

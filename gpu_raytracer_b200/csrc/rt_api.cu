@@ -15,6 +15,7 @@
 
 #include "rt_kernels.cuh"
 #include "rt_lbvh.cuh"
+#include "rt_path_kernel.cuh"
 
 namespace {
 
@@ -321,7 +322,7 @@ int rt_create(int device, RtContext** out) {
                                        1024 * sizeof(uint32_t) + 1024 * sizeof(RtVertex);
     if (c->meta.reserve(c->scene_metadata_capacity_bytes / 4) < 0 || c->mats.reserve(c->mats_capacity) < 0 ||
         c->textures.reserve(c->textures_capacity) < 0 || c->texdata.reserve(c->texdata_capacity) < 0 ||
-        c->tris.reserve(64) < 0 || c->dflag.reserve(1) < 0 || c->dcounters.reserve(8) < 0) {
+        c->tris.reserve(64) < 0 || c->dflag.reserve(1) < 0 || c->dcounters.reserve(16) < 0) {
         fail(nullptr, RT_ERR_CUDA, "rt_create: cudaMalloc failed");
         delete c;
         return RT_ERR_CUDA;
@@ -547,7 +548,7 @@ int build_rebuilt(RtContext* c, uint32_t n) {
         c->bnodes.reserve((size_t)n * 4) < 0 || c->btris.reserve((size_t)n * 3) < 0)
         return fail(c, RT_ERR_CUDA, "LBVH cudaMalloc failed for %u triangles", n);
     const uint32_t g = (n + 255) / 256;
-    const unsigned int init_bounds[6] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0u, 0u, 0u};
+    const unsigned int init_bounds[8] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0u, 0u, 0u, 0u, 0u}; // [6] = tree depth
     CK(c, cudaMemcpyAsync(c->lb_bounds.ptr, init_bounds, sizeof init_bounds, cudaMemcpyHostToDevice, c->stream));
     CK(c, cudaStreamSynchronize(c->stream)); // init_bounds is a stack array
     lbvh::centroid_bounds<<<g, 256, 0, c->stream>>>(c->pbox.ptr, n, c->lb_bounds.ptr);
@@ -564,12 +565,15 @@ int build_rebuilt(RtContext* c, uint32_t n) {
                                                   c->lb_parent_i.ptr, c->lb_parent_l.ptr, c->lb_nbox.ptr, c->lb_visits.ptr);
         lbvh::emit_wide<<<g, 256, 0, c->stream>>>(c->pbox.ptr, c->lb_vals_sorted.ptr, n, c->lb_children.ptr, c->lb_range.ptr,
                                                   c->lb_nbox.ptr, c->bnodes.ptr);
-        c->launches += 3;
+        lbvh::tree_depth<<<g, 256, 0, c->stream>>>(c->lb_parent_i.ptr, c->lb_parent_l.ptr, n, c->lb_bounds.ptr + 6);
+        c->launches += 4;
     }
     lbvh::gather_sorted<<<g, 256, 0, c->stream>>>(c->wtris.ptr, c->lb_vals_sorted.ptr, n, c->leaf_of_pos.ptr, c->btris.ptr);
     c->launches++;
     // root: the whole tree collapses into one leaf when n <= RT_LBVH_LEAF
     float4 rb[2];
+    unsigned int tree_depth = 0;
+    CK(c, cudaMemcpyAsync(&tree_depth, c->lb_bounds.ptr + 6, 4, cudaMemcpyDeviceToHost, c->stream));
     if (n >= 2) CK(c, cudaMemcpyAsync(rb, c->lb_nbox.ptr, sizeof rb, cudaMemcpyDeviceToHost, c->stream));
     else CK(c, cudaMemcpyAsync(rb, c->pbox.ptr, sizeof rb, cudaMemcpyDeviceToHost, c->stream));
     CK(c, cudaStreamSynchronize(c->stream));
@@ -580,7 +584,7 @@ int build_rebuilt(RtContext* c, uint32_t n) {
     float pad = m * 1.52587890625e-05f + 1e-30f; // same inflation as lbvh::inflate
     for (int k = 0; k < 3; k++) { c->broot_min[k] = v[k] - pad; c->broot_max[k] = v[3 + k] + pad; }
     c->broot_ref = n <= RT_LBVH_LEAF ? (RT_LEAF_FLAG | ((n - 1u) << 28)) : 0u;
-    c->rebuilt_ok = true;
+    c->rebuilt_ok = tree_depth < 60; // the traversal stacks hold 64 entries (many coincident centroids can deepen the tree)
     return RT_OK;
 }
 
@@ -700,11 +704,13 @@ int pick_policy(RtContext* c, const KParams& k, uint32_t traversal) {
 }
 
 // EXTENSION path tracing: persistent grid, one resident wave of 256-thread blocks
-int launch_path(RtContext* c, const KParams& k, uint32_t traversal) {
+int launch_path(RtContext* c, const KParams& k, uint32_t traversal, uint32_t variant) {
     if (k.n_work == 0) return RT_OK;
     int policy = pick_policy(c, k, traversal);
     if (policy < 0) return fail(c, RT_ERR_INVALID_SCENE, "requested traversal unavailable for this scene");
-    const void* fn = policy == 2 ? (const void*)rt_path_trace<2, false> : policy == 1 ? (const void*)rt_path_trace<1, false> : (const void*)rt_path_trace<0, false>;
+    const bool v2 = policy >= 1 && variant != 1; // variant 1 forces the first-generation kernel (A/B comparison)
+    const void* fn = v2 ? (policy == 2 ? (const void*)rt_path_trace_v2<2, false> : (const void*)rt_path_trace_v2<1, false>)
+                        : policy == 2 ? (const void*)rt_path_trace<2, false> : policy == 1 ? (const void*)rt_path_trace<1, false> : (const void*)rt_path_trace<0, false>;
     int per_sm = 0, sms = 0;
     CK(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, 256, 0));
     CK(c, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device));
@@ -712,7 +718,15 @@ int launch_path(RtContext* c, const KParams& k, uint32_t traversal) {
     uint32_t need = (k.n_work + 255u) / 256u;
     if (blocks > need) blocks = need;
     CK(c, cudaEventRecord(c->ev0, c->stream));
-    if (k.counters) {
+    if (v2) {
+        if (k.counters) {
+            if (policy == 2) rt_path_trace_v2<2, true><<<blocks, 256, 0, c->stream>>>(k);
+            else rt_path_trace_v2<1, true><<<blocks, 256, 0, c->stream>>>(k);
+        } else {
+            if (policy == 2) rt_path_trace_v2<2, false><<<blocks, 256, 0, c->stream>>>(k);
+            else rt_path_trace_v2<1, false><<<blocks, 256, 0, c->stream>>>(k);
+        }
+    } else if (k.counters) {
         if (policy == 2) rt_path_trace<2, true><<<blocks, 256, 0, c->stream>>>(k);
         else if (policy == 1) rt_path_trace<1, true><<<blocks, 256, 0, c->stream>>>(k);
         else rt_path_trace<0, true><<<blocks, 256, 0, c->stream>>>(k);
@@ -805,7 +819,7 @@ int rt_render_frame(RtContext* c, const RtCamera* cam, const RtFrameParams* fp) 
         k.seg_counter = c->dcounters.ptr + 6;
         k.work_counter = reinterpret_cast<unsigned int*>(c->dcounters.ptr + 7);
         CK(c, cudaMemsetAsync(c->dcounters.ptr + 6, 0, 2 * sizeof(unsigned long long), c->stream));
-        return launch_path(c, k, fp->traversal);
+        return launch_path(c, k, fp->traversal, fp->_reserved[0]);
     }
     return launch(c, k, my_tiles * 64u, fp->traversal);
 }
@@ -888,16 +902,18 @@ int rt_count_next_launch(RtContext* c) {
     if (!c) return RT_ERR_INVALID_ARGUMENT;
     CK(c, cudaSetDevice(c->device));
     CK(c, cudaMemsetAsync(c->dcounters.ptr, 0, 6 * sizeof(unsigned long long), c->stream));
+    CK(c, cudaMemsetAsync(c->dcounters.ptr + 8, 0, 8 * sizeof(unsigned long long), c->stream));
     c->count_next = true;
     return RT_OK;
 }
-int rt_read_counters(RtContext* c, uint64_t out[5]) {
+int rt_read_counters(RtContext* c, uint64_t out[9]) {
     if (!c || !out) return RT_ERR_INVALID_ARGUMENT;
     CK(c, cudaSetDevice(c->device));
-    unsigned long long h[5];
+    unsigned long long h[12];
     CK(c, cudaMemcpyAsync(h, c->dcounters.ptr, sizeof h, cudaMemcpyDeviceToHost, c->stream));
     CK(c, cudaStreamSynchronize(c->stream));
     for (int i = 0; i < 5; i++) out[i] = h[i];
+    for (int i = 0; i < 4; i++) out[5 + i] = h[8 + i]; // path kernel: S phases, ready lanes, T iterations, traversing lanes
     return RT_OK;
 }
 uint64_t rt_launch_count(const RtContext* c) { return c ? c->launches : 0; }

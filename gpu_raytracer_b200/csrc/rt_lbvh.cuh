@@ -140,6 +140,19 @@ __global__ void fit_boxes(const float4* __restrict__ pbox, const uint32_t* __res
     }
 }
 
+// depth of the radix tree (stack bound of the traversal): every leaf walks to the root
+__global__ void tree_depth(const uint32_t* __restrict__ parent_internal, const uint32_t* __restrict__ parent_leaf, uint32_t n,
+                           unsigned int* __restrict__ out_max) {
+    uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned int d = 0;
+    if (k < n && n >= 2) {
+        uint32_t node = parent_leaf[k];
+        while (node != 0xFFFFFFFFu) { d++; node = parent_internal[node]; }
+    }
+    for (int o = 16; o; o >>= 1) d = max(d, __shfl_xor_sync(0xFFFFFFFFu, d, o));
+    if ((threadIdx.x & 31u) == 0 && d) atomicMax(out_max, d);
+}
+
 __device__ __forceinline__ void inflate(float4& lo, float4& hi) {
     // conservative boxes: a Möller–Trumbore hit implies the true ray passes within a few
     // ulps (relative to coordinate magnitude) of the triangle; 2^-16 relative is ~100x that

@@ -97,10 +97,11 @@ class Context:
         self._ck(self.lib.rt_count_next_launch(self.handle))
 
     def read_counters(self):
-        out = np.zeros(5, np.uint64)
+        out = np.zeros(9, np.uint64)
         self._ck(self.lib.rt_read_counters(self.handle, _p(out)))
         return dict(box_tests=int(out[0]), tri_tests=int(out[1]), segments=int(out[2]), shaded=int(out[3]),
-                    literal_fallbacks=int(out[4]))
+                    literal_fallbacks=int(out[4]), s_phases=int(out[5]), s_ready_lanes=int(out[6]),
+                    t_iterations=int(out[7]), t_active_lanes=int(out[8]))
 
     @property
     def last_kernel_ms(self):
@@ -208,11 +209,12 @@ class ComputeRenderer:
 
     def render_frame(self, camera, mode=abi.MODE_LEGACY, outputs=abi.OUT_ACCUM | abi.OUT_COMPOSITE, spp=1,
                      first_sample=0, max_depth=0, base_seed=1, reset_accum=True, tile_stride=0, tile_phase=0,
-                     traversal=abi.TRAVERSAL_AUTO):
+                     traversal=abi.TRAVERSAL_AUTO, variant=0):
         cam = np.ascontiguousarray(camera, abi.Camera)
         fp = np.zeros((), abi.FrameParams)
         fp["mode"], fp["outputs"], fp["spp"], fp["first_sample"] = mode, outputs, spp, first_sample
         fp["max_depth"], fp["base_seed"], fp["reset_accum"] = max_depth, base_seed, int(reset_accum)
         fp["tile_stride"], fp["tile_phase"], fp["traversal"] = tile_stride, tile_phase, traversal
+        fp["_reserved"][0] = variant  # path mode: 1 = first-generation kernel (A/B comparison)
         self.ctx._ck(self.ctx.lib.rt_render_frame(self.ctx.handle, cam.ctypes.data_as(C.c_void_p),
                                                   fp.ctypes.data_as(C.c_void_p)))

@@ -142,9 +142,10 @@ void* rt_device_composite(RtContext* ctx);
 float rt_last_kernel_ms(RtContext* ctx);
 /* Instrumentation (not for timing): make the next launch count [0] box tests,
  * [1] triangle tests, [2] ray segments, [3] shaded hits, [4] rays whose REBUILT winner
- * failed certification and re-ran the literal policy; read them back. */
+ * failed certification and re-ran the literal policy, [5..8] path kernel: shading phases,
+ * lanes served by them, traversal iterations, lanes active in them (warp-level); read them back. */
 int rt_count_next_launch(RtContext* ctx);
-int rt_read_counters(RtContext* ctx, uint64_t out[5]);
+int rt_read_counters(RtContext* ctx, uint64_t out[9]);
 /* number of kernels this library has launched on ctx since creation */
 uint64_t rt_launch_count(const RtContext* ctx);
 /* which traversal the last launch used (RT_TRAVERSAL_LITERAL / _ORDERED / _REBUILT) */

@@ -172,14 +172,14 @@ def test_random_soup_all_policies():
 
 
 # ---- EXTENSION (SPEC.md): path tracing, bit-exact vs the extension oracle ------
-def render_gpu_path(scene, w, h, spp, max_depth, base_seed=1, traversal=abi.TRAVERSAL_AUTO, chunks=None):
+def render_gpu_path(scene, w, h, spp, max_depth, base_seed=1, traversal=abi.TRAVERSAL_AUTO, chunks=None, variant=0):
     ctx = g.Context(0, w, h)
     g.BufferManager(ctx).upload_scene(scene)
     cr = g.ComputeRenderer(ctx)
     segs, first = 0, 0
     for n in (chunks or [spp]):
         cr.render_frame(scene.camera, mode=abi.MODE_PATH, spp=n, first_sample=first, max_depth=max_depth,
-                        base_seed=base_seed, reset_accum=(first == 0), traversal=traversal,
+                        base_seed=base_seed, reset_accum=(first == 0), traversal=traversal, variant=variant,
                         outputs=abi.OUT_ACCUM | abi.OUT_HITS | abi.OUT_COMPOSITE)
         segs += ctx.last_segments
         first += n
@@ -223,13 +223,14 @@ def test_path_default_scene_glass_metal_and_resume(default_ref):
     compare_path(gpu, ref)
 
 
+@pytest.mark.parametrize("variant", [0, 1])
 @pytest.mark.parametrize("traversal", [abi.TRAVERSAL_ORDERED, abi.TRAVERSAL_REBUILT])
-def test_c3_path_terrain_1m(c3_scene_and_ref, traversal):
+def test_c3_path_terrain_1m(c3_scene_and_ref, traversal, variant):
     """C3 semantics (4 bounces) on the 1M-triangle terrain at reduced size/spp so the oracle finishes."""
     s, _ = c3_scene_and_ref
     w, h = 240, 136
     ref = ob.render_path(s, w, h, spp=2, max_depth=4, base_seed=1, policy=1)
-    gpu = render_gpu_path(s, w, h, 2, 4, base_seed=1, traversal=traversal)
+    gpu = render_gpu_path(s, w, h, 2, 4, base_seed=1, traversal=traversal, variant=variant)
     assert gpu["traversal"] == traversal
     compare_path(gpu, ref)
 
