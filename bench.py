@@ -57,7 +57,7 @@ def parse_args():
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU work for the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--variant", type=int, default=0, help="path mode: 1 = first-generation kernel (A/B)")
+    ap.add_argument("--variant", type=int, default=0, help="path mode engine: 0 megakernel (default), 2 wavefront, 3 state-machine megakernel")
     ap.add_argument("--traversal", default="auto", choices=["auto", "literal", "ordered", "rebuilt"])
     return ap.parse_args()
 

@@ -16,6 +16,7 @@
 #include "rt_kernels.cuh"
 #include "rt_lbvh.cuh"
 #include "rt_path_kernel.cuh"
+#include "rt_wavefront.cuh"
 
 namespace {
 
@@ -101,6 +102,12 @@ struct RtContext {
     uint32_t broot_ref = RT_CHILD_ABSENT;
     float broot_min[3] = {0, 0, 0}, broot_max[3] = {0, 0, 0};
     float last_build_ms = -1.0f;
+    // wavefront path tracing (rt_wavefront.cuh)
+    DevBuf<float4> wf_state;
+    DevBuf<uint4> wf_hit;
+    DevBuf<uint32_t> wf_queue[2];
+    DevBuf<WfCtrl> wf_ctrl;
+    bool last_was_wavefront = false;
 
     // outputs (src/renderer.rs:452-475) + progressive state (src/renderer.rs:821-855)
     uint32_t width = 0, height = 0;
@@ -708,7 +715,7 @@ int launch_path(RtContext* c, const KParams& k, uint32_t traversal, uint32_t var
     if (k.n_work == 0) return RT_OK;
     int policy = pick_policy(c, k, traversal);
     if (policy < 0) return fail(c, RT_ERR_INVALID_SCENE, "requested traversal unavailable for this scene");
-    const bool v2 = policy >= 1 && variant != 1; // variant 1 forces the first-generation kernel (A/B comparison)
+    const bool v2 = policy >= 1 && variant == 3;
     const void* fn = v2 ? (policy == 2 ? (const void*)rt_path_trace_v2<2, false> : (const void*)rt_path_trace_v2<1, false>)
                         : policy == 2 ? (const void*)rt_path_trace<2, false> : policy == 1 ? (const void*)rt_path_trace<1, false> : (const void*)rt_path_trace<0, false>;
     int per_sm = 0, sms = 0;
@@ -741,6 +748,60 @@ int launch_path(RtContext* c, const KParams& k, uint32_t traversal, uint32_t var
     c->launches++;
     c->last_traversal = policy == 2 ? RT_TRAVERSAL_REBUILT : (policy == 1 ? RT_TRAVERSAL_ORDERED : RT_TRAVERSAL_LITERAL);
     c->count_next = false;
+    return RT_OK;
+}
+
+// EXTENSION path tracing as a wavefront: per sample one generate, per depth one extend +
+// one shade launch; queue lengths stay on the device (no host sync inside the frame).
+int launch_wavefront(RtContext* c, KParams k, uint32_t traversal) {
+    if (k.n_work == 0) return RT_OK;
+    int policy = pick_policy(c, k, traversal);
+    if (policy < 1) return -100; // not available for the literal policy: caller falls back to the megakernel
+    size_t P = k.n_work;
+    if (c->wf_state.reserve(P * 4) < 0 || c->wf_hit.reserve(P) < 0 || c->wf_queue[0].reserve(P) < 0 ||
+        c->wf_queue[1].reserve(P) < 0 || c->wf_ctrl.reserve(1) < 0)
+        return fail(c, RT_ERR_CUDA, "wavefront cudaMalloc failed for %zu paths", P);
+    WfBuffers w;
+    w.state = c->wf_state.ptr; w.hit = c->wf_hit.ptr; w.queue[0] = c->wf_queue[0].ptr; w.queue[1] = c->wf_queue[1].ptr;
+    w.ctrl = c->wf_ctrl.ptr;
+    k.wf_rebuilt = policy == 2 ? 1u : 0u;
+    const bool count = k.counters != nullptr;
+    int per_sm = 0, sms = 0;
+    const void* fn = policy == 2 ? (const void*)wf_extend<2, false> : (const void*)wf_extend<1, false>;
+    CK(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, 256, 0));
+    CK(c, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device));
+    uint32_t ext_blocks = (uint32_t)(per_sm > 0 ? per_sm : 1) * (uint32_t)sms;
+    uint32_t full_blocks = (uint32_t)((P + 255) / 256);
+    if (ext_blocks > full_blocks) ext_blocks = full_blocks;
+    CK(c, cudaEventRecord(c->ev0, c->stream));
+    CK(c, cudaMemsetAsync(c->wf_ctrl.ptr, 0, sizeof(WfCtrl), c->stream));
+    for (uint32_t s = k.first_sample; s < k.first_sample + k.spp; s++) {
+        if (s != k.first_sample) CK(c, cudaMemsetAsync(c->wf_ctrl.ptr, 0, 16, c->stream)); // n[0], n[1], head
+        wf_generate<<<full_blocks, 256, 0, c->stream>>>(k, w, s);
+        for (uint32_t d = 0; d <= k.path_max_depth; d++) {
+            int qi = (int)(d & 1u);
+            if (policy == 2) { if (count) wf_extend<2, true><<<ext_blocks, 256, 0, c->stream>>>(k, w, qi); else wf_extend<2, false><<<ext_blocks, 256, 0, c->stream>>>(k, w, qi); }
+            else { if (count) wf_extend<1, true><<<ext_blocks, 256, 0, c->stream>>>(k, w, qi); else wf_extend<1, false><<<ext_blocks, 256, 0, c->stream>>>(k, w, qi); }
+            if (count) wf_shade<true><<<full_blocks, 256, 0, c->stream>>>(k, w, qi, s);
+            else wf_shade<false><<<full_blocks, 256, 0, c->stream>>>(k, w, qi, s);
+            c->launches += 2;
+        }
+        c->launches++;
+    }
+    CK(c, cudaGetLastError());
+    // publish the segment count (and instrumentation) where rt_last_segments / rt_read_counters look
+    CK(c, cudaMemcpyAsync(c->dcounters.ptr + 6, &c->wf_ctrl.ptr->segments, 8, cudaMemcpyDeviceToDevice, c->stream));
+    if (count) {
+        CK(c, cudaMemcpyAsync(c->dcounters.ptr + 0, &c->wf_ctrl.ptr->c[0], 16, cudaMemcpyDeviceToDevice, c->stream)); // box, tri
+        CK(c, cudaMemcpyAsync(c->dcounters.ptr + 2, &c->wf_ctrl.ptr->segments, 8, cudaMemcpyDeviceToDevice, c->stream));
+        CK(c, cudaMemcpyAsync(c->dcounters.ptr + 3, &c->wf_ctrl.ptr->c[2], 16, cudaMemcpyDeviceToDevice, c->stream)); // shaded, fallbacks
+        CK(c, cudaMemcpyAsync(c->dcounters.ptr + 8, &c->wf_ctrl.ptr->c[4], 8, cudaMemcpyDeviceToDevice, c->stream));  // refills
+    }
+    CK(c, cudaEventRecord(c->ev1, c->stream));
+    c->timed = true;
+    c->last_traversal = policy == 2 ? RT_TRAVERSAL_REBUILT : RT_TRAVERSAL_ORDERED;
+    c->count_next = false;
+    c->last_was_wavefront = true;
     return RT_OK;
 }
 
@@ -819,6 +880,13 @@ int rt_render_frame(RtContext* c, const RtCamera* cam, const RtFrameParams* fp) 
         k.seg_counter = c->dcounters.ptr + 6;
         k.work_counter = reinterpret_cast<unsigned int*>(c->dcounters.ptr + 7);
         CK(c, cudaMemsetAsync(c->dcounters.ptr + 6, 0, 2 * sizeof(unsigned long long), c->stream));
+        c->last_was_wavefront = false;
+        // _reserved[0] selects the path-tracing engine: 0/1 megakernel with path regeneration (default,
+        // fastest measured on C3), 2 wavefront pipeline, 3 state-machine megakernel (fastest on C4)
+        if (fp->_reserved[0] == 2) {
+            int wr = launch_wavefront(c, k, fp->traversal);
+            if (wr != -100) return wr;
+        }
         return launch_path(c, k, fp->traversal, fp->_reserved[0]);
     }
     return launch(c, k, my_tiles * 64u, fp->traversal);

@@ -14,7 +14,9 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
-#define RT_LBVH_LEAF 4u
+#ifndef RT_LBVH_LEAF
+#define RT_LBVH_LEAF 1u
+#endif
 // REBUILT leaf ref: bit31 | (count-1) << 28 | first sorted slot (28 bits)
 #define RT_LBVH_MAX_PRIMS (1u << 28)
 

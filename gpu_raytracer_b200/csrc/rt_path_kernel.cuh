@@ -20,7 +20,12 @@
 #include "rt_kernels.cuh"
 
 #define RT_SSTACK 16   // shared-memory stack entries per thread (16 KB per 256-thread block)
-#define RT_REFILL 8    // leave the traversal phase when this many lanes have finished
+#ifndef RT_REFILL
+#define RT_REFILL 12   // leave the traversal phase when this many lanes have finished their ray
+#endif
+#ifndef RT_TRI_BATCH
+#define RT_TRI_BATCH 16 // leave the node loop when this many lanes have triangles pending
+#endif
 
 enum { LS_NEED_WORK = 0, LS_TRAVERSING = 1, LS_READY = 2, LS_EXHAUSTED = 3 };
 
@@ -226,51 +231,64 @@ __global__ void __launch_bounds__(256, 3) rt_path_trace_v2(const __grid_constant
         if (__all_sync(full, state == LS_EXHAUSTED)) break;
 
         // ================================ phase T ================================
+        // "while-while": a node loop in which lanes that reach a leaf park (tri_rem > 0) until
+        // RT_TRI_BATCH lanes have triangles pending, then a triangle loop that tests one triangle
+        // per lane per iteration.  Keeps box tests and Möller–Trumbore tests in separate,
+        // densely populated instruction streams instead of one divergent if/else per step.
         for (;;) {
-            if (state == LS_TRAVERSING) {
-                if (tri_rem == 0u && cur != 0xFFFFFFFFu && (cur & RT_LEAF_FLAG)) { // ---- enter a leaf
-                    if (POLICY == 2) { tri_slot = cur & 0x0FFFFFFFu; tri_rem = ((cur >> 28) & 7u) + 1u; }
-                    else { tri_slot = cur & ~RT_LEAF_FLAG; tri_rem = __float_as_uint(__ldg(tris + (uint64_t)tri_slot * 3 + 2).w); }
-                    cur = 0xFFFFFFFFu; // consumed; its first triangles are tested in this same step
-                }
-                if (tri_rem) { // ---- up to 4 triangles of the current leaf
-                    uint32_t n = tri_rem < 4u ? tri_rem : 4u;
-                    for (uint32_t i = 0; i < n; i++, tri_slot++) {
-                        const float4* tpn = tris + (uint64_t)tri_slot * 3;
-                        float4 a = __ldg(tpn), c = __ldg(tpn + 1), d = __ldg(tpn + 2);
-                        float t = triangle_t(ray, mk(a.x, a.y, a.z), mk(a.w, c.x, c.y), mk(c.z, c.w, d.x));
-                        uint32_t pos = POLICY == 2 ? __float_as_uint(d.w) : tri_slot;
-                        if (t > 0.0f && (t < best_t || (t == best_t && best_slot != 0xFFFFFFFFu && pos < best_pos))) {
-                            best_t = t; best_slot = tri_slot; best_pos = pos;
+            for (;;) { // ---- node loop
+                if (state == LS_TRAVERSING && tri_rem == 0u) {
+                    if (cur == 0xFFFFFFFFu) { // need the next node
+                        if (sp == 0) state = LS_READY;
+                        else cur = pop();
+                    }
+                    if (state == LS_TRAVERSING) {
+                        if (cur & RT_LEAF_FLAG) { // enter a leaf; its triangles wait for the triangle loop
+                            if (POLICY == 2) { tri_slot = cur & 0x0FFFFFFFu; tri_rem = ((cur >> 28) & 7u) + 1u; }
+                            else { tri_slot = cur & ~RT_LEAF_FLAG; tri_rem = __float_as_uint(__ldg(tris + (uint64_t)tri_slot * 3 + 2).w); }
+                            cur = 0xFFFFFFFFu;
+                        } else { // internal node: two box tests, near child first
+                            const float4* np = nodes + (uint64_t)cur * 4;
+                            float4 q0 = __ldg(np), q1 = __ldg(np + 1), q2 = __ldg(np + 2), q3 = __ldg(np + 3);
+                            uint32_t lref = __float_as_uint(q3.x), rref = __float_as_uint(q3.y);
+                            float el, er;
+                            if (COUNT) c_box += 2;
+                            bool hl = slab(ray.o, inv, mk(q0.x, q0.y, q0.z), mk(q0.w, q1.x, q1.y), &el);
+                            bool hr = slab(ray.o, inv, mk(q1.z, q1.w, q2.x), mk(q2.y, q2.z, q2.w), &er);
+                            float limit = best_t * RT_PRUNE_SCALE + RT_PRUNE_ABS;
+                            hl = hl && (lref != RT_CHILD_ABSENT) && (el <= limit);
+                            hr = hr && (rref != RT_CHILD_ABSENT) && (er <= limit);
+                            if (hl && hr) {
+                                bool right_first = er < el;
+                                push(right_first ? lref : rref);
+                                cur = right_first ? rref : lref;
+                            } else if (hl) cur = lref;
+                            else if (hr) cur = rref;
+                            else cur = 0xFFFFFFFFu;
                         }
                     }
-                    if (COUNT) c_tri += n;
-                    tri_rem -= n;
-                } else if (cur != 0xFFFFFFFFu) { // ---- internal node: two box tests, near child first
-                    const float4* np = nodes + (uint64_t)cur * 4;
-                    float4 q0 = __ldg(np), q1 = __ldg(np + 1), q2 = __ldg(np + 2), q3 = __ldg(np + 3);
-                    uint32_t lref = __float_as_uint(q3.x), rref = __float_as_uint(q3.y);
-                    float el, er;
-                    if (COUNT) c_box += 2;
-                    bool hl = slab(ray.o, inv, mk(q0.x, q0.y, q0.z), mk(q0.w, q1.x, q1.y), &el);
-                    bool hr = slab(ray.o, inv, mk(q1.z, q1.w, q2.x), mk(q2.y, q2.z, q2.w), &er);
-                    float limit = best_t * RT_PRUNE_SCALE + RT_PRUNE_ABS;
-                    hl = hl && (lref != RT_CHILD_ABSENT) && (el <= limit);
-                    hr = hr && (rref != RT_CHILD_ABSENT) && (er <= limit);
-                    if (hl && hr) {
-                        bool right_first = er < el;
-                        push(right_first ? lref : rref);
-                        cur = right_first ? rref : lref;
-                    } else if (hl) cur = lref;
-                    else if (hr) cur = rref;
-                    else cur = 0xFFFFFFFFu;
                 }
-                if (tri_rem == 0u && cur == 0xFFFFFFFFu) { // need the next node
-                    if (sp == 0) state = LS_READY;
-                    else cur = pop();
+                unsigned node_l = __ballot_sync(full, state == LS_TRAVERSING && tri_rem == 0u);
+                unsigned tri_l = __ballot_sync(full, state == LS_TRAVERSING && tri_rem != 0u);
+                unsigned ready_l = __ballot_sync(full, state == LS_READY);
+                if (COUNT) { c_titer++; c_tactive += __popc(node_l); }
+                if (node_l == 0u || __popc(tri_l) >= RT_TRI_BATCH || __popc(ready_l) >= RT_REFILL) break;
+            }
+            for (;;) { // ---- triangle loop: one triangle per lane per iteration
+                bool has = state == LS_TRAVERSING && tri_rem != 0u;
+                if (!__any_sync(full, has)) break;
+                if (has) {
+                    const float4* tpn = tris + (uint64_t)tri_slot * 3;
+                    float4 a = __ldg(tpn), c = __ldg(tpn + 1), d = __ldg(tpn + 2);
+                    float t = triangle_t(ray, mk(a.x, a.y, a.z), mk(a.w, c.x, c.y), mk(c.z, c.w, d.x));
+                    uint32_t pos = POLICY == 2 ? __float_as_uint(d.w) : tri_slot;
+                    if (t > 0.0f && (t < best_t || (t == best_t && best_slot != 0xFFFFFFFFu && pos < best_pos))) {
+                        best_t = t; best_slot = tri_slot; best_pos = pos;
+                    }
+                    if (COUNT) c_tri++;
+                    tri_slot++; tri_rem--;
                 }
             }
-            if (COUNT) { unsigned a = __ballot_sync(full, state == LS_TRAVERSING); c_titer++; c_tactive += __popc(a); }
             unsigned ready = __ballot_sync(full, state == LS_READY);
             unsigned trav = __ballot_sync(full, state == LS_TRAVERSING);
             if (trav == 0u || __popc(ready) >= RT_REFILL) break;

@@ -206,12 +206,13 @@ def test_path_spp1_depth0_is_reference_wavefront(default_ref):
     assert np.array_equal(gpu["composite"], wf["composite"])
 
 
-@pytest.mark.parametrize("traversal", [abi.TRAVERSAL_LITERAL, abi.TRAVERSAL_ORDERED])
-def test_c4_cornell_depth8(traversal):
+@pytest.mark.parametrize("traversal,variant", [(abi.TRAVERSAL_LITERAL, 0), (abi.TRAVERSAL_ORDERED, 0),
+                                               (abi.TRAVERSAL_ORDERED, 2), (abi.TRAVERSAL_ORDERED, 3)])
+def test_c4_cornell_depth8(traversal, variant):
     """C4: Cornell box, diffuse bounces to depth 8 (incoherent rays; divergence stress)."""
     s = g.cornell_scene()
     ref = ob.render_path(s, 256, 256, spp=8, max_depth=8, base_seed=11)
-    gpu = render_gpu_path(s, 256, 256, 8, 8, base_seed=11, traversal=traversal)
+    gpu = render_gpu_path(s, 256, 256, 8, 8, base_seed=11, traversal=traversal, variant=variant)
     compare_path(gpu, ref)
     assert gpu["segments"] > 256 * 256 * 8 * 3
 
@@ -223,7 +224,7 @@ def test_path_default_scene_glass_metal_and_resume(default_ref):
     compare_path(gpu, ref)
 
 
-@pytest.mark.parametrize("variant", [0, 1])
+@pytest.mark.parametrize("variant", [0, 2, 3])
 @pytest.mark.parametrize("traversal", [abi.TRAVERSAL_ORDERED, abi.TRAVERSAL_REBUILT])
 def test_c3_path_terrain_1m(c3_scene_and_ref, traversal, variant):
     """C3 semantics (4 bounces) on the 1M-triangle terrain at reduced size/spp so the oracle finishes."""
