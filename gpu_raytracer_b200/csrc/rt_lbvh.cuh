@@ -65,9 +65,14 @@ __global__ void morton_keys(const float4* __restrict__ pbox, uint32_t n, const u
     float4 lo = pbox[(size_t)i * 2], hi = pbox[(size_t)i * 2 + 1];
     float c[3] = {0.5f * (lo.x + hi.x), 0.5f * (lo.y + hi.y), 0.5f * (lo.z + hi.z)};
     unsigned long long q[3];
+    // One scale for all three axes (the largest centroid extent): the Morton cells stay cubes, so a
+    // flat scene (terrain: y extent << x, z extents) is split in x/z only until the cells are as
+    // small as its height range.  Per-axis normalisation would spend every third split on height
+    // slices that overlap completely in x/z (measured on C3: 92.6 -> see DESIGN.md box tests/ray).
+    float ext = 0.0f;
+    for (int k = 0; k < 3; k++) ext = fmaxf(ext, ord2f(bounds[3 + k]) - ord2f(bounds[k]));
     for (int k = 0; k < 3; k++) {
-        float mn = ord2f(bounds[k]), mx = ord2f(bounds[3 + k]);
-        float ext = mx - mn;
+        float mn = ord2f(bounds[k]);
         float u = ext > 0.0f ? (c[k] - mn) / ext : 0.0f;
         u = fminf(fmaxf(u, 0.0f), 1.0f);
         q[k] = (unsigned long long)min(2097151.0f, u * 2097152.0f);
