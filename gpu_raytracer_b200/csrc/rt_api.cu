@@ -9,6 +9,7 @@
 #include <math.h>
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 #include <string>
 #include <vector>
@@ -17,6 +18,7 @@
 #include "rt_lbvh.cuh"
 #include "rt_path_kernel.cuh"
 #include "rt_wavefront.cuh"
+#include "rt_wave.cuh"
 
 namespace {
 
@@ -108,6 +110,10 @@ struct RtContext {
     DevBuf<uint32_t> wf_queue[2];
     DevBuf<WfCtrl> wf_ctrl;
     bool last_was_wavefront = false;
+    // streaming wavefront engine (rt_wave.cuh)
+    DevBuf<float4> wv_state[2], wv_lbuf;
+    DevBuf<uint2> wv_hit[2];
+    DevBuf<WvCtrl> wv_ctrl;
 
     // outputs (src/renderer.rs:452-475) + progressive state (src/renderer.rs:821-855)
     uint32_t width = 0, height = 0;
@@ -805,6 +811,79 @@ int launch_wavefront(RtContext* c, KParams k, uint32_t traversal) {
     return RT_OK;
 }
 
+// EXTENSION path tracing, streaming wavefront engine (rt_wave.cuh): all samples of a wave in
+// flight at once; per wave one generate, per depth one extend + one shade, one resolve.
+// Queue lengths stay on the device (no host sync inside the frame).
+template <int POLICY>
+void launch_wave_depth(RtContext* c, const KParams& k, const WvBuffers& w, int qi, bool count, uint32_t ext_blocks, uint32_t shade_blocks) {
+    if (count) {
+        wv_extend<POLICY, true><<<ext_blocks, 256, 0, c->stream>>>(k, w, qi);
+        wv_shade<POLICY, true><<<shade_blocks, 256, 0, c->stream>>>(k, w, qi);
+    } else {
+        wv_extend<POLICY, false><<<ext_blocks, 256, 0, c->stream>>>(k, w, qi);
+        wv_shade<POLICY, false><<<shade_blocks, 256, 0, c->stream>>>(k, w, qi);
+    }
+}
+
+int launch_wave(RtContext* c, KParams k, uint32_t traversal) {
+    if (k.n_work == 0) return RT_OK;
+    int policy = pick_policy(c, k, traversal);
+    if (policy < 1) return -100; // literal policy: the caller falls back to the megakernel
+    size_t cap = 40u << 20; // paths in flight per wave (64 B state x2 + 8 B hit x2 + 16 B radiance each)
+    if (const char* e = getenv("RTB200_WAVE_PATHS")) { long long v = atoll(e); if (v > 0) cap = (size_t)v; }
+    uint32_t spp_wave = (uint32_t)(cap / k.n_work);
+    if (spp_wave < 1u) spp_wave = 1u;
+    if (spp_wave > k.spp) spp_wave = k.spp;
+    const size_t P = (size_t)k.n_work * spp_wave;
+    if (c->wv_state[0].reserve(P * 4) < 0 || c->wv_state[1].reserve(P * 4) < 0 || c->wv_hit[0].reserve(P) < 0 ||
+        c->wv_hit[1].reserve(P) < 0 || c->wv_lbuf.reserve(P) < 0 || c->wv_ctrl.reserve(1) < 0)
+        return fail(c, RT_ERR_CUDA, "wave engine cudaMalloc failed for %zu paths", P);
+    WvBuffers w;
+    w.state[0] = c->wv_state[0].ptr; w.state[1] = c->wv_state[1].ptr;
+    w.hit[0] = c->wv_hit[0].ptr; w.hit[1] = c->wv_hit[1].ptr;
+    w.lbuf = c->wv_lbuf.ptr; w.ctrl = c->wv_ctrl.ptr;
+    const bool count = k.counters != nullptr;
+    int per_sm = 0, sms = 0;
+    const void* fn = policy == 2 ? (const void*)wv_extend<2, false> : (const void*)wv_extend<1, false>;
+    CK(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, 256, 0));
+    CK(c, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device));
+    uint32_t ext_blocks = (uint32_t)(per_sm > 0 ? per_sm : 1) * (uint32_t)sms;
+    uint32_t full_blocks = (uint32_t)((P + 255) / 256);
+    if (ext_blocks > full_blocks) ext_blocks = full_blocks;
+    uint32_t stream_blocks = (uint32_t)sms * 8u;
+    if (stream_blocks > full_blocks) stream_blocks = full_blocks;
+    CK(c, cudaEventRecord(c->ev0, c->stream));
+    CK(c, cudaMemsetAsync(c->wv_ctrl.ptr, 0, sizeof(WvCtrl), c->stream));
+    const uint32_t s_end = k.first_sample + k.spp;
+    for (uint32_t s0 = k.first_sample; s0 < s_end; s0 += spp_wave) {
+        w.s0 = s0; w.spp_wave = s_end - s0 < spp_wave ? s_end - s0 : spp_wave;
+        w.first_wave = s0 == k.first_sample; w.last_wave = s0 + w.spp_wave == s_end;
+        if (!w.first_wave) CK(c, cudaMemsetAsync(c->wv_ctrl.ptr, 0, 16, c->stream)); // n[0], n[1], head
+        wv_generate<<<stream_blocks, 256, 0, c->stream>>>(k, w);
+        for (uint32_t d = 0; d <= k.path_max_depth; d++) {
+            if (policy == 2) launch_wave_depth<2>(c, k, w, (int)(d & 1u), count, ext_blocks, stream_blocks);
+            else launch_wave_depth<1>(c, k, w, (int)(d & 1u), count, ext_blocks, stream_blocks);
+            c->launches += 2;
+        }
+        wv_resolve<<<stream_blocks, 256, 0, c->stream>>>(k, w);
+        c->launches += 2;
+    }
+    CK(c, cudaGetLastError());
+    // publish the segment count (and instrumentation) where rt_last_segments / rt_read_counters look
+    CK(c, cudaMemcpyAsync(c->dcounters.ptr + 6, &c->wv_ctrl.ptr->segments, 8, cudaMemcpyDeviceToDevice, c->stream));
+    if (count) {
+        CK(c, cudaMemcpyAsync(c->dcounters.ptr + 0, &c->wv_ctrl.ptr->c[0], 16, cudaMemcpyDeviceToDevice, c->stream)); // box, tri
+        CK(c, cudaMemcpyAsync(c->dcounters.ptr + 2, &c->wv_ctrl.ptr->segments, 8, cudaMemcpyDeviceToDevice, c->stream));
+        CK(c, cudaMemcpyAsync(c->dcounters.ptr + 3, &c->wv_ctrl.ptr->c[2], 16, cudaMemcpyDeviceToDevice, c->stream)); // shaded, fallbacks
+    }
+    CK(c, cudaEventRecord(c->ev1, c->stream));
+    c->timed = true;
+    c->last_traversal = policy == 2 ? RT_TRAVERSAL_REBUILT : RT_TRAVERSAL_ORDERED;
+    c->count_next = false;
+    c->last_was_wavefront = true;
+    return RT_OK;
+}
+
 int check_ready(RtContext* c) {
     if (!c) return RT_ERR_INVALID_ARGUMENT;
     if (c->width == 0) return fail(c, RT_ERR_NOT_READY, "rt_resize has not been called");
@@ -885,6 +964,10 @@ int rt_render_frame(RtContext* c, const RtCamera* cam, const RtFrameParams* fp) 
         // fastest measured on C3), 2 wavefront pipeline, 3 state-machine megakernel (fastest on C4)
         if (fp->_reserved[0] == 2) {
             int wr = launch_wavefront(c, k, fp->traversal);
+            if (wr != -100) return wr;
+        }
+        if (fp->_reserved[0] == 4) {
+            int wr = launch_wave(c, k, fp->traversal);
             if (wr != -100) return wr;
         }
         return launch_path(c, k, fp->traversal, fp->_reserved[0]);

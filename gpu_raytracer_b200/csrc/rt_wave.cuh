@@ -1,0 +1,436 @@
+// rt_wave.cuh — EXTENSION (SPEC.md) path tracing, streaming wavefront engine ("wave").
+//
+// Same per-path arithmetic and bit-identical results as rt_path_trace (rt_kernels.cuh);
+// the execution shape is chosen from what ncu showed on the megakernel (profiles/r1h_*):
+// 10 of 32 lanes active per issued instruction (triangle tests 3.6 lanes, stack pops 5.7),
+// and more L1 data-stage wavefronts spent on the local-memory traversal stack than on the
+// BVH itself.  Here
+//   * all samples of a wave are in flight at once as compact path records (64 B state +
+//     8 B hit), ping-ponged by depth, so there is one extend + one shade launch per depth
+//     for the whole frame instead of per sample, and the extend kernel's idle lanes are
+//     refilled by loading 40 bytes instead of running the shading code;
+//   * wv_extend keeps box tests and Möller–Trumbore tests in separate, densely populated
+//     instruction streams: a lane that reaches a leaf postpones it and (speculatively) keeps
+//     descending until it holds a second leaf; the warp leaves the node loop when too few
+//     lanes can still descend, then all lanes test their postponed triangles together;
+//   * the traversal stack is a per-thread column of shared memory (entry k of the 32 lanes
+//     of a warp are 32 consecutive words: conflict-free whatever the lanes' depths are);
+//   * the REBUILT certification (one exact slab test on the winner's uploaded leaf box)
+//     moves to wv_shade, which runs convergent over compacted paths;
+//   * sample radiances go to Lbuf[sample][pixel] and wv_resolve adds them in sample order,
+//     so fp32 accumulation stays bit-identical to the sequential definition (SPEC.md step 4).
+#pragma once
+#include "rt_kernels.cuh"
+
+struct WvCtrl {
+    unsigned int n[2];          // live paths at the current / next depth (ping-pong)
+    unsigned int head;          // wv_extend work cursor
+    unsigned int _pad;
+    unsigned long long segments;
+    unsigned long long c[4];    // instrumentation: box tests, triangle tests, shaded hits, literal fallbacks
+};
+
+struct WvBuffers {
+    float4* state[2];  // 4 x float4 per path: (o, rng) (d, depth) (throughput, work idx) (L, local sample)
+    uint2* hit[2];     // per path: (t bits, id); in: sphere seed, out: closest hit
+    float4* lbuf;      // [local sample][work idx]: finished sample radiance
+    WvCtrl* ctrl;
+    uint32_t s0, spp_wave; // samples [s0, s0 + spp_wave) are in this wave
+    uint32_t last_wave;    // resolve writes the composite
+    uint32_t first_wave;   // resolve honours reset_accum
+};
+
+// hit id encoding
+#define WV_ID_MISS 0xFFFFFFFFu
+#define WV_KIND_TRI 0u      // id = slot in btris / wtris
+#define WV_KIND_SPHERE 1u   // id = 1<<30 | sphere index
+#define WV_KIND_LITERAL 2u  // id = 2<<30 | (sphere index or 0x3FFFFFFF): wv_shade runs the literal policy
+#define WV_NO_SPHERE 0x3FFFFFFFu
+
+#ifndef WV_STK
+#define WV_STK 24          // shared-memory stack entries per thread (24 KB per 256-thread block)
+#endif
+#ifndef WV_REFILL
+#define WV_REFILL 6        // refill when this many lanes have finished their ray
+#endif
+#ifndef WV_NODE_MIN
+#define WV_NODE_MIN 20     // leave the node loop when fewer lanes than this can still descend
+#endif
+#ifndef WV_TRI_AGAIN
+#define WV_TRI_AGAIN 16    // repeat the triangle phase while this many lanes hold a second leaf
+#endif
+#ifndef WV_SPEC
+#define WV_SPEC 1          // speculative descent past the first postponed leaf
+#endif
+
+// spheres first (shader/src/lib.rs:183-190, 252-269): returns the seed t and the sphere index
+__device__ __forceinline__ void wv_sphere_seed(const KParams& p, const Ray& ray, float* closest, uint32_t* sphere_idx) {
+    float c = FLT_MAX - 2.0f;
+    uint32_t si = WV_NO_SPHERE;
+    for (uint32_t i = 0; i < p.off.spheres_count; i++) {
+        uint64_t o = (uint64_t)p.off.spheres_offset + (uint64_t)i * 5;
+        float t;
+        if (sphere_t(ray, mk(meta_f(p, o), meta_f(p, o + 1), meta_f(p, o + 2)), meta_f(p, o + 3), c, &t)) { c = t; si = i; }
+    }
+    *closest = c; *sphere_idx = si;
+}
+__device__ __forceinline__ uint2 wv_seed_record(const KParams& p, const Ray& ray) {
+    if (p.off.spheres_count == 0u) return make_uint2(__float_as_uint(FLT_MAX - 2.0f), WV_ID_MISS);
+    float c; uint32_t si;
+    wv_sphere_seed(p, ray, &c, &si);
+    return make_uint2(__float_as_uint(c), si == WV_NO_SPHERE ? WV_ID_MISS : ((WV_KIND_SPHERE << 30) | si));
+}
+
+// ---- wave start: SPEC.md steps 1-2 for every (pixel, sample) of this wave ---------------
+// Warp = one 8x4 pixel group for one sample; consecutive warps = the samples of that group.
+__global__ void __launch_bounds__(256) wv_generate(const __grid_constant__ KParams p, WvBuffers w) {
+    const unsigned full = 0xFFFFFFFFu;
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint64_t total_warps = (uint64_t)(p.n_work >> 5) * w.spp_wave;
+    for (uint64_t wi = (uint64_t)blockIdx.x * 8u + (threadIdx.x >> 5); wi < total_warps; wi += (uint64_t)gridDim.x * 8u) {
+        uint32_t group = (uint32_t)(wi / w.spp_wave), sl = (uint32_t)(wi % w.spp_wave);
+        uint32_t idx = group * 32u + lane, px = 0, py = 0;
+        bool ok = work_to_pixel(p, idx, &px, &py);
+        unsigned m = __ballot_sync(full, ok);
+        if (!m) continue;
+        uint32_t base = 0;
+        int leader = __ffs(m) - 1;
+        if ((int)lane == leader) base = atomicAdd(&w.ctrl->n[0], (unsigned int)__popc(m));
+        base = __shfl_sync(full, base, leader);
+        if (!ok) continue;
+        uint32_t slot = base + __popc(m & ((1u << lane) - 1u));
+        uint32_t s = w.s0 + sl;
+        SimpleRng rng; rng.seed = p.base_seed + s + px + py * p.width;
+        float jx = 0.5f, jy = 0.5f;
+        if (s != 0u) { jx = rng.next_f32(); jy = rng.next_f32(); }
+        Ray ray = camera_ray(p, px, py, jx, jy, true);
+        float4* st = w.state[0] + (size_t)slot * 4;
+        st[0] = make_float4(ray.o.x, ray.o.y, ray.o.z, __uint_as_float(rng.seed));
+        st[1] = make_float4(ray.d.x, ray.d.y, ray.d.z, __uint_as_float(0u));
+        st[2] = make_float4(1.0f, 1.0f, 1.0f, __uint_as_float(idx));
+        st[3] = make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(sl));
+        w.hit[0][slot] = wv_seed_record(p, ray);
+    }
+}
+
+// ---- extend: closest triangle of every ray of the current depth ---------------------------
+template <int POLICY, bool COUNT> // POLICY 1 (ORDERED, uploaded tree) or 2 (REBUILT, internal LBVH)
+__global__ void __launch_bounds__(256, 3) wv_extend(const __grid_constant__ KParams p, WvBuffers w, int qi) {
+    __shared__ uint32_t s_stack[WV_STK][256];
+    uint32_t lstack[64 - WV_STK];
+    const uint32_t tid = threadIdx.x, lane = tid & 31u;
+    const unsigned full = 0xFFFFFFFFu;
+    constexpr uint32_t EMPTY = 0xFFFFFFFFu; // has RT_LEAF_FLAG set: never an internal node
+    const float4* __restrict__ nodes = POLICY == 2 ? p.bnodes : p.wnodes;
+    const float4* __restrict__ tris = POLICY == 2 ? p.btris : p.wtris;
+    const uint32_t root_ref = POLICY == 2 ? p.broot_ref : p.root_ref;
+    const uint32_t n = w.ctrl->n[qi];
+    const float4* __restrict__ state = w.state[qi];
+    uint2* __restrict__ hit = w.hit[qi];
+    if (blockIdx.x == 0 && tid == 0) w.ctrl->n[qi ^ 1] = 0; // wv_shade of this depth appends there
+
+    uint32_t slot = EMPTY;      // queue position of the ray this lane traces
+    bool exhausted = false, literal = false;
+    float ox = 0, oy = 0, oz = 0, dx = 0, dy = 0, dz = 1, ix = 0, iy = 0, iz = 0, kx = 0, ky = 0, kz = 0;
+    float best_t = FLT_MAX, limit = FLT_MAX;
+    uint32_t best_slot = EMPTY, best_pos = 0u, seed_id = WV_ID_MISS;
+    uint32_t cur = EMPTY, pend = EMPTY;
+    int sp = 0;
+    unsigned long long c_box = 0, c_tri = 0;
+
+    auto push = [&](uint32_t v) { if (sp < WV_STK) s_stack[sp][tid] = v; else lstack[sp - WV_STK] = v; sp++; };
+    auto pop = [&]() -> uint32_t {
+        if (sp == 0) return EMPTY;
+        sp--;
+        return sp < WV_STK ? s_stack[sp][tid] : lstack[sp - WV_STK];
+    };
+    auto flush = [&]() { // store the finished ray's record
+        if (slot != EMPTY) {
+            if (literal) hit[slot] = make_uint2(__float_as_uint(best_t), (WV_KIND_LITERAL << 30) | (seed_id == WV_ID_MISS ? WV_NO_SPHERE : (seed_id & WV_NO_SPHERE)));
+            else if (best_slot != EMPTY) hit[slot] = make_uint2(__float_as_uint(best_t), best_slot);
+            slot = EMPTY;
+        }
+    };
+
+    for (;;) {
+        // ---- refill finished lanes from the queue
+        const bool done = cur == EMPTY && pend == EMPTY;
+        const unsigned idle = __ballot_sync(full, done && !exhausted);
+        const unsigned act = __ballot_sync(full, !done);
+        if (idle && (__popc(idle) >= WV_REFILL || act == 0u)) {
+            uint32_t base = 0;
+            int leader = __ffs(idle) - 1;
+            if ((int)lane == leader) base = atomicAdd(&w.ctrl->head, (unsigned int)__popc(idle));
+            base = __shfl_sync(full, base, leader);
+            if (done && !exhausted) {
+                flush();
+                uint32_t q = base + __popc(idle & ((1u << lane) - 1u));
+                if (q >= n) exhausted = true;
+                else {
+                    slot = q;
+                    float4 a = __ldcs(state + (size_t)q * 4), b = __ldcs(state + (size_t)q * 4 + 1);
+                    uint2 seed = hit[q];
+                    ox = a.x; oy = a.y; oz = a.z; dx = b.x; dy = b.y; dz = b.z;
+                    best_t = __uint_as_float(seed.x); seed_id = seed.y;
+                    limit = best_t * RT_PRUNE_SCALE + RT_PRUNE_ABS;
+                    best_slot = EMPTY; best_pos = 0u; sp = 0; pend = EMPTY; literal = false;
+                    cur = root_ref == RT_CHILD_ABSENT ? EMPTY : root_ref;
+                    if (POLICY == 2) {
+                        // zero / tiny direction components: neither the certification argument nor the
+                        // FMA slab applies (closest_triangle_rebuilt) -> wv_shade runs the literal policy
+                        if (!(fabsf(dx) >= 1e-30f && fabsf(dy) >= 1e-30f && fabsf(dz) >= 1e-30f)) { literal = true; cur = EMPTY; }
+                        // boxes of the internal tree are conservative (inflated 2^-16 relative), so
+                        // the slab test may use t = b * inv - o * inv with one FMA per plane
+                        ix = 1.0f / dx; iy = 1.0f / dy; iz = 1.0f / dz;
+                        kx = ox * ix; ky = oy * iy; kz = oz * iz;
+                        float e;
+                        if (COUNT) c_box++;
+                        if (cur != EMPTY && !slab_fma(mk(ix, iy, iz), mk(kx, ky, kz), mka(p.broot_min), mka(p.broot_max), &e)) cur = EMPTY;
+                    } else {
+                        ix = 1.0f / dx; iy = 1.0f / dy; iz = 1.0f / dz; // exact: intersection.rs:152
+                        float e;
+                        if (COUNT) c_box++;
+                        if (cur != EMPTY && !slab(mk(ox, oy, oz), mk(ix, iy, iz), mka(p.root_min), mka(p.root_max), &e)) cur = EMPTY;
+                    }
+                    if (cur != EMPTY && (cur & RT_LEAF_FLAG)) { pend = cur; cur = EMPTY; } // the root is a leaf
+                }
+            }
+        }
+        const unsigned live = __ballot_sync(full, !(cur == EMPTY && pend == EMPTY));
+        if (live == 0u) {
+            if (__all_sync(full, exhausted)) break;
+            continue;
+        }
+        // ---- node loop: every lane holding an internal node descends; a lane that reaches a leaf
+        // postpones it and keeps going until it holds a second one
+        const int nl = __popc(live);
+        const int node_min = nl - (nl >> 2) < WV_NODE_MIN ? nl - (nl >> 2) : WV_NODE_MIN;
+        for (;;) {
+            if (!(cur & RT_LEAF_FLAG)) {
+                const float4* np = nodes + (uint64_t)cur * 4;
+                float4 q0 = __ldg(np), q1 = __ldg(np + 1), q2 = __ldg(np + 2), q3 = __ldg(np + 3);
+                uint32_t lref = __float_as_uint(q3.x), rref = __float_as_uint(q3.y);
+                float el, er;
+                bool hl, hr;
+                if (COUNT) c_box += 2;
+                if (POLICY == 2) {
+                    hl = slab_fma(mk(ix, iy, iz), mk(kx, ky, kz), mk(q0.x, q0.y, q0.z), mk(q0.w, q1.x, q1.y), &el);
+                    hr = slab_fma(mk(ix, iy, iz), mk(kx, ky, kz), mk(q1.z, q1.w, q2.x), mk(q2.y, q2.z, q2.w), &er);
+                } else {
+                    hl = slab(mk(ox, oy, oz), mk(ix, iy, iz), mk(q0.x, q0.y, q0.z), mk(q0.w, q1.x, q1.y), &el) && lref != RT_CHILD_ABSENT;
+                    hr = slab(mk(ox, oy, oz), mk(ix, iy, iz), mk(q1.z, q1.w, q2.x), mk(q2.y, q2.z, q2.w), &er) && rref != RT_CHILD_ABSENT;
+                }
+                hl = hl && (el <= limit);
+                hr = hr && (er <= limit);
+                if (hl && hr) {
+                    bool right_first = er < el;
+                    push(right_first ? lref : rref);
+                    cur = right_first ? rref : lref;
+                } else if (hl) cur = lref;
+                else if (hr) cur = rref;
+                else cur = pop();
+                if (WV_SPEC && (cur & RT_LEAF_FLAG) && cur != EMPTY && pend == EMPTY) { pend = cur; cur = pop(); }
+            }
+            if (__popc(__ballot_sync(full, !(cur & RT_LEAF_FLAG))) < node_min) break;
+        }
+        // ---- triangle phase: all lanes test their postponed leaf together
+        for (;;) {
+            uint32_t leaf = pend;
+            if (!WV_SPEC && leaf == EMPTY && (cur & RT_LEAF_FLAG) && cur != EMPTY) { leaf = cur; cur = pop(); }
+            if (leaf != EMPTY) {
+                uint32_t ts = POLICY == 2 ? (leaf & 0x0FFFFFFFu) : (leaf & ~RT_LEAF_FLAG);
+                uint32_t rem = POLICY == 2 ? ((leaf >> 28) & 7u) + 1u : 0u;
+                Ray ray; ray.o = mk(ox, oy, oz); ray.d = mk(dx, dy, dz);
+                for (;;) {
+                    const float4* tpn = tris + (uint64_t)ts * 3;
+                    float4 a = __ldg(tpn), c = __ldg(tpn + 1), d = __ldg(tpn + 2);
+                    float t = triangle_t(ray, mk(a.x, a.y, a.z), mk(a.w, c.x, c.y), mk(c.z, c.w, d.x));
+                    uint32_t pos = POLICY == 2 ? __float_as_uint(d.w) : ts;
+                    if (COUNT) c_tri++;
+                    // strict `t < closest` in visit order; with re-ordered visits the equal-t winner is
+                    // the smaller triangle_indices position (== first in the reference's DFS order)
+                    if (t > 0.0f && (t < best_t || (t == best_t && best_slot != EMPTY && pos < best_pos))) {
+                        best_t = t; best_slot = ts; best_pos = pos;
+                        limit = best_t * RT_PRUNE_SCALE + RT_PRUNE_ABS;
+                    }
+                    if (POLICY == 2) { if (--rem == 0u) break; }
+                    else if (__float_as_uint(d.w) <= 1u) break;
+                    ts++;
+                }
+                pend = EMPTY;
+                if (WV_SPEC && (cur & RT_LEAF_FLAG) && cur != EMPTY) { pend = cur; cur = pop(); }
+            }
+            if (!WV_SPEC) break;
+            if (__popc(__ballot_sync(full, pend != EMPTY)) < WV_TRI_AGAIN) break;
+        }
+    }
+    flush();
+    if (COUNT) {
+        for (int o = 16; o; o >>= 1) { c_box += __shfl_xor_sync(full, c_box, o); c_tri += __shfl_xor_sync(full, c_tri, o); }
+        if (lane == 0u) { atomicAdd(&w.ctrl->c[0], c_box); atomicAdd(&w.ctrl->c[1], c_tri); }
+    }
+}
+
+// ---- shade: SPEC.md steps 3.2-3.8 and 4 for every path of the current depth ----------------
+template <int POLICY, bool COUNT>
+__global__ void __launch_bounds__(256) wv_shade(const __grid_constant__ KParams p, WvBuffers w, int qi) {
+    const unsigned full = 0xFFFFFFFFu;
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t n = w.ctrl->n[qi];
+    const float4* __restrict__ tris = POLICY == 2 ? p.btris : p.wtris;
+    if (blockIdx.x == 0 && threadIdx.x == 0) { w.ctrl->head = 0; w.ctrl->segments += n; } // wv_extend of this depth has finished
+    const uint32_t n_round = (n + 31u) & ~31u;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += gridDim.x * blockDim.x) {
+        bool cont = false;
+        Ray ray; ray.o = mk(0, 0, 0); ray.d = mk(0, 0, 1);
+        V3 tp = mk(0, 0, 0), L = mk(0, 0, 0);
+        SimpleRng rng; rng.seed = 0;
+        uint32_t depth = 0, idx = 0, sl = 0;
+        if (i < n) {
+            const float4* st = w.state[qi] + (size_t)i * 4;
+            float4 s0 = __ldcs(st), s1 = __ldcs(st + 1), s2 = __ldcs(st + 2), s3 = __ldcs(st + 3);
+            uint2 hr = w.hit[qi][i];
+            ray.o = mk(s0.x, s0.y, s0.z); ray.d = mk(s1.x, s1.y, s1.z);
+            rng.seed = __float_as_uint(s0.w);
+            depth = __float_as_uint(s1.w); idx = __float_as_uint(s2.w); sl = __float_as_uint(s3.w);
+            tp = mk(s2.x, s2.y, s2.z); L = mk(s3.x, s3.y, s3.z);
+            // ---- rebuild the Hit from the record
+            Hit h;
+            h.t = FLT_MAX; h.kind = 0u; h.prim = 0xFFFFFFFFu; h.material_id = 0xFFFFFFFFu;
+            h.point = mk(0, 0, 0); h.normal = mk(0, 0, 0);
+            const uint32_t kind = hr.y >> 30;
+            bool lit = hr.y != WV_ID_MISS && kind == WV_KIND_LITERAL;
+            TriBest b;
+            b.hit = false; b.n_box = 0; b.n_tri = 0; b.n_fallback = 0;
+            if (hr.y != WV_ID_MISS && kind == WV_KIND_TRI) {
+                const float4* tpn = tris + (uint64_t)hr.y * 3;
+                float4 a = __ldg(tpn), c = __ldg(tpn + 1), d = __ldg(tpn + 2);
+                b.hit = true; b.t = __uint_as_float(hr.x);
+                b.v0 = mk(a.x, a.y, a.z); b.e1 = mk(a.w, c.x, c.y); b.e2 = mk(c.z, c.w, d.x);
+                b.mat = __float_as_uint(d.y); b.prim = __float_as_uint(d.z);
+                if (POLICY == 2) { // certification against the uploaded tree (see closest_triangle_rebuilt)
+                    uint32_t leaf = __ldg(p.leaf_of_pos + __float_as_uint(d.w));
+                    uint64_t no = (uint64_t)p.off.bvh_nodes_offset + (uint64_t)leaf * 12;
+                    V3 inv = mk(1.0f / ray.d.x, 1.0f / ray.d.y, 1.0f / ray.d.z);
+                    float entry;
+                    lit = !slab(ray.o, inv, mk(meta_f(p, no), meta_f(p, no + 1), meta_f(p, no + 2)),
+                                mk(meta_f(p, no + 4), meta_f(p, no + 5), meta_f(p, no + 6)), &entry);
+                }
+            }
+            float sphere_seed = FLT_MAX - 2.0f;
+            uint32_t sphere_idx = WV_NO_SPHERE;
+            if (hr.y != WV_ID_MISS && kind == WV_KIND_SPHERE) { sphere_seed = __uint_as_float(hr.x); sphere_idx = hr.y & WV_NO_SPHERE; }
+            if (lit) { // rare: the reference's own traversal for this ray
+                wv_sphere_seed(p, ray, &sphere_seed, &sphere_idx);
+                closest_triangle_literal(p, ray, sphere_seed, b);
+                if (COUNT) { atomicAdd(&w.ctrl->c[3], 1ull); atomicAdd(&w.ctrl->c[0], (unsigned long long)b.n_box); atomicAdd(&w.ctrl->c[1], (unsigned long long)b.n_tri); }
+            }
+            if (b.hit) {
+                h.t = b.t; h.kind = 2u; h.prim = b.prim; h.material_id = b.mat;
+                h.point = ray.o + ray.d * b.t;
+                h.normal = normalize3(cross3(b.e1, b.e2));
+            } else if (sphere_idx != WV_NO_SPHERE) {
+                uint64_t o = (uint64_t)p.off.spheres_offset + (uint64_t)sphere_idx * 5;
+                V3 c = mk(meta_f(p, o), meta_f(p, o + 1), meta_f(p, o + 2));
+                h.t = sphere_seed; h.kind = 1u; h.prim = sphere_idx; h.material_id = meta_at(p, o + 4);
+                h.point = ray.o + ray.d * sphere_seed;
+                h.normal = normalize3(h.point - c);
+            }
+            if (COUNT && h.kind != 0u) atomicAdd(&w.ctrl->c[2], 1ull);
+            if (depth == 0u && w.s0 + sl == 0u && (p.outputs & RT_OUT_HITS)) {
+                uint32_t px, py;
+                work_to_pixel(p, idx, &px, &py);
+                reinterpret_cast<uint4*>(p.hits)[(size_t)py * p.width + px] = make_uint4(h.kind, h.prim, __float_as_uint(h.t), h.material_id);
+            }
+            bool end = false;
+            if (h.kind == 0u) { L = L + mk(0.1f, 0.2f, 0.3f) * tp; end = true; }
+            else if (h.material_id >= p.n_mats) { L = L + mk(1.0f, 0.0f, 1.0f) * tp; end = true; }
+            else {
+                MatEval m = load_material(p, h.material_id);
+                L = L + shade_hit_m(p, h, m, 0xFFu) * tp;
+                if (depth == p.path_max_depth) end = true;
+                if (!end && depth >= 3u) { // Russian roulette
+                    float pr = fminf(fmaxf(fmaxf(fmaxf(tp.x, tp.y), tp.z), 0.05f), 1.0f);
+                    float r = rng.next_f32();
+                    if (r > pr) end = true;
+                    else tp = mk(tp.x / pr, tp.y / pr, tp.z / pr);
+                }
+                if (!end) {
+                    float r0 = rng.next_f32();
+                    V3 u = mk(0.0f, 0.0f, 0.0f);
+                    for (int k = 0; k < 8; k++) {
+                        float a = rng.next_f32_signed(), bb = rng.next_f32_signed(), cc = rng.next_f32_signed();
+                        float q = a * a + bb * bb + cc * cc;
+                        if (q > 1e-6f && q <= 1.0f) { u = mk(a, bb, cc) * (1.0f / sqrtf(q)); break; }
+                    }
+                    V3 d = ray.d, nn = h.normal;
+                    float cosi = dot3(nn, d);
+                    V3 nf = cosi < 0.0f ? nn : -nn;
+                    V3 wv = nf + u;
+                    if (dot3(wv, wv) < 1e-8f) wv = nf;
+                    wv = normalize3(wv);
+                    float T = fminf(fmaxf(m.transmission, 0.0f), 1.0f);
+                    V3 dir;
+                    float side = 1.0f;
+                    if (T > 0.0f && r0 < T) {
+                        float eta = cosi < 0.0f ? 1.0f / m.ior : m.ior;
+                        float c1 = -dot3(d, nf);
+                        float k = 1.0f - eta * eta * (1.0f - c1 * c1);
+                        if (k < 0.0f) dir = d - nf * (2.0f * dot3(d, nf));
+                        else { dir = d * eta + nf * (eta * c1 - sqrtf(k)); side = -1.0f; }
+                        dir = normalize3(dir);
+                    } else if (m.metallic > 0.5f) {
+                        V3 mr = d - nf * (2.0f * dot3(d, nf));
+                        dir = mr * (1.0f - m.roughness) + wv * m.roughness;
+                        if (dot3(dir, dir) < 1e-8f || dot3(dir, nf) <= 0.0f) dir = wv;
+                        dir = normalize3(dir);
+                    } else {
+                        dir = wv;
+                    }
+                    tp = tp * m.albedo;
+                    ray.o = h.point + nf * (side * 1e-3f);
+                    ray.d = dir;
+                    depth++;
+                    cont = true;
+                }
+            }
+            if (end) w.lbuf[(size_t)sl * p.n_work + idx] = make_float4(L.x, L.y, L.z, 1.0f); // SPEC.md step 4, summed by wv_resolve
+        }
+        // ---- survivors become the compact path list of the next depth (order within the warp kept)
+        unsigned m = __ballot_sync(full, cont);
+        if (m) {
+            uint32_t base = 0;
+            int leader = __ffs(m) - 1;
+            if ((int)lane == leader) base = atomicAdd(&w.ctrl->n[qi ^ 1], (unsigned int)__popc(m));
+            base = __shfl_sync(full, base, leader);
+            if (cont) {
+                uint32_t ns = base + __popc(m & ((1u << lane) - 1u));
+                float4* st = w.state[qi ^ 1] + (size_t)ns * 4;
+                st[0] = make_float4(ray.o.x, ray.o.y, ray.o.z, __uint_as_float(rng.seed));
+                st[1] = make_float4(ray.d.x, ray.d.y, ray.d.z, __uint_as_float(depth));
+                st[2] = make_float4(tp.x, tp.y, tp.z, __uint_as_float(idx));
+                st[3] = make_float4(L.x, L.y, L.z, __uint_as_float(sl));
+                w.hit[qi ^ 1][ns] = wv_seed_record(p, ray);
+            }
+        }
+    }
+}
+
+// ---- resolve: add the wave's sample radiances to the accumulation buffer in sample order ----
+__global__ void __launch_bounds__(256) wv_resolve(const __grid_constant__ KParams p, WvBuffers w) {
+    for (uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x; idx < p.n_work; idx += gridDim.x * blockDim.x) {
+        uint32_t px, py;
+        if (!work_to_pixel(p, idx, &px, &py)) continue;
+        const size_t pix = (size_t)py * p.width + px;
+        float4 a = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        if (!(w.first_wave && p.reset_accum)) a = p.accum[pix];
+        for (uint32_t sl = 0; sl < w.spp_wave; sl++) {
+            float4 l = __ldcs(w.lbuf + (size_t)sl * p.n_work + idx);
+            a.x = a.x + l.x; a.y = a.y + l.y; a.z = a.z + l.z; a.w = a.w + 1.0f;
+        }
+        if (!w.last_wave || (p.outputs & RT_OUT_ACCUM)) p.accum[pix] = a;
+        if (w.last_wave && (p.outputs & RT_OUT_COMPOSITE))
+            p.composite[pix] = make_uchar4((unsigned char)unorm8(a.x / a.w), (unsigned char)unorm8(a.y / a.w),
+                                           (unsigned char)unorm8(a.z / a.w), 255);
+    }
+}

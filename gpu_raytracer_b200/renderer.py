@@ -215,6 +215,6 @@ class ComputeRenderer:
         fp["mode"], fp["outputs"], fp["spp"], fp["first_sample"] = mode, outputs, spp, first_sample
         fp["max_depth"], fp["base_seed"], fp["reset_accum"] = max_depth, base_seed, int(reset_accum)
         fp["tile_stride"], fp["tile_phase"], fp["traversal"] = tile_stride, tile_phase, traversal
-        fp["_reserved"][0] = variant  # path mode engine: 0 megakernel, 2 wavefront, 3 state-machine megakernel
+        fp["_reserved"][0] = variant  # path mode engine: 0 megakernel, 2 wavefront, 3 state-machine megakernel, 4 streaming wavefront (wave)
         self.ctx._ck(self.ctx.lib.rt_render_frame(self.ctx.handle, cam.ctypes.data_as(C.c_void_p),
                                                   fp.ctypes.data_as(C.c_void_p)))

@@ -207,7 +207,8 @@ def test_path_spp1_depth0_is_reference_wavefront(default_ref):
 
 
 @pytest.mark.parametrize("traversal,variant", [(abi.TRAVERSAL_LITERAL, 0), (abi.TRAVERSAL_ORDERED, 0),
-                                               (abi.TRAVERSAL_ORDERED, 2), (abi.TRAVERSAL_ORDERED, 3)])
+                                               (abi.TRAVERSAL_ORDERED, 2), (abi.TRAVERSAL_ORDERED, 3),
+                                               (abi.TRAVERSAL_ORDERED, 4)])
 def test_c4_cornell_depth8(traversal, variant):
     """C4: Cornell box, diffuse bounces to depth 8 (incoherent rays; divergence stress)."""
     s = g.cornell_scene()
@@ -217,14 +218,25 @@ def test_c4_cornell_depth8(traversal, variant):
     assert gpu["segments"] > 256 * 256 * 8 * 3
 
 
-def test_path_default_scene_glass_metal_and_resume(default_ref):
+@pytest.mark.parametrize("variant", [0, 4])
+def test_path_default_scene_glass_metal_and_resume(default_ref, variant):
     s, _ = default_ref
     ref = ob.render_path(s, 320, 180, spp=6, max_depth=5, base_seed=2)
-    gpu = render_gpu_path(s, 320, 180, 6, 5, base_seed=2, chunks=[1, 2, 3])  # progressive in 3 calls
+    gpu = render_gpu_path(s, 320, 180, 6, 5, base_seed=2, chunks=[1, 2, 3], variant=variant)  # progressive in 3 calls
     compare_path(gpu, ref)
 
 
-@pytest.mark.parametrize("variant", [0, 2, 3])
+def test_wave_engine_multi_wave(default_ref, monkeypatch):
+    """Wave engine with a path budget so small that the 5 samples take 3 waves (2 + 2 + 1): the
+    per-wave resolve must add the samples in the same order as one wave / the megakernel."""
+    s, _ = default_ref
+    ref = ob.render_path(s, 320, 180, spp=5, max_depth=4, base_seed=9)
+    monkeypatch.setenv("RTB200_WAVE_PATHS", str(2 * 6 * 16384))  # 320x180 = 3x2 tiles of 16384 work items
+    gpu = render_gpu_path(s, 320, 180, 5, 4, base_seed=9, variant=4)
+    compare_path(gpu, ref)
+
+
+@pytest.mark.parametrize("variant", [0, 2, 3, 4])
 @pytest.mark.parametrize("traversal", [abi.TRAVERSAL_ORDERED, abi.TRAVERSAL_REBUILT])
 def test_c3_path_terrain_1m(c3_scene_and_ref, traversal, variant):
     """C3 semantics (4 bounces) on the 1M-triangle terrain at reduced size/spp so the oracle finishes."""
