@@ -86,6 +86,16 @@ struct Ray {
     V3 o, d;
 };
 
+// One 64-byte BVH node = two 256-bit read-only loads (sm_100 LDG.E.256; SASS: LDG.E.ENL2.256.CONSTANT).
+// ncu on the traversal kernels showed the L1 data stage (wavefronts per load instruction x distinct
+// line) as the busiest unit, so a node costs two load instructions per lane instead of four.
+__device__ __forceinline__ void ldg_node(const float4* __restrict__ np, float4& q0, float4& q1, float4& q2, float4& q3) {
+    asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+        : "=f"(q0.x), "=f"(q0.y), "=f"(q0.z), "=f"(q0.w), "=f"(q1.x), "=f"(q1.y), "=f"(q1.z), "=f"(q1.w) : "l"(np));
+    asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+        : "=f"(q2.x), "=f"(q2.y), "=f"(q2.z), "=f"(q2.w), "=f"(q3.x), "=f"(q3.y), "=f"(q3.z), "=f"(q3.w) : "l"(np + 2));
+}
+
 struct Hit {
     float t;
     uint32_t kind;  // 0 miss 1 sphere 2 triangle
@@ -312,7 +322,8 @@ __device__ void closest_triangle_ordered(const KParams& p, const Ray& ray, float
     for (;;) {
         while (!(cur & RT_LEAF_FLAG)) {
             const float4* np = p.wnodes + (uint64_t)cur * 4;
-            float4 q0 = __ldg(np), q1 = __ldg(np + 1), q2 = __ldg(np + 2), q3 = __ldg(np + 3);
+            float4 q0, q1, q2, q3;
+            ldg_node(np, q0, q1, q2, q3);
             uint32_t lref = __float_as_uint(q3.x), rref = __float_as_uint(q3.y);
             float el, er;
             b.n_box += 2;
@@ -389,7 +400,8 @@ __device__ void closest_triangle_rebuilt(const KParams& p, const Ray& ray, float
             }
         } else {
             const float4* np = p.bnodes + (uint64_t)cur * 4;
-            float4 q0 = __ldg(np), q1 = __ldg(np + 1), q2 = __ldg(np + 2), q3 = __ldg(np + 3);
+            float4 q0, q1, q2, q3;
+            ldg_node(np, q0, q1, q2, q3);
             uint32_t lref = __float_as_uint(q3.x), rref = __float_as_uint(q3.y);
             float el, er;
             b.n_box += 2;

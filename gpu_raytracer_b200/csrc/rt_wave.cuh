@@ -135,12 +135,18 @@ __global__ void __launch_bounds__(256, 3) wv_extend(const __grid_constant__ KPar
     float best_t = FLT_MAX, limit = FLT_MAX;
     uint32_t best_slot = EMPTY, best_pos = 0u, seed_id = WV_ID_MISS;
     uint32_t cur = EMPTY, pend = EMPTY;
-    int sp = 0;
+    int sp = 1;
     unsigned long long c_box = 0, c_tri = 0;
+    // warp-uniform work-fetch state
+    uint32_t chunk_next = 0, chunk_end = 0;
+    bool queue_done = n == 0u;
+    const uint32_t chunk = n >= gridDim.x * 8u * 128u * 4u ? 128u : 32u;
 
     auto push = [&](uint32_t v) { if (sp < WV_STK) s_stack[sp][tid] = v; else lstack[sp - WV_STK] = v; sp++; };
+    // entry 0 of every column holds EMPTY and sp starts at 1: popping the last entry yields EMPTY
+    // ("traversal finished") without an emptiness test; a finished lane is never popped again
+    s_stack[0][tid] = EMPTY;
     auto pop = [&]() -> uint32_t {
-        if (sp == 0) return EMPTY;
         sp--;
         return sp < WV_STK ? s_stack[sp][tid] : lstack[sp - WV_STK];
     };
@@ -158,14 +164,32 @@ __global__ void __launch_bounds__(256, 3) wv_extend(const __grid_constant__ KPar
         const unsigned idle = __ballot_sync(full, done && !exhausted);
         const unsigned act = __ballot_sync(full, !done);
         if (idle && (__popc(idle) >= WV_REFILL || act == 0u)) {
-            uint32_t base = 0;
-            int leader = __ffs(idle) - 1;
-            if ((int)lane == leader) base = atomicAdd(&w.ctrl->head, (unsigned int)__popc(idle));
-            base = __shfl_sync(full, base, leader);
+            // the warp reserves `chunk` consecutive queue positions at a time: one atomic per chunk
+            // instead of one per refill, and consecutive positions are neighbouring rays
+            const uint32_t need = (uint32_t)__popc(idle);
+            uint32_t rest_base = 0, rest_n = 0;
+            if (chunk_end - chunk_next < need && !queue_done) {
+                uint32_t nb = 0;
+                if (lane == 0u) nb = atomicAdd(&w.ctrl->head, (unsigned int)chunk);
+                nb = __shfl_sync(full, nb, 0);
+                rest_base = chunk_next; rest_n = chunk_end - chunk_next; // left-overs of the old chunk go first
+                if (nb >= n) { chunk_next = chunk_end = 0; queue_done = true; }
+                else {
+                    chunk_next = nb; chunk_end = nb + chunk;
+                    if (chunk_end >= n) { chunk_end = n; queue_done = true; }
+                }
+            }
+            const uint32_t r = (uint32_t)__popc(idle & ((1u << lane) - 1u));
+            uint32_t q = EMPTY;
+            if (r < rest_n) q = rest_base + r;
+            else if (chunk_next + (r - rest_n) < chunk_end) q = chunk_next + (r - rest_n);
+            {
+                uint32_t take = need > rest_n ? need - rest_n : 0u;
+                chunk_next = chunk_next + take < chunk_end ? chunk_next + take : chunk_end;
+            }
             if (done && !exhausted) {
                 flush();
-                uint32_t q = base + __popc(idle & ((1u << lane) - 1u));
-                if (q >= n) exhausted = true;
+                if (q == EMPTY) exhausted = queue_done;
                 else {
                     slot = q;
                     float4 a = __ldcs(state + (size_t)q * 4), b = __ldcs(state + (size_t)q * 4 + 1);
@@ -173,7 +197,7 @@ __global__ void __launch_bounds__(256, 3) wv_extend(const __grid_constant__ KPar
                     ox = a.x; oy = a.y; oz = a.z; dx = b.x; dy = b.y; dz = b.z;
                     best_t = __uint_as_float(seed.x); seed_id = seed.y;
                     limit = best_t * RT_PRUNE_SCALE + RT_PRUNE_ABS;
-                    best_slot = EMPTY; best_pos = 0u; sp = 0; pend = EMPTY; literal = false;
+                    best_slot = EMPTY; best_pos = 0u; sp = 1; pend = EMPTY; literal = false;
                     cur = root_ref == RT_CHILD_ABSENT ? EMPTY : root_ref;
                     if (POLICY == 2) {
                         // zero / tiny direction components: neither the certification argument nor the
@@ -208,7 +232,8 @@ __global__ void __launch_bounds__(256, 3) wv_extend(const __grid_constant__ KPar
         for (;;) {
             if (!(cur & RT_LEAF_FLAG)) {
                 const float4* np = nodes + (uint64_t)cur * 4;
-                float4 q0 = __ldg(np), q1 = __ldg(np + 1), q2 = __ldg(np + 2), q3 = __ldg(np + 3);
+                float4 q0, q1, q2, q3;
+                ldg_node(np, q0, q1, q2, q3);
                 uint32_t lref = __float_as_uint(q3.x), rref = __float_as_uint(q3.y);
                 float el, er;
                 bool hl, hr;
