@@ -114,6 +114,8 @@ struct RtContext {
     DevBuf<float4> wv_state[2], wv_lbuf;
     DevBuf<uint2> wv_hit[2];
     DevBuf<WvCtrl> wv_ctrl;
+    std::vector<cudaEvent_t> wv_events;  // one before the first and one after every launch of the last wave frame
+    std::vector<int> wv_event_stage;     // stage of the launch that ends at event i+1: 0 generate, 1 extend, 2 shade, 3 resolve
 
     // outputs (src/renderer.rs:452-475) + progressive state (src/renderer.rs:821-855)
     uint32_t width = 0, height = 0;
@@ -350,6 +352,7 @@ void rt_destroy(RtContext* c) {
     if (c->stream) { cudaStreamSynchronize(c->stream); cudaStreamDestroy(c->stream); }
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
+    for (cudaEvent_t e : c->wv_events) cudaEventDestroy(e);
     delete c;
 }
 
@@ -814,17 +817,6 @@ int launch_wavefront(RtContext* c, KParams k, uint32_t traversal) {
 // EXTENSION path tracing, streaming wavefront engine (rt_wave.cuh): all samples of a wave in
 // flight at once; per wave one generate, per depth one extend + one shade, one resolve.
 // Queue lengths stay on the device (no host sync inside the frame).
-template <int POLICY>
-void launch_wave_depth(RtContext* c, const KParams& k, const WvBuffers& w, int qi, bool count, uint32_t ext_blocks, uint32_t shade_blocks) {
-    if (count) {
-        wv_extend<POLICY, true><<<ext_blocks, 256, 0, c->stream>>>(k, w, qi);
-        wv_shade<POLICY, true><<<shade_blocks, 256, 0, c->stream>>>(k, w, qi);
-    } else {
-        wv_extend<POLICY, false><<<ext_blocks, 256, 0, c->stream>>>(k, w, qi);
-        wv_shade<POLICY, false><<<shade_blocks, 256, 0, c->stream>>>(k, w, qi);
-    }
-}
-
 int launch_wave(RtContext* c, KParams k, uint32_t traversal) {
     if (k.n_work == 0) return RT_OK;
     int policy = pick_policy(c, k, traversal);
@@ -855,17 +847,39 @@ int launch_wave(RtContext* c, KParams k, uint32_t traversal) {
     CK(c, cudaEventRecord(c->ev0, c->stream));
     CK(c, cudaMemsetAsync(c->wv_ctrl.ptr, 0, sizeof(WvCtrl), c->stream));
     const uint32_t s_end = k.first_sample + k.spp;
+    // per-stage timing: an event between consecutive launches (rt_last_stage_ms)
+    size_t n_ev = 0;
+    c->wv_event_stage.clear();
+    auto mark = [&](int stage) -> int {
+        if (n_ev >= c->wv_events.size()) {
+            cudaEvent_t e;
+            if (cudaEventCreate(&e) != cudaSuccess) return -1;
+            c->wv_events.push_back(e);
+        }
+        if (cudaEventRecord(c->wv_events[n_ev++], c->stream) != cudaSuccess) return -1;
+        if (stage >= 0) c->wv_event_stage.push_back(stage);
+        return 0;
+    };
+    if (mark(-1)) return fail(c, RT_ERR_CUDA, "wave engine: event record failed");
     for (uint32_t s0 = k.first_sample; s0 < s_end; s0 += spp_wave) {
         w.s0 = s0; w.spp_wave = s_end - s0 < spp_wave ? s_end - s0 : spp_wave;
         w.first_wave = s0 == k.first_sample; w.last_wave = s0 + w.spp_wave == s_end;
         if (!w.first_wave) CK(c, cudaMemsetAsync(c->wv_ctrl.ptr, 0, 16, c->stream)); // n[0], n[1], head
+        if (!w.first_wave) mark(-1);
         wv_generate<<<stream_blocks, 256, 0, c->stream>>>(k, w);
+        mark(0);
         for (uint32_t d = 0; d <= k.path_max_depth; d++) {
-            if (policy == 2) launch_wave_depth<2>(c, k, w, (int)(d & 1u), count, ext_blocks, stream_blocks);
-            else launch_wave_depth<1>(c, k, w, (int)(d & 1u), count, ext_blocks, stream_blocks);
+            const int qi = (int)(d & 1u);
+            if (policy == 2) { if (count) wv_extend<2, true><<<ext_blocks, 256, 0, c->stream>>>(k, w, qi); else wv_extend<2, false><<<ext_blocks, 256, 0, c->stream>>>(k, w, qi); }
+            else { if (count) wv_extend<1, true><<<ext_blocks, 256, 0, c->stream>>>(k, w, qi); else wv_extend<1, false><<<ext_blocks, 256, 0, c->stream>>>(k, w, qi); }
+            mark(1);
+            if (policy == 2) { if (count) wv_shade<2, true><<<stream_blocks, 256, 0, c->stream>>>(k, w, qi); else wv_shade<2, false><<<stream_blocks, 256, 0, c->stream>>>(k, w, qi); }
+            else { if (count) wv_shade<1, true><<<stream_blocks, 256, 0, c->stream>>>(k, w, qi); else wv_shade<1, false><<<stream_blocks, 256, 0, c->stream>>>(k, w, qi); }
+            mark(2);
             c->launches += 2;
         }
         wv_resolve<<<stream_blocks, 256, 0, c->stream>>>(k, w);
+        mark(3);
         c->launches += 2;
     }
     CK(c, cudaGetLastError());
@@ -882,6 +896,30 @@ int launch_wave(RtContext* c, KParams k, uint32_t traversal) {
     c->count_next = false;
     c->last_was_wavefront = true;
     return RT_OK;
+}
+
+// Microbenchmark behind the traversal roofline: every lane loads one random, independent
+// 32-byte sector per iteration (ld.global.nc.v8.f32, the node-fetch instruction) from a
+// buffer of `sectors` sectors.  A small footprint measures the SM's L1 rate for divergent
+// sector gathers, a footprint between L1 and L2 size the L2 rate, a larger one HBM.
+__global__ void __launch_bounds__(256) probe_gather(const float4* __restrict__ buf, uint32_t sector_mask, uint32_t iters,
+                                                    float* __restrict__ out) {
+    uint32_t x = (blockIdx.x * blockDim.x + threadIdx.x) * 2654435761u + 12345u;
+    float acc = 0.0f;
+    for (uint32_t i = 0; i < iters; i += 4) {
+        float4 a[4], b[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            x = x * 1664525u + 1013904223u;
+            const float4* sp = buf + (size_t)((x >> 7) & sector_mask) * 2;
+            asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                         : "=f"(a[u].x), "=f"(a[u].y), "=f"(a[u].z), "=f"(a[u].w), "=f"(b[u].x), "=f"(b[u].y), "=f"(b[u].z), "=f"(b[u].w)
+                         : "l"(sp));
+        }
+#pragma unroll
+        for (int u = 0; u < 4; u++) acc += a[u].x + b[u].w;
+    }
+    out[blockIdx.x * blockDim.x + threadIdx.x] = acc;
 }
 
 int check_ready(RtContext* c) {
@@ -960,13 +998,15 @@ int rt_render_frame(RtContext* c, const RtCamera* cam, const RtFrameParams* fp) 
         k.work_counter = reinterpret_cast<unsigned int*>(c->dcounters.ptr + 7);
         CK(c, cudaMemsetAsync(c->dcounters.ptr + 6, 0, 2 * sizeof(unsigned long long), c->stream));
         c->last_was_wavefront = false;
-        // _reserved[0] selects the path-tracing engine: 0/1 megakernel with path regeneration (default,
-        // fastest measured on C3), 2 wavefront pipeline, 3 state-machine megakernel (fastest on C4)
+        c->wv_event_stage.clear();
+        // _reserved[0] selects the path-tracing engine: 0 auto = 4 where a re-laid-out traversal policy is
+        // available (fastest measured on C3 and C4), else 1; 1 megakernel with path regeneration;
+        // 2 per-sample wavefront pipeline; 3 state-machine megakernel; 4 streaming wavefront (rt_wave.cuh)
         if (fp->_reserved[0] == 2) {
             int wr = launch_wavefront(c, k, fp->traversal);
             if (wr != -100) return wr;
         }
-        if (fp->_reserved[0] == 4) {
+        if (fp->_reserved[0] == 4 || fp->_reserved[0] == 0) {
             int wr = launch_wave(c, k, fp->traversal);
             if (wr != -100) return wr;
         }
@@ -1110,5 +1150,56 @@ int rt_last_segments(RtContext* c, uint64_t* out) {
     return RT_OK;
 }
 float rt_last_build_ms(const RtContext* c) { return c ? c->last_build_ms : -1.0f; }
+
+// GPU time per stage of the last streaming-wavefront frame (rt_wave.cuh), summed over its
+// launches: out[0] generate, [1] extend, [2] shade, [3] resolve (ms); out[4..7] launch counts.
+int rt_last_stage_ms(RtContext* c, float out[8]) {
+    if (!c || !out) return RT_ERR_INVALID_ARGUMENT;
+    for (int i = 0; i < 8; i++) out[i] = 0.0f;
+    if (!c->last_was_wavefront || c->wv_event_stage.empty()) return fail(c, RT_ERR_NOT_READY, "the last launch was not a wave-engine frame");
+    CK(c, cudaSetDevice(c->device));
+    CK(c, cudaStreamSynchronize(c->stream));
+    size_t e = 0;
+    for (size_t i = 0; i < c->wv_event_stage.size(); i++) {
+        int st = c->wv_event_stage[i];
+        if (st == 0 && i != 0) e++; // a new wave starts with its own opening event
+        float ms = 0.0f;
+        CK(c, cudaEventElapsedTime(&ms, c->wv_events[e], c->wv_events[e + 1]));
+        out[st] += ms; out[4 + st] += 1.0f;
+        e++;
+    }
+    return RT_OK;
+}
+
+// Measured gather bandwidth (GB/s) for random independent 32-byte sector loads over a
+// footprint of `footprint_bytes` (rounded down to a power of two, >= 4 KiB): the roofline
+// denominators of the traversal kernels (L1-resident, L2-resident, HBM-resident node sets).
+int rt_probe_gather_bandwidth(RtContext* c, uint64_t footprint_bytes, float* out_gbs) {
+    if (!c || !out_gbs) return RT_ERR_INVALID_ARGUMENT;
+    CK(c, cudaSetDevice(c->device));
+    uint64_t fp = 4096;
+    while (fp * 2 <= footprint_bytes && fp < (1ull << 34)) fp *= 2;
+    int sms = 0;
+    CK(c, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device));
+    const uint32_t blocks = (uint32_t)sms * 8u, iters = 4096u;
+    float4* buf = nullptr; float* out = nullptr;
+    CK(c, cudaMalloc((void**)&buf, fp));
+    if (cudaMalloc((void**)&out, (size_t)blocks * 256 * 4) != cudaSuccess) { cudaFree(buf); return fail(c, RT_ERR_CUDA, "probe cudaMalloc failed"); }
+    cudaMemsetAsync(buf, 0, fp, c->stream);
+    const uint32_t mask = (uint32_t)(fp / 32 - 1);
+    probe_gather<<<blocks, 256, 0, c->stream>>>(buf, mask, 256u, out); // warm-up
+    cudaEventRecord(c->ev0, c->stream);
+    probe_gather<<<blocks, 256, 0, c->stream>>>(buf, mask, iters, out);
+    cudaEventRecord(c->ev1, c->stream);
+    cudaError_t e = cudaEventSynchronize(c->ev1);
+    float ms = 0.0f;
+    if (e == cudaSuccess) e = cudaEventElapsedTime(&ms, c->ev0, c->ev1);
+    cudaFree(buf); cudaFree(out);
+    c->launches += 2;
+    c->timed = false;
+    if (e != cudaSuccess || !(ms > 0.0f)) return fail(c, RT_ERR_CUDA, "probe_gather failed: %s", cudaGetErrorString(e));
+    *out_gbs = (float)((double)blocks * 256.0 * iters * 32.0 / (ms * 1e-3) / 1e9);
+    return RT_OK;
+}
 
 } // extern "C"

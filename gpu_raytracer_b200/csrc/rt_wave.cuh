@@ -48,10 +48,10 @@ struct WvBuffers {
 #define WV_NO_SPHERE 0x3FFFFFFFu
 
 #ifndef WV_STK
-#define WV_STK 24          // shared-memory stack entries per thread (24 KB per 256-thread block)
+#define WV_STK 16          // shared-memory stack entries per thread (16 KB per 256-thread block; deeper entries spill to local memory)
 #endif
 #ifndef WV_REFILL
-#define WV_REFILL 6        // refill when this many lanes have finished their ray
+#define WV_REFILL 10       // refill when this many lanes have finished their ray
 #endif
 #ifndef WV_NODE_MIN
 #define WV_NODE_MIN 20     // leave the node loop when fewer lanes than this can still descend
@@ -61,6 +61,9 @@ struct WvBuffers {
 #endif
 #ifndef WV_SPEC
 #define WV_SPEC 1          // speculative descent past the first postponed leaf
+#endif
+#ifndef WV_BLOCKS
+#define WV_BLOCKS 4        // resident 256-thread blocks per SM the extend kernel is compiled for
 #endif
 
 // spheres first (shader/src/lib.rs:183-190, 252-269): returns the seed t and the sphere index
@@ -115,7 +118,7 @@ __global__ void __launch_bounds__(256) wv_generate(const __grid_constant__ KPara
 
 // ---- extend: closest triangle of every ray of the current depth ---------------------------
 template <int POLICY, bool COUNT> // POLICY 1 (ORDERED, uploaded tree) or 2 (REBUILT, internal LBVH)
-__global__ void __launch_bounds__(256, 3) wv_extend(const __grid_constant__ KParams p, WvBuffers w, int qi) {
+__global__ void __launch_bounds__(256, WV_BLOCKS) wv_extend(const __grid_constant__ KParams p, WvBuffers w, int qi) {
     __shared__ uint32_t s_stack[WV_STK][256];
     uint32_t lstack[64 - WV_STK];
     const uint32_t tid = threadIdx.x, lane = tid & 31u;

@@ -103,6 +103,19 @@ class Context:
                     literal_fallbacks=int(out[4]), s_phases=int(out[5]), s_ready_lanes=int(out[6]),
                     t_iterations=int(out[7]), t_active_lanes=int(out[8]))
 
+    def probe_gather_bandwidth(self, footprint_bytes):
+        """GB/s of random independent 32-byte sector loads over a footprint (traversal roofline denominators)."""
+        out = C.c_float(0.0)
+        self._ck(self.lib.rt_probe_gather_bandwidth(self.handle, int(footprint_bytes), C.byref(out)))
+        return float(out.value)
+
+    def last_stage_ms(self):
+        """Per-stage GPU ms of the last wave-engine frame: dict(generate, extend, shade, resolve, launches)."""
+        out = np.zeros(8, np.float32)
+        self._ck(self.lib.rt_last_stage_ms(self.handle, _p(out)))
+        return dict(generate=float(out[0]), extend=float(out[1]), shade=float(out[2]), resolve=float(out[3]),
+                    launches=[int(x) for x in out[4:8]])
+
     @property
     def last_kernel_ms(self):
         return float(self.lib.rt_last_kernel_ms(self.handle))

@@ -71,7 +71,8 @@ typedef struct RtFrameParams {
     uint32_t tile_stride;  /* multi-GPU tile split: this context renders the */
     uint32_t tile_phase;   /*   128x128 tiles i with i % tile_stride == tile_phase (0,0 = all) */
     uint32_t traversal;    /* RT_TRAVERSAL_* */
-    uint32_t _reserved[2];
+    uint32_t _reserved[2]; /* [0]: RT_MODE_PATH engine (0 auto; tuning/tests: 1 megakernel, 2 per-sample
+                            * wavefront, 3 state-machine megakernel, 4 streaming wavefront); [1]: 0 */
 } RtFrameParams;
 
 /* ---- context: stands in for RenderState.device/queue + the three output
@@ -164,6 +165,17 @@ void* rt_stream(RtContext* ctx);
 int rt_last_segments(RtContext* ctx, uint64_t* out);
 /* GPU time of the last upload-time re-layout + LBVH build, ms (<0 if none) */
 float rt_last_build_ms(const RtContext* ctx);
+/* EXTENSION, streaming wavefront engine: GPU time per stage of the last RT_MODE_PATH frame,
+ * summed over its launches (CUDA events between consecutive launches on the context
+ * stream): out[0] generate, [1] extend (closest hit), [2] shade, [3] resolve, in ms;
+ * out[4..7] the number of launches of each stage.  RT_ERR_NOT_READY if the last frame used
+ * another engine. */
+int rt_last_stage_ms(RtContext* ctx, float out[8]);
+/* Microbenchmark for the traversal roofline (no reference analogue): GB/s of random,
+ * independent 32-byte sector loads (the node-fetch instruction) over a buffer of
+ * footprint_bytes (rounded down to a power of two): small = L1 gather rate, between L1 and
+ * L2 size = L2 gather rate, larger = HBM gather rate. */
+int rt_probe_gather_bandwidth(RtContext* ctx, uint64_t footprint_bytes, float* out_gbs);
 
 #ifdef __cplusplus
 }

@@ -206,7 +206,7 @@ def test_path_spp1_depth0_is_reference_wavefront(default_ref):
     assert np.array_equal(gpu["composite"], wf["composite"])
 
 
-@pytest.mark.parametrize("traversal,variant", [(abi.TRAVERSAL_LITERAL, 0), (abi.TRAVERSAL_ORDERED, 0),
+@pytest.mark.parametrize("traversal,variant", [(abi.TRAVERSAL_LITERAL, 0), (abi.TRAVERSAL_ORDERED, 1),
                                                (abi.TRAVERSAL_ORDERED, 2), (abi.TRAVERSAL_ORDERED, 3),
                                                (abi.TRAVERSAL_ORDERED, 4)])
 def test_c4_cornell_depth8(traversal, variant):
@@ -218,7 +218,7 @@ def test_c4_cornell_depth8(traversal, variant):
     assert gpu["segments"] > 256 * 256 * 8 * 3
 
 
-@pytest.mark.parametrize("variant", [0, 4])
+@pytest.mark.parametrize("variant", [1, 4])
 def test_path_default_scene_glass_metal_and_resume(default_ref, variant):
     s, _ = default_ref
     ref = ob.render_path(s, 320, 180, spp=6, max_depth=5, base_seed=2)
@@ -236,7 +236,7 @@ def test_wave_engine_multi_wave(default_ref, monkeypatch):
     compare_path(gpu, ref)
 
 
-@pytest.mark.parametrize("variant", [0, 2, 3, 4])
+@pytest.mark.parametrize("variant", [1, 2, 3, 4])
 @pytest.mark.parametrize("traversal", [abi.TRAVERSAL_ORDERED, abi.TRAVERSAL_REBUILT])
 def test_c3_path_terrain_1m(c3_scene_and_ref, traversal, variant):
     """C3 semantics (4 bounces) on the 1M-triangle terrain at reduced size/spp so the oracle finishes."""
