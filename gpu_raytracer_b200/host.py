@@ -165,6 +165,67 @@ def cornell_scene(strategy=abi.BVH_AUTO):
     return Scene(cam, np.zeros(0, dtype=abi.Sphere), t, v[:nv.value].copy(), m, l, name="cornell").rebuild_bvh(strategy)
 
 
+class GltfError(ValueError):
+    """GltfError (src/gltf_loader.rs:14-20)."""
+
+
+def _copy_array(ptr, n, dtype):
+    if not n:
+        return np.zeros(0, dtype=dtype)
+    buf = (C.c_uint8 * (n * np.dtype(dtype).itemsize)).from_address(ptr)
+    return np.frombuffer(buf, dtype=dtype, count=n).copy()
+
+
+def load_gltf(source, scene_index=None, strategy=abi.BVH_AUTO, base_dir=None):
+    """SceneState::load_from_gltf (src/scene.rs:43-69): GltfLoader::load_from_path / load_from_glb +
+    extract_scene (src/gltf_loader.rs:53-125), first camera or Camera::new, then BvhBuilder::build.
+    `source` is a path (.gltf / .glb) or bytes."""
+    lib = load()
+    h = C.c_void_p()
+    err = C.create_string_buffer(512)
+    si = -1 if scene_index is None else int(scene_index)
+    if isinstance(source, (bytes, bytearray, memoryview)):
+        data = np.frombuffer(bytes(source), dtype=np.uint8)
+        rc = lib.rt_gltf_load_memory(_p(data), len(data), (base_dir or ".").encode(), si, C.byref(h), err, len(err))
+    else:
+        rc = lib.rt_gltf_load_file(str(source).encode(), si, C.byref(h), err, len(err))
+    if rc != 0:
+        raise GltfError(err.value.decode(errors="replace"))
+    try:
+        cnt = np.zeros(10, dtype=np.uint64)
+        lib.rt_gltf_counts(h, _p(cnt))
+        nt, nv, nm, ns, nl, nc, ntex, ntb, _nscenes, nwarn = (int(x) for x in cnt)
+        cams = _copy_array(lib.rt_gltf_cameras(h), nc, abi.Camera)
+        sc = Scene(cams[0].copy() if nc else camera_default(),
+                   _copy_array(lib.rt_gltf_spheres(h), ns, abi.Sphere), _copy_array(lib.rt_gltf_triangles(h), nt, abi.Triangle),
+                   _copy_array(lib.rt_gltf_vertices(h), nv, abi.Vertex), _copy_array(lib.rt_gltf_materials(h), nm, abi.Material),
+                   _copy_array(lib.rt_gltf_lights(h), nl, abi.Light),
+                   textures=_copy_array(lib.rt_gltf_textures(h), ntex, abi.TextureInfo),
+                   texture_data=_copy_array(lib.rt_gltf_texture_data(h), ntb, np.uint8), name="gltf")
+        sc.cameras = cams
+        sc.warnings = [lib.rt_gltf_warning(h, i).decode() for i in range(nwarn)]
+    finally:
+        lib.rt_gltf_free(h)
+    return sc.rebuild_bvh(strategy) if strategy is not None else sc
+
+
+def write_image(path, rgba8):
+    """Output stage (SURVEY.md 8f #4): .ppm or .png from an (H, W, 4) uint8 image (composite / channel read-back)."""
+    a = np.ascontiguousarray(rgba8, dtype=np.uint8)
+    h, w = a.shape[:2]
+    fn = load().rt_write_png_rgba8 if str(path).lower().endswith(".png") else load().rt_write_ppm_rgba8
+    if fn(str(path).encode(), _p(a), w, h) != 0:
+        raise OSError(f"cannot write {path}")
+
+
+def write_pfm(path, accum):
+    """rgb / sample count of the (H, W, 4) float32 accumulation buffer as a PFM file."""
+    a = np.ascontiguousarray(accum, dtype=np.float32)
+    h, w = a.shape[:2]
+    if load().rt_write_pfm_accum(str(path).encode(), _p(a), w, h) != 0:
+        raise OSError(f"cannot write {path}")
+
+
 def pack_scene_metadata(scene):
     """The combined scene-metadata buffer and offsets, exactly as
     BufferManager::update_scene_metadata lays them out (src/buffers.rs:213-268).

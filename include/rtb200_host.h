@@ -74,6 +74,37 @@ void rt_scene_terrain(uint32_t nx, uint32_t nz, uint32_t seed, RtVertex* vertice
 void rt_scene_cornell(RtVertex* vertices, uint32_t* n_vertices, RtTriangle triangles[36], RtMaterial materials[4],
                       RtLight lights[1], RtCamera* camera);
 
+/* ---- glTF 2.0 / GLB ingestion (src/gltf_loader.rs:53-590, src/scene.rs:43-69): JSON + external
+ * .bin / base64 / GLB buffers, node hierarchy (matrix or TRS), TRIANGLES / STRIP / FAN with u8 / u16 /
+ * u32 or no indices, bit-exact position de-duplication per primitive, cameras, KHR_lights_punctual,
+ * pbrMetallicRoughness + KHR_materials_{pbrSpecularGlossiness,transmission,ior,specular,volume}.
+ * Images are not decoded (dimensions from the PNG/JPEG header, RGBA8 block zero-filled): the shader
+ * never reads textures.  scene_index < 0 = the default scene.  Returns 0, or -1 with a message in err. */
+typedef struct RtGltfScene RtGltfScene;
+typedef struct RtGltfCounts {
+    uint64_t triangles, vertices, materials, spheres, lights, cameras, textures, texture_bytes, scenes, warnings;
+} RtGltfCounts;
+int rt_gltf_load_file(const char* path, int scene_index, RtGltfScene** out, char* err, uint64_t err_len);
+int rt_gltf_load_memory(const uint8_t* data, uint64_t n, const char* base_dir, int scene_index, RtGltfScene** out,
+                        char* err, uint64_t err_len);
+void rt_gltf_free(RtGltfScene* scene);
+void rt_gltf_counts(const RtGltfScene* scene, RtGltfCounts* out);
+const RtTriangle* rt_gltf_triangles(const RtGltfScene* scene);
+const RtVertex* rt_gltf_vertices(const RtGltfScene* scene);
+const RtMaterial* rt_gltf_materials(const RtGltfScene* scene);
+const RtSphere* rt_gltf_spheres(const RtGltfScene* scene);   /* always empty, like LoadedScene.spheres */
+const RtLight* rt_gltf_lights(const RtGltfScene* scene);
+const RtCamera* rt_gltf_cameras(const RtGltfScene* scene);
+const RtTextureInfo* rt_gltf_textures(const RtGltfScene* scene);
+const uint8_t* rt_gltf_texture_data(const RtGltfScene* scene);
+const char* rt_gltf_warning(const RtGltfScene* scene, uint64_t i);
+
+/* ---- output stage (the reference presents to a window only, shader/src/lib.rs:368-391): image files
+ * from the buffers rt_read_composite_rgba8 / rt_read_channel_rgba8 / rt_read_accum_f32 return. */
+int rt_write_ppm_rgba8(const char* path, const uint8_t* rgba, uint32_t width, uint32_t height);
+int rt_write_png_rgba8(const char* path, const uint8_t* rgba, uint32_t width, uint32_t height);
+int rt_write_pfm_accum(const char* path, const float* accum, uint32_t width, uint32_t height);
+
 #ifdef __cplusplus
 }
 #endif
