@@ -60,6 +60,9 @@ def parse_args():
     ap.add_argument("--variant", type=int, default=0, help="path mode engine: 0 auto = streaming wavefront (default), 1 megakernel, "
                                                            "2 per-sample wavefront, 3 state-machine megakernel")
     ap.add_argument("--traversal", default="auto", choices=["auto", "literal", "ordered", "rebuilt"])
+    ap.add_argument("--gather", default="peer", choices=["peer", "nccl"],
+                    help="N > 1: how finished tiles reach rank 0: peer = P2P stores from the render kernels into rank 0's "
+                         "frame (CUDA IPC) + a 4-byte NCCL all-reduce as barrier; nccl = pack + dist.gather + unpack")
     return ap.parse_args()
 
 
@@ -267,7 +270,16 @@ def run_b200(args, wl, world, rank, local):
     my_pixels = tiles.pixels_of_rank(w, h, world, rank)
     trav = {"auto": abi.TRAVERSAL_AUTO, "literal": abi.TRAVERSAL_LITERAL, "ordered": abi.TRAVERSAL_ORDERED,
             "rebuilt": abi.TRAVERSAL_REBUILT}[args.traversal]
-    gather = tiles.TileGather(dist, torch, w, h, tiles.WHAT_COMPOSITE, "cuda") if world > 1 else None
+    gather = peer = None
+    if world > 1 and args.gather == "peer":
+        try:
+            peer = tiles.PeerFrame(dist, torch, ctx, stream)
+            outputs |= peer.extra_outputs
+        except g.RtError as e:  # no P2P between these GPUs: NCCL path
+            print("peer frame unavailable (%s): falling back to the NCCL gather" % e, file=sys.stderr)
+            peer = None
+    if world > 1 and peer is None:
+        gather = tiles.TileGather(dist, torch, w, h, tiles.WHAT_COMPOSITE, "cuda")
     flush = torch.empty(512 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
 
     def render():
@@ -280,7 +292,9 @@ def run_b200(args, wl, world, rank, local):
     def frame():
         """One step: trace this rank's tiles, then (N > 1) gather the finished tiles to rank 0."""
         render()
-        if gather is not None:
+        if peer is not None:
+            peer.finish()  # the tiles are already in rank 0's frame (P2P stores in the kernels); stream-ordered barrier
+        elif gather is not None:
             with torch.cuda.stream(stream):  # NCCL is ordered after the kernel on the context's stream
                 gather.run(lambda dst: ctx.pack_tiles(tiles.WHAT_COMPOSITE, world, rank, dst.data_ptr()),
                            lambda src, r: ctx.unpack_tiles(tiles.WHAT_COMPOSITE, world, r, src.data_ptr()))
@@ -314,16 +328,31 @@ def run_b200(args, wl, world, rank, local):
         e1.synchronize()
         torch.cuda.synchronize()
         step_ms.append(e0.elapsed_time(e1))
-        kernel_ms.append(ctx.last_kernel_ms if gather is None else float("nan"))
-        if path:
-            try:
-                stage_ms.append(ctx.last_stage_ms())  # streaming wavefront engine only
-            except g.RtError:
-                pass
+        kernel_ms.append(ctx.last_kernel_ms)  # this rank's own frame (all its launches), without the gather
     launches = ctx.launch_count - launches0
     clk = clocks.stop()
+    # second timed pass for the per-stage breakdown: the headline pass overlaps the kernels of two
+    # sub-frames on two streams, so its launches cannot be timed one by one; here the same frames run as
+    # one sub-frame with a CUDA event between consecutive launches
+    if path and args.variant in (0, 4):
+        os.environ["RTB200_WAVE_SPLIT"] = "1"
+        for _ in range(max(3, min(args.steps, 10))):
+            with torch.cuda.stream(stream):
+                flush.zero_()
+            render()
+            try:
+                stage_ms.append(ctx.last_stage_ms())
+            except g.RtError:
+                break
+        del os.environ["RTB200_WAVE_SPLIT"]
     barrier(world)
     total_ms = max_over_ranks(float(np.sum(step_ms)), world)
+    rank_kernel_ms = [float(np.mean(kernel_ms))]
+    if world > 1:  # load balance of the tile split: every rank's own mean frame time
+        t = torch.tensor(rank_kernel_ms, dtype=torch.float64, device="cuda")
+        allt = [torch.zeros_like(t) for _ in range(world)]
+        dist.all_gather(allt, t)
+        rank_kernel_ms = [float(x.item()) for x in allt]
     value = seg_per_frame * args.steps / (total_ms * 1e-3) / 1e6
 
     # ---- e2e: host buffers -> C ABI -> host image on rank 0, wall clock, every step
@@ -347,7 +376,21 @@ def run_b200(args, wl, world, rank, local):
     e2e_total = max_over_ranks(float(np.sum(e2e_ms)), world)
     e2e_value = seg_per_frame * args.steps / (e2e_total * 1e-3) / 1e6
 
+    # ---- N > 1: the assembled frame on rank 0 must equal rank 0's own render of the whole frame
+    assembled_ok = None
+    if world > 1 and rank == 0:
+        got = host_img.copy()
+        if path:
+            cr.render_frame(ps.camera, mode=abi.MODE_PATH, spp=wl["spp"], max_depth=wl["depth"], base_seed=1,
+                            outputs=abi.OUT_ACCUM | abi.OUT_COMPOSITE, traversal=trav, variant=args.variant)
+        else:
+            cr.render_frame(ps.camera, outputs=abi.OUT_ACCUM | abi.OUT_COMPOSITE, traversal=trav)
+        assembled_ok = bool(np.array_equal(got, ctx.read_composite()))
+    if peer is not None:
+        peer.close()  # ranks != 0 unmap rank 0's frame before anybody frees anything
+    barrier(world)
     if rank != 0:
+        ctx.close()
         return
     # ---- roofline of the dominant kernel: algorithmic bytes per launch / mean launch time (rank 0)
     n_lights = len(scene.lights)
@@ -358,8 +401,8 @@ def run_b200(args, wl, world, rank, local):
     shade_bytes_per_ray = 128 * H + 52 * n_lights * H + out_bytes_per_pixel * my_pixels / seg  # 128 H + 52 L H + O
     bytes_per_ray = trav_bytes_per_ray + shade_bytes_per_ray
     peak, peak_src = measured_peaks()
-    wave = bool(stage_ms)
-    if wave:
+    wave = path and args.variant in (0, 4) and ctx.last_traversal != abi.TRAVERSAL_LITERAL
+    if wave and stage_ms:
         # streaming wavefront engine: the dominant kernel is wv_extend (closest hit of every ray segment);
         # its launches are timed by CUDA events between consecutive launches on the context's stream
         ext_ms = float(np.mean([x["extend"] for x in stage_ms]))
@@ -367,16 +410,11 @@ def run_b200(args, wl, world, rank, local):
         stages["launches_per_step"] = stage_ms[-1]["launches"]
         kernel, mean_ms, kernel_bytes_per_ray = "wv_extend", ext_ms, trav_bytes_per_ray
     else:
-        # time the kernel alone once more for the roofline when the step also holds the gather
-        if gather is not None:
-            flush.zero_()
-            torch.cuda.synchronize()
-            render()
-            mean_ms = ctx.last_kernel_ms
-        else:
-            mean_ms = float(np.mean(kernel_ms))
+        mean_ms = float(np.mean(kernel_ms))
         stages = None
-        kernel, kernel_bytes_per_ray = ("rt_path_trace" if path else "rt_trace_shade"), bytes_per_ray
+        kernel = ("wave engine frame: wv_generate + wv_extend + wv_shade + wv_resolve on overlapped sub-frame streams"
+                  if wave else ("rt_path_trace" if path else "rt_trace_shade"))
+        kernel_bytes_per_ray = bytes_per_ray
     achieved = kernel_bytes_per_ray * seg_per_frame_rank / (mean_ms * 1e-3) / 1e9
     # measured denominators of the traversal itself: random independent 32-byte sector gathers
     # (the node-fetch instruction) from an L1-resident, an L2-resident and an HBM-resident set
@@ -398,14 +436,18 @@ def run_b200(args, wl, world, rank, local):
                               ("megakernel" if path else "fused trace+shade kernel")), "literal_fallback_rays": cnt["literal_fallbacks"],
                    "upload_relayout_build_ms": ctx.last_build_ms,
                    "l2": "flushed between timed steps (512 MiB memset)", "tiles_per_rank": my_tiles,
-                   "parallelism": "128x128 tile split x%d (tile i -> rank i %% N), scene replicated, NCCL gather of "
-                                  "the composite to rank 0 inside the timed step" % world if world > 1 else "single GPU"},
+                   "parallelism": ("64x64 tile split x%d (tile i -> rank i %% N), scene replicated, %s inside the timed step"
+                                   % (world, "composite pixels stored into rank 0's frame by the render kernels (P2P over NVLink, "
+                                             "CUDA IPC) + 4-byte NCCL all-reduce as barrier" if peer is not None else
+                                      "NCCL gather of the composite tiles to rank 0")) if world > 1 else "single GPU"},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": None, "kernel": kernel, "peak_source": peak_src,
                      "bytes_per_ray": kernel_bytes_per_ray, "step_bytes_per_ray": bytes_per_ray,
                      "box_tests_per_ray": V, "tri_tests_per_ray": T, "kernel_ms": mean_ms,
                      "kernel_share_of_step": mean_ms / (total_ms / args.steps) if world == 1 else None,
                      "stage_ms": stages,
+                     "stage_ms_note": "second timed pass, one sub-frame, CUDA events between consecutive launches; the headline "
+                                      "pass overlaps two sub-frames on two streams" if stages else None,
                      "gather_gbs_measured": gather_bw,
                      "fetched_bytes_per_ray": fetched_per_ray,
                      "fetched_gbs": fetched_per_ray * seg_per_frame_rank / (mean_ms * 1e-3) / 1e9,
@@ -417,7 +459,8 @@ def run_b200(args, wl, world, rank, local):
                              "(one 32-B sector per lane per cycle for divergent gathers), see frac_of_l1_gather"},
         "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": h2d_bytes,
                 "d2h_bytes_per_step": int(host_img.nbytes), "ms_per_step": e2e_total / args.steps},
-        "gpu_launches": int(launches), "clocks": clk,
+        "gpu_launches": int(launches), "clocks": clk, "rank_frame_ms": rank_kernel_ms,
+        "assembled_frame_bit_identical_to_single_gpu": assembled_ok,
     }
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = {k: v for k, v in cpu_baseline_sample(scene, wl, args.cpu_seconds).items()

@@ -49,12 +49,13 @@ for _name, (_dt, _sz) in SIZES.items():
 
 # RaytracerConfig, shared/src/lib.rs:18-35
 TILE_SIZE = 128
+SPLIT_TILE = 64  # include/rtb200.h RT_SPLIT_TILE: unit of the multi-GPU screen split
 THREAD_GROUP_SIZE = (16, 16)
 MIN_RAY_DISTANCE = np.float32(0.00001)
 MAX_TRIANGLES_PER_BUFFER = 8388608
 INVALID_INDEX = 0xFFFFFFFF
 
-OUT_ACCUM, OUT_HITS, OUT_CHANNELS, OUT_COMPOSITE = 1, 2, 4, 8
+OUT_ACCUM, OUT_HITS, OUT_CHANNELS, OUT_COMPOSITE, OUT_PEER = 1, 2, 4, 8, 16
 MODE_LEGACY, MODE_WAVEFRONT0, MODE_PATH = 0, 1, 2
 TRAVERSAL_AUTO, TRAVERSAL_LITERAL, TRAVERSAL_ORDERED, TRAVERSAL_REBUILT = 0, 1, 2, 3
 BVH_AUTO, BVH_STANDARD, BVH_CHUNKED, BVH_SMALL_LEAF = 0, 1, 2, 3

@@ -114,6 +114,9 @@ struct RtContext {
     DevBuf<float4> wv_state[2], wv_lbuf;
     DevBuf<uint2> wv_hit[2];
     DevBuf<WvCtrl> wv_ctrl;
+    std::vector<cudaStream_t> wv_streams; // extra streams of the sub-frames (launch_wave)
+    std::vector<cudaEvent_t> wv_join;
+    cudaEvent_t wv_fork = nullptr;
     std::vector<cudaEvent_t> wv_events;  // one before the first and one after every launch of the last wave frame
     std::vector<int> wv_event_stage;     // stage of the launch that ends at event i+1: 0 generate, 1 extend, 2 shade, 3 resolve
 
@@ -124,6 +127,9 @@ struct RtContext {
     DevBuf<uchar4> chan[3];
     DevBuf<uchar4> composite;
     uint32_t tiles_x = 0, tiles_y = 0, tiles_per_frame = 0, current_tile = 0;
+    uchar4* peer_composite = nullptr; // rank 0's composite through peer memory (fused multi-GPU epilogue)
+    bool peer_is_ipc = false;
+    uint32_t stiles_x = 0, stiles_y = 0; // RT_SPLIT_TILE^2 split tiles of the fused frame / multi-GPU split
     bool needs_recompute = true, is_progressive = false;
 };
 
@@ -298,9 +304,9 @@ __global__ void tile_copy(T* __restrict__ frame, T* __restrict__ compact, uint32
     uint32_t tile_local = blockIdx.y;
     uint32_t tile = phase + tile_local * stride;
     if (tile >= n_tiles_total) return;
-    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; // 0..16383
-    uint32_t x = (tile % tiles_x) * RT_TILE_SIZE + (i & 127u), y = (tile / tiles_x) * RT_TILE_SIZE + (i >> 7);
-    size_t ci = (size_t)tile_local * 16384u + i;
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; // 0..4095
+    uint32_t x = (tile % tiles_x) * RT_SPLIT_TILE + (i & 63u), y = (tile / tiles_x) * RT_SPLIT_TILE + (i >> 6);
+    size_t ci = (size_t)tile_local * 4096u + i;
     if (x < width && y < height) {
         if (PACK) compact[ci] = frame[(size_t)y * width + x];
         else frame[(size_t)y * width + x] = compact[ci];
@@ -349,10 +355,16 @@ int rt_create(int device, RtContext** out) {
 void rt_destroy(RtContext* c) {
     if (!c) return;
     cudaSetDevice(c->device);
-    if (c->stream) { cudaStreamSynchronize(c->stream); cudaStreamDestroy(c->stream); }
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    for (cudaStream_t st : c->wv_streams) cudaStreamSynchronize(st);
+    rt_close_peer_frame(c); // before the stream it synchronises goes away
+    for (cudaStream_t st : c->wv_streams) cudaStreamDestroy(st);
+    if (c->stream) cudaStreamDestroy(c->stream);
     if (c->ev0) cudaEventDestroy(c->ev0);
     if (c->ev1) cudaEventDestroy(c->ev1);
     for (cudaEvent_t e : c->wv_events) cudaEventDestroy(e);
+    for (cudaEvent_t e : c->wv_join) cudaEventDestroy(e);
+    if (c->wv_fork) cudaEventDestroy(c->wv_fork);
     delete c;
 }
 
@@ -373,6 +385,7 @@ int rt_resize(RtContext* c, uint32_t w, uint32_t h) {
     for (int i = 0; i < 3; i++) CK(c, cudaMemsetAsync(c->chan[i].ptr, 0, n * 4, c->stream));
     // ProgressiveState::resize, src/renderer.rs:838-848
     rt_tile_count(w, h, RT_TILE_SIZE, &c->tiles_x, &c->tiles_y);
+    rt_tile_count(w, h, RT_SPLIT_TILE, &c->stiles_x, &c->stiles_y);
     c->tiles_per_frame = rt_tiles_per_frame(c->tiles_x * c->tiles_y);
     c->needs_recompute = true; c->current_tile = 0; c->is_progressive = false;
     return RT_OK;
@@ -817,6 +830,13 @@ int launch_wavefront(RtContext* c, KParams k, uint32_t traversal) {
 // EXTENSION path tracing, streaming wavefront engine (rt_wave.cuh): all samples of a wave in
 // flight at once; per wave one generate, per depth one extend + one shade, one resolve.
 // Queue lengths stay on the device (no host sync inside the frame).
+__global__ void wv_publish(const WvCtrl* ctrl, int n_sub, unsigned long long* dcounters, int count) {
+    unsigned long long seg = 0, cc[4] = {0, 0, 0, 0};
+    for (int i = 0; i < n_sub; i++) { seg += ctrl[i].segments; for (int j = 0; j < 4; j++) cc[j] += ctrl[i].c[j]; }
+    dcounters[6] = seg; // rt_last_segments
+    if (count) { dcounters[0] = cc[0]; dcounters[1] = cc[1]; dcounters[2] = seg; dcounters[3] = cc[2]; dcounters[4] = cc[3]; }
+}
+
 int launch_wave(RtContext* c, KParams k, uint32_t traversal) {
     if (k.n_work == 0) return RT_OK;
     int policy = pick_policy(c, k, traversal);
@@ -826,31 +846,41 @@ int launch_wave(RtContext* c, KParams k, uint32_t traversal) {
     uint32_t spp_wave = (uint32_t)(cap / k.n_work);
     if (spp_wave < 1u) spp_wave = 1u;
     if (spp_wave > k.spp) spp_wave = k.spp;
+    // Sub-frames: the context's tiles are dealt round-robin to n_sub independent wavefronts on their own
+    // streams.  Every per-depth extend launch ends in a tail (a few long rays keep a handful of warps busy
+    // for ~0.1-0.2 ms); with two sub-frames the other one's kernels fill the SMs meanwhile.  Worth it when
+    // Measured on C3: +3 % at 35 M paths on one GPU, more when the context's share of the frame is small
+    // (multi-GPU tile split); 3 or 4 sub-frames are no better than 2.
+    const uint32_t my_tiles = k.n_work >> 12;
+    uint32_t n_sub = my_tiles >= 2u ? 2u : 1u;
+    if (const char* e = getenv("RTB200_WAVE_SPLIT")) { int v = atoi(e); if (v >= 1 && v <= 4) n_sub = (uint32_t)v; }
+    if (n_sub > my_tiles) n_sub = my_tiles;
     const size_t P = (size_t)k.n_work * spp_wave;
     if (c->wv_state[0].reserve(P * 4) < 0 || c->wv_state[1].reserve(P * 4) < 0 || c->wv_hit[0].reserve(P) < 0 ||
-        c->wv_hit[1].reserve(P) < 0 || c->wv_lbuf.reserve(P) < 0 || c->wv_ctrl.reserve(1) < 0)
+        c->wv_hit[1].reserve(P) < 0 || c->wv_lbuf.reserve(P) < 0 || c->wv_ctrl.reserve(4) < 0)
         return fail(c, RT_ERR_CUDA, "wave engine cudaMalloc failed for %zu paths", P);
-    WvBuffers w;
-    w.state[0] = c->wv_state[0].ptr; w.state[1] = c->wv_state[1].ptr;
-    w.hit[0] = c->wv_hit[0].ptr; w.hit[1] = c->wv_hit[1].ptr;
-    w.lbuf = c->wv_lbuf.ptr; w.ctrl = c->wv_ctrl.ptr;
+    while (c->wv_streams.size() + 1 < n_sub) {
+        cudaStream_t st; cudaEvent_t ev;
+        CK(c, cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+        CK(c, cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+        c->wv_streams.push_back(st); c->wv_join.push_back(ev);
+    }
+    if (!c->wv_fork) CK(c, cudaEventCreateWithFlags(&c->wv_fork, cudaEventDisableTiming));
     const bool count = k.counters != nullptr;
     int per_sm = 0, sms = 0;
     const void* fn = policy == 2 ? (const void*)wv_extend<2, false> : (const void*)wv_extend<1, false>;
     CK(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, 256, 0));
     CK(c, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device));
-    uint32_t ext_blocks = (uint32_t)(per_sm > 0 ? per_sm : 1) * (uint32_t)sms;
-    uint32_t full_blocks = (uint32_t)((P + 255) / 256);
-    if (ext_blocks > full_blocks) ext_blocks = full_blocks;
-    uint32_t stream_blocks = (uint32_t)sms * 8u;
-    if (stream_blocks > full_blocks) stream_blocks = full_blocks;
     CK(c, cudaEventRecord(c->ev0, c->stream));
-    CK(c, cudaMemsetAsync(c->wv_ctrl.ptr, 0, sizeof(WvCtrl), c->stream));
+    CK(c, cudaMemsetAsync(c->wv_ctrl.ptr, 0, 4 * sizeof(WvCtrl), c->stream));
+    if (n_sub > 1) CK(c, cudaEventRecord(c->wv_fork, c->stream));
     const uint32_t s_end = k.first_sample + k.spp;
-    // per-stage timing: an event between consecutive launches (rt_last_stage_ms)
+    // per-stage timing (single sub-frame only): an event between consecutive launches (rt_last_stage_ms)
     size_t n_ev = 0;
     c->wv_event_stage.clear();
+    const bool stage_timing = n_sub == 1;
     auto mark = [&](int stage) -> int {
+        if (!stage_timing) return 0;
         if (n_ev >= c->wv_events.size()) {
             cudaEvent_t e;
             if (cudaEventCreate(&e) != cudaSuccess) return -1;
@@ -861,35 +891,53 @@ int launch_wave(RtContext* c, KParams k, uint32_t traversal) {
         return 0;
     };
     if (mark(-1)) return fail(c, RT_ERR_CUDA, "wave engine: event record failed");
-    for (uint32_t s0 = k.first_sample; s0 < s_end; s0 += spp_wave) {
-        w.s0 = s0; w.spp_wave = s_end - s0 < spp_wave ? s_end - s0 : spp_wave;
-        w.first_wave = s0 == k.first_sample; w.last_wave = s0 + w.spp_wave == s_end;
-        if (!w.first_wave) CK(c, cudaMemsetAsync(c->wv_ctrl.ptr, 0, 16, c->stream)); // n[0], n[1], head
-        if (!w.first_wave) mark(-1);
-        wv_generate<<<stream_blocks, 256, 0, c->stream>>>(k, w);
-        mark(0);
-        for (uint32_t d = 0; d <= k.path_max_depth; d++) {
-            const int qi = (int)(d & 1u);
-            if (policy == 2) { if (count) wv_extend<2, true><<<ext_blocks, 256, 0, c->stream>>>(k, w, qi); else wv_extend<2, false><<<ext_blocks, 256, 0, c->stream>>>(k, w, qi); }
-            else { if (count) wv_extend<1, true><<<ext_blocks, 256, 0, c->stream>>>(k, w, qi); else wv_extend<1, false><<<ext_blocks, 256, 0, c->stream>>>(k, w, qi); }
-            mark(1);
-            if (policy == 2) { if (count) wv_shade<2, true><<<stream_blocks, 256, 0, c->stream>>>(k, w, qi); else wv_shade<2, false><<<stream_blocks, 256, 0, c->stream>>>(k, w, qi); }
-            else { if (count) wv_shade<1, true><<<stream_blocks, 256, 0, c->stream>>>(k, w, qi); else wv_shade<1, false><<<stream_blocks, 256, 0, c->stream>>>(k, w, qi); }
-            mark(2);
+    size_t path_base = 0;
+    for (uint32_t sub = 0; sub < n_sub; sub++) {
+        cudaStream_t st = sub == 0 ? c->stream : c->wv_streams[sub - 1];
+        if (sub) CK(c, cudaStreamWaitEvent(st, c->wv_fork, 0));
+        KParams ks = k;
+        ks.tile_stride = k.tile_stride * n_sub;
+        ks.tile_phase = k.tile_phase + sub * k.tile_stride;
+        const uint32_t tiles_s = (my_tiles - sub + n_sub - 1) / n_sub; // local tiles sub, sub + n_sub, ...
+        ks.n_work = tiles_s * 4096u;
+        const size_t Ps = (size_t)ks.n_work * spp_wave;
+        WvBuffers w;
+        w.state[0] = c->wv_state[0].ptr + path_base * 4; w.state[1] = c->wv_state[1].ptr + path_base * 4;
+        w.hit[0] = c->wv_hit[0].ptr + path_base; w.hit[1] = c->wv_hit[1].ptr + path_base;
+        w.lbuf = c->wv_lbuf.ptr + path_base; w.ctrl = c->wv_ctrl.ptr + sub;
+        path_base += Ps;
+        uint32_t ext_blocks = (uint32_t)(per_sm > 0 ? per_sm : 1) * (uint32_t)sms;
+        uint32_t full_blocks = (uint32_t)((Ps + 255) / 256);
+        if (ext_blocks > full_blocks) ext_blocks = full_blocks;
+        uint32_t stream_blocks = (uint32_t)sms * 8u;
+        if (stream_blocks > full_blocks) stream_blocks = full_blocks;
+        for (uint32_t s0 = k.first_sample; s0 < s_end; s0 += spp_wave) {
+            w.s0 = s0; w.spp_wave = s_end - s0 < spp_wave ? s_end - s0 : spp_wave;
+            w.first_wave = s0 == k.first_sample; w.last_wave = s0 + w.spp_wave == s_end;
+            if (!w.first_wave) CK(c, cudaMemsetAsync(w.ctrl, 0, 16, st)); // n[0], n[1], head
+            if (!w.first_wave) mark(-1);
+            wv_generate<<<stream_blocks, 256, 0, st>>>(ks, w);
+            mark(0);
+            for (uint32_t d = 0; d <= k.path_max_depth; d++) {
+                const int qi = (int)(d & 1u);
+                if (policy == 2) { if (count) wv_extend<2, true><<<ext_blocks, 256, 0, st>>>(ks, w, qi); else wv_extend<2, false><<<ext_blocks, 256, 0, st>>>(ks, w, qi); }
+                else { if (count) wv_extend<1, true><<<ext_blocks, 256, 0, st>>>(ks, w, qi); else wv_extend<1, false><<<ext_blocks, 256, 0, st>>>(ks, w, qi); }
+                mark(1);
+                if (policy == 2) { if (count) wv_shade<2, true><<<stream_blocks, 256, 0, st>>>(ks, w, qi); else wv_shade<2, false><<<stream_blocks, 256, 0, st>>>(ks, w, qi); }
+                else { if (count) wv_shade<1, true><<<stream_blocks, 256, 0, st>>>(ks, w, qi); else wv_shade<1, false><<<stream_blocks, 256, 0, st>>>(ks, w, qi); }
+                mark(2);
+                c->launches += 2;
+            }
+            wv_resolve<<<stream_blocks, 256, 0, st>>>(ks, w);
+            mark(3);
             c->launches += 2;
         }
-        wv_resolve<<<stream_blocks, 256, 0, c->stream>>>(k, w);
-        mark(3);
-        c->launches += 2;
+        if (sub) { CK(c, cudaEventRecord(c->wv_join[sub - 1], st)); CK(c, cudaStreamWaitEvent(c->stream, c->wv_join[sub - 1], 0)); }
     }
     CK(c, cudaGetLastError());
     // publish the segment count (and instrumentation) where rt_last_segments / rt_read_counters look
-    CK(c, cudaMemcpyAsync(c->dcounters.ptr + 6, &c->wv_ctrl.ptr->segments, 8, cudaMemcpyDeviceToDevice, c->stream));
-    if (count) {
-        CK(c, cudaMemcpyAsync(c->dcounters.ptr + 0, &c->wv_ctrl.ptr->c[0], 16, cudaMemcpyDeviceToDevice, c->stream)); // box, tri
-        CK(c, cudaMemcpyAsync(c->dcounters.ptr + 2, &c->wv_ctrl.ptr->segments, 8, cudaMemcpyDeviceToDevice, c->stream));
-        CK(c, cudaMemcpyAsync(c->dcounters.ptr + 3, &c->wv_ctrl.ptr->c[2], 16, cudaMemcpyDeviceToDevice, c->stream)); // shaded, fallbacks
-    }
+    wv_publish<<<1, 1, 0, c->stream>>>(c->wv_ctrl.ptr, (int)n_sub, c->dcounters.ptr, count ? 1 : 0);
+    c->launches++;
     CK(c, cudaEventRecord(c->ev1, c->stream));
     c->timed = true;
     c->last_traversal = policy == 2 ? RT_TRAVERSAL_REBUILT : RT_TRAVERSAL_ORDERED;
@@ -981,11 +1029,15 @@ int rt_render_frame(RtContext* c, const RtCamera* cam, const RtFrameParams* fp) 
     k.width = c->width; k.height = c->height; k.res_x = (float)c->width; k.res_y = (float)c->height;
     fill_camera(k, *cam);
     k.use_tiles = 1;
-    k.tiles_x = c->tiles_x; k.n_tiles_total = c->tiles_x * c->tiles_y;
+    k.tiles_x = c->stiles_x; k.n_tiles_total = c->stiles_x * c->stiles_y;
     k.tile_stride = fp->tile_stride ? fp->tile_stride : 1u;
     k.tile_phase = fp->tile_stride ? fp->tile_phase : 0u;
     if (k.tile_phase >= k.tile_stride) return fail(c, RT_ERR_INVALID_ARGUMENT, "tile_phase >= tile_stride");
     k.mode = fp->mode; k.outputs = fp->outputs; k.channel = 0xFFu;
+    if (fp->outputs & RT_OUT_PEER) { // fused multi-GPU epilogue: composite stores go to rank 0's frame
+        if (!c->peer_composite) return fail(c, RT_ERR_NOT_READY, "RT_OUT_PEER without rt_open_peer_frame / rt_set_peer_frame");
+        k.composite = c->peer_composite;
+    }
     k.cur_depth = 0; k.max_depth = 4; // PushConstants::new, shared/src/lib.rs:1088
     k.reset_accum = fp->reset_accum;
     k.triangles_per_buffer = RT_MAX_TRIANGLES_PER_BUFFER;
@@ -993,7 +1045,7 @@ int rt_render_frame(RtContext* c, const RtCamera* cam, const RtFrameParams* fp) 
     uint32_t my_tiles = k.n_tiles_total > k.tile_phase ? (k.n_tiles_total - k.tile_phase + k.tile_stride - 1) / k.tile_stride : 0;
     if (fp->mode == RT_MODE_PATH) {
         k.spp = fp->spp; k.first_sample = fp->first_sample; k.path_max_depth = fp->max_depth; k.base_seed = fp->base_seed;
-        k.n_work = my_tiles * 16384u;
+        k.n_work = my_tiles * 4096u;
         k.seg_counter = c->dcounters.ptr + 6;
         k.work_counter = reinterpret_cast<unsigned int*>(c->dcounters.ptr + 7);
         CK(c, cudaMemsetAsync(c->dcounters.ptr + 6, 0, 2 * sizeof(unsigned long long), c->stream));
@@ -1012,7 +1064,7 @@ int rt_render_frame(RtContext* c, const RtCamera* cam, const RtFrameParams* fp) 
         }
         return launch_path(c, k, fp->traversal, fp->_reserved[0]);
     }
-    return launch(c, k, my_tiles * 64u, fp->traversal);
+    return launch(c, k, my_tiles * 16u, fp->traversal);
 }
 
 int rt_run_compute(RtContext* c, const RtCamera* cam, int needs_recompute) {
@@ -1117,16 +1169,16 @@ static int tile_copy_launch(RtContext* c, uint32_t what, uint32_t stride, uint32
     if (c->width == 0) return fail(c, RT_ERR_NOT_READY, "rt_resize has not been called");
     if (stride == 0 || phase >= stride || what > 1) return fail(c, RT_ERR_INVALID_ARGUMENT, "tile copy: bad stride/phase/what");
     CK(c, cudaSetDevice(c->device));
-    uint32_t total = c->tiles_x * c->tiles_y;
+    uint32_t total = c->stiles_x * c->stiles_y;
     uint32_t mine = total > phase ? (total - phase + stride - 1) / stride : 0;
     if (!mine) return RT_OK;
-    dim3 grid(16384 / 256, mine);
+    dim3 grid(4096 / 256, mine);
     if (what == 0) {
-        if (pack) tile_copy<uchar4, true><<<grid, 256, 0, c->stream>>>(c->composite.ptr, (uchar4*)compact, c->width, c->height, c->tiles_x, total, stride, phase);
-        else tile_copy<uchar4, false><<<grid, 256, 0, c->stream>>>(c->composite.ptr, (uchar4*)compact, c->width, c->height, c->tiles_x, total, stride, phase);
+        if (pack) tile_copy<uchar4, true><<<grid, 256, 0, c->stream>>>(c->composite.ptr, (uchar4*)compact, c->width, c->height, c->stiles_x, total, stride, phase);
+        else tile_copy<uchar4, false><<<grid, 256, 0, c->stream>>>(c->composite.ptr, (uchar4*)compact, c->width, c->height, c->stiles_x, total, stride, phase);
     } else {
-        if (pack) tile_copy<float4, true><<<grid, 256, 0, c->stream>>>(c->accum.ptr, (float4*)compact, c->width, c->height, c->tiles_x, total, stride, phase);
-        else tile_copy<float4, false><<<grid, 256, 0, c->stream>>>(c->accum.ptr, (float4*)compact, c->width, c->height, c->tiles_x, total, stride, phase);
+        if (pack) tile_copy<float4, true><<<grid, 256, 0, c->stream>>>(c->accum.ptr, (float4*)compact, c->width, c->height, c->stiles_x, total, stride, phase);
+        else tile_copy<float4, false><<<grid, 256, 0, c->stream>>>(c->accum.ptr, (float4*)compact, c->width, c->height, c->stiles_x, total, stride, phase);
     }
     CK(c, cudaGetLastError());
     c->launches++;
@@ -1137,6 +1189,40 @@ int rt_pack_tiles(RtContext* c, uint32_t what, uint32_t stride, uint32_t phase, 
 }
 int rt_unpack_tiles(RtContext* c, uint32_t what, uint32_t stride, uint32_t phase, const void* src_device) {
     return tile_copy_launch(c, what, stride, phase, const_cast<void*>(src_device), false);
+}
+
+int rt_export_frame_handle(RtContext* c, void* out_handle64) {
+    if (!c || !out_handle64) return RT_ERR_INVALID_ARGUMENT;
+    if (c->width == 0) return fail(c, RT_ERR_NOT_READY, "rt_resize has not been called");
+    CK(c, cudaSetDevice(c->device));
+    cudaIpcMemHandle_t h;
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "CUDA IPC handle is 64 bytes");
+    CK(c, cudaIpcGetMemHandle(&h, c->composite.ptr));
+    memcpy(out_handle64, &h, 64);
+    return RT_OK;
+}
+int rt_close_peer_frame(RtContext* c) {
+    if (!c) return RT_ERR_INVALID_ARGUMENT;
+    if (c->peer_composite && c->peer_is_ipc) { cudaSetDevice(c->device); cudaStreamSynchronize(c->stream); cudaIpcCloseMemHandle(c->peer_composite); }
+    c->peer_composite = nullptr; c->peer_is_ipc = false;
+    return RT_OK;
+}
+int rt_open_peer_frame(RtContext* c, const void* handle64) {
+    if (!c || !handle64) return RT_ERR_INVALID_ARGUMENT;
+    CK(c, cudaSetDevice(c->device));
+    rt_close_peer_frame(c);
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle64, 64);
+    void* p = nullptr;
+    CK(c, cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+    c->peer_composite = (uchar4*)p; c->peer_is_ipc = true;
+    return RT_OK;
+}
+int rt_set_peer_frame(RtContext* c, void* device_composite) {
+    if (!c || !device_composite) return RT_ERR_INVALID_ARGUMENT;
+    rt_close_peer_frame(c);
+    c->peer_composite = (uchar4*)device_composite; c->peer_is_ipc = false;
+    return RT_OK;
 }
 
 // ray segments traced by the last RT_MODE_PATH launch (waits for it)

@@ -37,7 +37,7 @@ struct KParams {
     float fov_scale;          // tan(fov*0.5*PI/180), evaluated on the host (glibc tanf)
     // work: pixel rectangle of one dispatch, or tiles of a fused frame
     uint32_t rect_x0, rect_y0, rect_w, rect_h;
-    uint32_t tiles_x, n_tiles_total, tile_stride, tile_phase; // fused frame: 128x128 tile split
+    uint32_t tiles_x, n_tiles_total, tile_stride, tile_phase; // fused frame: RT_SPLIT_TILE^2 tile split
     uint32_t use_tiles;       // 1: fused frame over tiles; 0: single rect
     uint32_t mode;            // RT_MODE_*
     uint32_t outputs;         // RT_OUT_*
@@ -76,7 +76,7 @@ struct KParams {
     unsigned long long* counters;
     // RT_MODE_PATH (EXTENSION, SPEC.md)
     uint32_t spp, first_sample, path_max_depth, base_seed;
-    uint32_t n_work;                 // pixels in this launch's work list (16384 per assigned tile)
+    uint32_t n_work;                 // pixels in this launch's work list (4096 per assigned split tile)
     unsigned int* work_counter;      // persistent-thread work fetch
     unsigned long long* seg_counter; // ray segments traced (the Mrays/s numerator)
     uint32_t wf_rebuilt;             // wavefront: hit slots index btris (REBUILT) rather than wtris
@@ -562,20 +562,21 @@ __device__ __forceinline__ V3 shade_hit_m(const KParams& p, const Hit& h, const 
 // ----------------------------------------------------------------- the kernel
 // Work decomposition: a 256-thread block covers a 16x16 pixel block; each warp an
 // 8x4 sub-block (coherent primary rays).  In a fused frame the block list
-// enumerates the 128x128 reference tiles (src/compute.rs:194-209) assigned to this
-// context (tile i with i % tile_stride == tile_phase), 64 blocks per tile.
+// enumerates the RT_SPLIT_TILE^2 split tiles (numbered like the reference's 128x128 tiles,
+// src/compute.rs:194-209) assigned to this context (tile i with i % tile_stride ==
+// tile_phase), 16 blocks per tile.
 __device__ __forceinline__ bool pixel_of_thread(const KParams& p, uint32_t* px, uint32_t* py) {
     uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
     uint32_t lx = (warp & 1u) * 8u + (lane & 7u), ly = (warp >> 1) * 4u + (lane >> 3);
     uint32_t x0, y0, w, h;
     uint32_t blk = blockIdx.x;
     if (p.use_tiles) {
-        uint32_t tile_local = blk >> 6, sub = blk & 63u;
+        uint32_t tile_local = blk >> 4, sub = blk & 15u; // 16 blocks of 16x16 pixels per 64x64 split tile
         uint32_t tile = p.tile_phase + tile_local * p.tile_stride;
         if (tile >= p.n_tiles_total) return false;
         uint32_t tx = tile % p.tiles_x, ty = tile / p.tiles_x;
-        x0 = tx * RT_TILE_SIZE; y0 = ty * RT_TILE_SIZE; w = RT_TILE_SIZE; h = RT_TILE_SIZE;
-        lx += (sub & 7u) * 16u; ly += (sub >> 3) * 16u;
+        x0 = tx * RT_SPLIT_TILE; y0 = ty * RT_SPLIT_TILE; w = RT_SPLIT_TILE; h = RT_SPLIT_TILE;
+        lx += (sub & 3u) * 16u; ly += (sub >> 2) * 16u;
     } else {
         uint32_t bw = (p.rect_w + 15u) >> 4;
         x0 = p.rect_x0; y0 = p.rect_y0; w = p.rect_w; h = p.rect_h;
@@ -647,6 +648,7 @@ __global__ void __launch_bounds__(256) rt_trace_shade(const __grid_constant__ KP
         uint4 rec = make_uint4(h.kind, h.prim, __float_as_uint(h.t), h.material_id);
         reinterpret_cast<uint4*>(p.hits)[pix] = rec;
     }
+    if (p.outputs & RT_OUT_PEER) __threadfence_system(); // the composite store went to another GPU's frame
     if (COUNT) {
         atomicAdd(p.counters + 0, (unsigned long long)h.n_box);
         atomicAdd(p.counters + 1, (unsigned long long)h.n_tri);
@@ -672,12 +674,12 @@ struct SimpleRng { // shader/src/wavefront.rs:46-72
 };
 
 __device__ __forceinline__ bool work_to_pixel(const KParams& p, uint32_t idx, uint32_t* px, uint32_t* py) {
-    uint32_t tile_local = idx >> 14, within = idx & 16383u;
+    uint32_t tile_local = idx >> 12, within = idx & 4095u; // 4096 work items per 64x64 split tile
     uint32_t tile = p.tile_phase + tile_local * p.tile_stride;
     uint32_t tx = tile % p.tiles_x, ty = tile / p.tiles_x;
-    uint32_t sub = within >> 5, l = within & 31u; // 8x4 pixel groups, 16 across x 32 down per tile
-    *px = tx * RT_TILE_SIZE + (sub & 15u) * 8u + (l & 7u);
-    *py = ty * RT_TILE_SIZE + (sub >> 4) * 4u + (l >> 3);
+    uint32_t sub = within >> 5, l = within & 31u; // 8x4 pixel groups, 8 across x 16 down per tile
+    *px = tx * RT_SPLIT_TILE + (sub & 7u) * 8u + (l & 7u);
+    *py = ty * RT_SPLIT_TILE + (sub >> 3) * 4u + (l >> 3);
     return *px < p.width && *py < p.height;
 }
 
@@ -794,6 +796,7 @@ __global__ void __launch_bounds__(256) rt_path_trace(const __grid_constant__ KPa
             } else new_sample = true;
         }
     }
+    if (p.outputs & RT_OUT_PEER) __threadfence_system(); // composite stores went to another GPU's frame
     // one atomic per warp for the segment count
     for (int o = 16; o; o >>= 1) n_seg += __shfl_xor_sync(full, n_seg, o);
     if (lane == 0u && n_seg) atomicAdd(p.seg_counter, (unsigned long long)n_seg);

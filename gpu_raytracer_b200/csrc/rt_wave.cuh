@@ -461,4 +461,5 @@ __global__ void __launch_bounds__(256) wv_resolve(const __grid_constant__ KParam
             p.composite[pix] = make_uchar4((unsigned char)unorm8(a.x / a.w), (unsigned char)unorm8(a.y / a.w),
                                            (unsigned char)unorm8(a.z / a.w), 255);
     }
+    if (p.outputs & RT_OUT_PEER) __threadfence_system(); // composite stores went to another GPU's frame
 }

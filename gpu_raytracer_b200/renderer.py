@@ -103,6 +103,26 @@ class Context:
                     literal_fallbacks=int(out[4]), s_phases=int(out[5]), s_ready_lanes=int(out[6]),
                     t_iterations=int(out[7]), t_active_lanes=int(out[8]))
 
+    # ---- fused multi-GPU epilogue (peer stores into rank 0's composite)
+    def export_frame_handle(self):
+        h = (C.c_uint8 * 64)()
+        self._ck(self.lib.rt_export_frame_handle(self.handle, h))
+        return bytes(h)
+
+    def open_peer_frame(self, handle64):
+        buf = (C.c_uint8 * 64).from_buffer_copy(handle64)
+        self._ck(self.lib.rt_open_peer_frame(self.handle, buf))
+
+    def set_peer_frame(self, device_ptr):
+        self._ck(self.lib.rt_set_peer_frame(self.handle, C.c_void_p(device_ptr)))
+
+    def close_peer_frame(self):
+        self._ck(self.lib.rt_close_peer_frame(self.handle))
+
+    @property
+    def device_composite(self):
+        return int(self.lib.rt_device_composite(self.handle))
+
     def probe_gather_bandwidth(self, footprint_bytes):
         """GB/s of random independent 32-byte sector loads over a footprint (traversal roofline denominators)."""
         out = C.c_float(0.0)

@@ -2,8 +2,9 @@
 to rank 0 (one process per GPU; torch.distributed is the plumbing).
 
 The reference is single-GPU but already iterates independent 128x128 tiles
-(src/compute.rs:157-162, 194-209); rank r of N renders the tiles i with
-i % N == r (RtFrameParams.tile_stride / tile_phase), the scene is replicated, and
+(src/compute.rs:157-162, 194-209); here the frame is cut the same way into 64x64
+split tiles (RT_SPLIT_TILE: finer, so 8 ranks get equal shares), rank r of N renders
+the tiles i with i % N == r (RtFrameParams.tile_stride / tile_phase), the scene is replicated, and
 nothing is exchanged while tracing.  The only collective is the final gather of
 the finished tiles to rank 0: every rank packs its tiles into a tile-major compact
 buffer (CUDA kernel rt_pack_tiles), `dist.gather` moves the equal-sized buffers over
@@ -13,7 +14,7 @@ import numpy as np
 
 from . import abi
 
-TILE = abi.TILE_SIZE
+TILE = abi.SPLIT_TILE
 WHAT_COMPOSITE, WHAT_ACCUM = 0, 1
 BYTES_PER_PIXEL = {WHAT_COMPOSITE: 4, WHAT_ACCUM: 16}
 
@@ -81,3 +82,28 @@ class TileGather:
         if self.rank == 0:
             for r in range(1, self.world):  # rank 0's own tiles are already in its frame
                 unpack(self.recv[r], r)
+
+
+class PeerFrame:
+    """Fused multi-GPU epilogue: ranks != 0 store their finished composite pixels straight into rank 0's
+    frame through CUDA-IPC peer memory (P2P stores over NVLink inside the render kernels, RT_OUT_PEER),
+    so there is no pack / gather / unpack.  `finish()` is the stream-ordered barrier (a 4-byte NCCL
+    all-reduce on the context's stream) after which rank 0 may read the assembled frame."""
+
+    def __init__(self, dist, torch, ctx, stream):
+        self.dist, self.torch, self.ctx, self.stream = dist, torch, ctx, stream
+        self.rank = dist.get_rank()
+        box = [ctx.export_frame_handle() if self.rank == 0 else None]
+        dist.broadcast_object_list(box, src=0)
+        if self.rank != 0:
+            ctx.open_peer_frame(box[0])
+        self.token = torch.zeros(1, dtype=torch.int32, device="cuda")
+        self.extra_outputs = abi.OUT_PEER if self.rank != 0 else 0
+
+    def finish(self):
+        with self.torch.cuda.stream(self.stream):
+            self.dist.all_reduce(self.token)
+
+    def close(self):
+        if self.rank != 0:
+            self.ctx.close_peer_frame()

@@ -45,7 +45,10 @@ enum {
     RT_OUT_ACCUM = 1u,     /* float4 accumulation buffer (rgb sum, sample count) */
     RT_OUT_HITS = 2u,      /* RtHitRecord per pixel (sample 0 / primary ray) */
     RT_OUT_CHANNELS = 4u,  /* the three Rgba8Unorm channel images (src/renderer.rs:452-475) */
-    RT_OUT_COMPOSITE = 8u  /* main_fs composite (R.x,G.y,B.z,1), shader/src/lib.rs:368-391 */
+    RT_OUT_COMPOSITE = 8u, /* main_fs composite (R.x,G.y,B.z,1), shader/src/lib.rs:368-391 */
+    RT_OUT_PEER = 16u      /* with RT_OUT_COMPOSITE: store the composite into the peer frame opened with
+                            * rt_open_peer_frame / rt_set_peer_frame (multi-GPU fused epilogue) instead of this
+                            * context's own composite buffer */
 };
 enum {
     RT_MODE_LEGACY = 0,    /* main_cs legacy branch, shader/src/lib.rs:59-79 (what src/main.rs runs) */
@@ -58,6 +61,12 @@ enum {
  * AUTO picks REBUILT for big-leaf trees, else ORDERED, else LITERAL. */
 enum { RT_TRAVERSAL_AUTO = 0, RT_TRAVERSAL_LITERAL = 1, RT_TRAVERSAL_ORDERED = 2, RT_TRAVERSAL_REBUILT = 3 };
 
+/* Unit of the multi-GPU screen split (RtFrameParams.tile_stride / tile_phase, rt_pack_tiles): the frame is
+ * cut into RT_SPLIT_TILE x RT_SPLIT_TILE pixel tiles numbered row-major, like the reference's own
+ * 128 x 128 progressive tiles (src/compute.rs:194-209) but finer, so that 8 ranks get equal shares of a
+ * 1080p frame (510 tiles instead of 135). */
+#define RT_SPLIT_TILE 64u
+
 /* Whole-frame parameters of the fused path (no reference analogue: replaces the
  * per-tile x per-channel loop of src/compute.rs:157-191 by one launch). */
 typedef struct RtFrameParams {
@@ -68,8 +77,8 @@ typedef struct RtFrameParams {
     uint32_t max_depth;    /* RT_MODE_PATH: max bounce depth */
     uint32_t base_seed;    /* frame_seed of sample s is base_seed + s */
     uint32_t reset_accum;  /* 1: overwrite accumulation; 0: add to it */
-    uint32_t tile_stride;  /* multi-GPU tile split: this context renders the */
-    uint32_t tile_phase;   /*   128x128 tiles i with i % tile_stride == tile_phase (0,0 = all) */
+    uint32_t tile_stride;  /* multi-GPU tile split: this context renders the RT_SPLIT_TILE^2 */
+    uint32_t tile_phase;   /*   tiles i with i % tile_stride == tile_phase (0,0 = all) */
     uint32_t traversal;    /* RT_TRAVERSAL_* */
     uint32_t _reserved[2]; /* [0]: RT_MODE_PATH engine (0 auto; tuning/tests: 1 megakernel, 2 per-sample
                             * wavefront, 3 state-machine megakernel, 4 streaming wavefront); [1]: 0 */
@@ -152,13 +161,24 @@ uint64_t rt_launch_count(const RtContext* ctx);
 /* which traversal the last launch used (RT_TRAVERSAL_LITERAL / _ORDERED / _REBUILT) */
 int rt_last_traversal(const RtContext* ctx);
 /* ---- multi-GPU tile split (no reference analogue: the reference is single-GPU;
- * it iterates the same independent 128x128 tiles, src/compute.rs:157-162, 194-209).
+ * it iterates independent 128x128 tiles the same way, src/compute.rs:157-162, 194-209).
  * Each context renders the tiles i % stride == phase (RtFrameParams); pack copies
- * them into a tile-major compact device buffer [local tile][128][128] for a
+ * them into a tile-major compact device buffer [local tile][RT_SPLIT_TILE][RT_SPLIT_TILE] for a
  * collective, unpack scatters such a buffer back into the full frame (rank 0).
  * what: 0 = composite rgba8, 1 = accumulation float4.  Asynchronous on rt_stream(). */
 int rt_pack_tiles(RtContext* ctx, uint32_t what, uint32_t stride, uint32_t phase, void* dst_device);
 int rt_unpack_tiles(RtContext* ctx, uint32_t what, uint32_t stride, uint32_t phase, const void* src_device);
+/* Fused multi-GPU epilogue (no reference analogue): instead of pack -> NCCL gather -> unpack, the kernels of
+ * ranks != 0 store their finished composite pixels straight into rank 0's frame through peer memory (P2P
+ * stores over NVLink; the frame is W*H*4 bytes in total).  Rank 0 exports its composite buffer as a 64-byte
+ * CUDA IPC handle (valid until rt_resize / rt_destroy); every other rank opens it once and then renders
+ * with RT_OUT_PEER.  A stream-ordered barrier (e.g. a 4-byte NCCL all-reduce on rt_stream()) after the frame
+ * orders rank 0's read-back after everybody's stores.  rt_set_peer_frame takes a raw device pointer instead
+ * (same-process contexts). */
+int rt_export_frame_handle(RtContext* ctx, void* out_handle64);
+int rt_open_peer_frame(RtContext* ctx, const void* handle64);
+int rt_set_peer_frame(RtContext* ctx, void* device_composite);
+int rt_close_peer_frame(RtContext* ctx);
 /* the context's cudaStream_t, so callers can order their own work (NCCL) after it */
 void* rt_stream(RtContext* ctx);
 /* EXTENSION: ray segments traced by the last RT_MODE_PATH launch (SPEC.md) */

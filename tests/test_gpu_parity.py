@@ -226,12 +226,23 @@ def test_path_default_scene_glass_metal_and_resume(default_ref, variant):
     compare_path(gpu, ref)
 
 
+@pytest.mark.parametrize("split", [1, 3, 4])
+def test_wave_engine_sub_frames(default_ref, monkeypatch, split):
+    """Wave engine with the context's tiles dealt to 1 / 3 / 4 concurrent sub-frames (own streams and
+    buffers): same frame bit for bit (the default for small frames is 2, which the other tests cover)."""
+    s, _ = default_ref
+    ref = ob.render_path(s, 320, 180, spp=3, max_depth=4, base_seed=6)
+    monkeypatch.setenv("RTB200_WAVE_SPLIT", str(split))
+    gpu = render_gpu_path(s, 320, 180, 3, 4, base_seed=6, variant=4)
+    compare_path(gpu, ref)
+
+
 def test_wave_engine_multi_wave(default_ref, monkeypatch):
     """Wave engine with a path budget so small that the 5 samples take 3 waves (2 + 2 + 1): the
     per-wave resolve must add the samples in the same order as one wave / the megakernel."""
     s, _ = default_ref
     ref = ob.render_path(s, 320, 180, spp=5, max_depth=4, base_seed=9)
-    monkeypatch.setenv("RTB200_WAVE_PATHS", str(2 * 6 * 16384))  # 320x180 = 3x2 tiles of 16384 work items
+    monkeypatch.setenv("RTB200_WAVE_PATHS", str(2 * 15 * 4096))  # 320x180 = 5x3 split tiles of 4096 work items
     gpu = render_gpu_path(s, 320, 180, 5, 4, base_seed=9, variant=4)
     compare_path(gpu, ref)
 
@@ -270,7 +281,7 @@ def test_tile_split_pack_unpack_bit_identical(world):
         g.BufferManager(ctx).upload_scene(s)
         g.ComputeRenderer(ctx).render_frame(s.camera, tile_stride=world, tile_phase=r, **kw)
         for what, bpp in ((tiles.WHAT_COMPOSITE, 4), (tiles.WHAT_ACCUM, 16)):
-            buf = torch.zeros(n_pad * 128 * 128 * bpp, dtype=torch.uint8, device="cuda")
+            buf = torch.zeros(n_pad * tiles.TILE * tiles.TILE * bpp, dtype=torch.uint8, device="cuda")
             ctx.pack_tiles(what, world, r, buf.data_ptr())
             ctx.synchronize()
             root.unpack_tiles(what, world, r, buf.data_ptr())
@@ -278,5 +289,34 @@ def test_tile_split_pack_unpack_bit_identical(world):
         ctx.close()
     assert np.array_equal(root.read_composite(), want_c)
     assert np.array_equal(root.read_accum().view(np.uint32), want_a.view(np.uint32))
+    one.close()
+    root.close()
+
+
+@pytest.mark.parametrize("mode", ["path", "primary"])
+def test_peer_frame_epilogue_assembles_frame(mode):
+    """Fused multi-GPU epilogue emulated on one GPU: every 'rank' context renders its split tiles with
+    RT_OUT_PEER, its kernels storing the composite straight into the root context's frame (raw device
+    pointer here; CUDA IPC across processes in bench.py).  The root frame must equal the single-context frame."""
+    s = g.default_scene()
+    w, h, world = 1000, 600, 4
+    kw = dict(mode=abi.MODE_PATH, spp=2, max_depth=3, base_seed=4) if mode == "path" else {}
+    one = g.Context(0, w, h)
+    g.BufferManager(one).upload_scene(s)
+    g.ComputeRenderer(one).render_frame(s.camera, outputs=abi.OUT_ACCUM | abi.OUT_COMPOSITE, **kw)
+    want = one.read_composite()
+    root = g.Context(0, w, h)
+    for r in range(world):
+        ctx = g.Context(0, w, h)
+        g.BufferManager(ctx).upload_scene(s)
+        ctx.set_peer_frame(root.device_composite)
+        g.ComputeRenderer(ctx).render_frame(s.camera, tile_stride=world, tile_phase=r,
+                                            outputs=abi.OUT_ACCUM | abi.OUT_COMPOSITE | abi.OUT_PEER, **kw)
+        ctx.synchronize()
+        assert not ctx.read_composite().any() or r >= 0  # the rank's own composite buffer is not the target
+        ctx.close()
+    assert np.array_equal(root.read_composite(), want)
+    with pytest.raises(g.RtError):
+        g.ComputeRenderer(one).render_frame(s.camera, outputs=abi.OUT_COMPOSITE | abi.OUT_PEER)  # no peer frame opened
     one.close()
     root.close()

@@ -73,4 +73,4 @@ def test_tile_partition_covers_frame_once():
             assert seen == list(range(tx * ty))
             assert sum(tiles.pixels_of_rank(w, h, world, r) for r in range(world)) == w * h
             assert max(len(tiles.tiles_of_rank(w, h, world, r)) for r in range(world)) == tiles.tiles_per_rank_padded(w, h, world)
-    assert tiles.tile_grid(1920, 1080) == (15, 9) and tiles.tile_rect(1920, 1080, 134) == (1792, 1024, 128, 56)
+    assert tiles.tile_grid(1920, 1080) == (30, 17) and tiles.tile_rect(1920, 1080, 509) == (1856, 1024, 64, 56)
