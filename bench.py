@@ -333,7 +333,7 @@ def run_b200(args, wl, world, rank, local):
     launches = ctx.launch_count - launches0
     t_end = time.perf_counter() + 2.0
     while len(clocks.rows) < 3 and time.perf_counter() < t_end:  # short timed region: keep the same load up until sampled
-        frame()
+        render()  # rank-local (no collective: ranks may loop a different number of times)
         ctx.synchronize()
     clk = clocks.stop()
     # second timed pass for the per-stage breakdown: the headline pass overlaps the kernels of two
