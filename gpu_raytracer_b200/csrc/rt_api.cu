@@ -567,9 +567,11 @@ namespace {
 int build_rebuilt(RtContext* c, uint32_t n) {
     c->rebuilt_ok = false;
     if (n == 0 || n >= RT_LBVH_MAX_PRIMS) return RT_OK;
-    size_t temp_bytes = 0;
+    size_t temp_bytes = 0, scan_bytes = 0;
     cub::DeviceRadixSort::SortPairs(nullptr, temp_bytes, (unsigned long long*)nullptr, (unsigned long long*)nullptr,
                                     (uint32_t*)nullptr, (uint32_t*)nullptr, (int)n, 0, 63, c->stream);
+    cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, (uint32_t*)nullptr, (uint32_t*)nullptr, (int)n, c->stream);
+    if (scan_bytes > temp_bytes) temp_bytes = scan_bytes;
     if (c->lb_keys.reserve(n) < 0 || c->lb_keys_sorted.reserve(n) < 0 || c->lb_vals.reserve(n) < 0 ||
         c->lb_vals_sorted.reserve(n) < 0 || c->lb_temp.reserve(temp_bytes) < 0 || c->lb_children.reserve(n) < 0 ||
         c->lb_range.reserve(n) < 0 || c->lb_parent_i.reserve(n) < 0 || c->lb_parent_l.reserve(n) < 0 ||
@@ -592,10 +594,14 @@ int build_rebuilt(RtContext* c, uint32_t n) {
                                                          c->lb_parent_i.ptr, c->lb_parent_l.ptr);
         lbvh::fit_boxes<<<g, 256, 0, c->stream>>>(c->pbox.ptr, c->lb_vals_sorted.ptr, n, c->lb_children.ptr,
                                                   c->lb_parent_i.ptr, c->lb_parent_l.ptr, c->lb_nbox.ptr, c->lb_visits.ptr);
+        // compact index of every emitted node: flags in lb_visits (free after the fit), scan into lb_vals (free after the sort)
+        lbvh::mark_emitted<<<g, 256, 0, c->stream>>>(c->lb_range.ptr, n, c->lb_visits.ptr);
+        if (cub::DeviceScan::ExclusiveSum(c->lb_temp.ptr, temp_bytes, c->lb_visits.ptr, c->lb_vals.ptr, (int)n, c->stream) != cudaSuccess)
+            return fail(c, RT_ERR_CUDA, "LBVH node compaction scan failed");
         lbvh::emit_wide<<<g, 256, 0, c->stream>>>(c->pbox.ptr, c->lb_vals_sorted.ptr, n, c->lb_children.ptr, c->lb_range.ptr,
-                                                  c->lb_nbox.ptr, c->bnodes.ptr);
+                                                  c->lb_nbox.ptr, c->lb_vals.ptr, c->bnodes.ptr);
         lbvh::tree_depth<<<g, 256, 0, c->stream>>>(c->lb_parent_i.ptr, c->lb_parent_l.ptr, n, c->lb_bounds.ptr + 6);
-        c->launches += 4;
+        c->launches += 6;
     }
     lbvh::gather_sorted<<<g, 256, 0, c->stream>>>(c->wtris.ptr, c->lb_vals_sorted.ptr, n, c->leaf_of_pos.ptr, c->btris.ptr);
     c->launches++;

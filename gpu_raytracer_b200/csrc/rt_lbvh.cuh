@@ -11,11 +11,12 @@
 // rt_kernels.cuh); otherwise that ray re-runs the literal policy.
 #pragma once
 #include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
 #ifndef RT_LBVH_LEAF
-#define RT_LBVH_LEAF 1u
+#define RT_LBVH_LEAF 2u
 #endif
 // REBUILT leaf ref: bit31 | (count-1) << 28 | first sorted slot (28 bits)
 #define RT_LBVH_MAX_PRIMS (1u << 28)
@@ -168,18 +169,30 @@ __device__ __forceinline__ void inflate(float4& lo, float4& hi) {
     lo.x -= pad; lo.y -= pad; lo.z -= pad; hi.x += pad; hi.y += pad; hi.z += pad;
 }
 
-__device__ __forceinline__ uint32_t emit_ref(uint32_t child, const uint2* __restrict__ range) {
+// 1 for every radix-tree node that becomes a traversal node (covers more than RT_LBVH_LEAF triangles); an
+// exclusive scan of these flags gives the compact index: the emitted nodes are stored densely, in radix-tree
+// (= Morton) order, instead of leaving the collapsed subtrees' slots as holes between them (with 2-triangle
+// leaves about half of the slots), which halves the node footprint in L2 / L1.
+__global__ void mark_emitted(const uint2* __restrict__ range, uint32_t n, uint32_t* __restrict__ flags) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint32_t f = 0u;
+    if (n >= 2 && i < n - 1) { uint2 r = range[i]; f = (r.y - r.x + 1u > RT_LBVH_LEAF) ? 1u : 0u; }
+    flags[i] = f;
+}
+
+__device__ __forceinline__ uint32_t emit_ref(uint32_t child, const uint2* __restrict__ range, const uint32_t* __restrict__ compact) {
     if (child & 0x80000000u) return 0x80000000u | (child & 0x7FFFFFFFu); // single triangle: count-1 = 0
     uint2 r = range[child];
     uint32_t cnt = r.y - r.x + 1u;
     if (cnt <= RT_LBVH_LEAF) return 0x80000000u | ((cnt - 1u) << 28) | r.x; // collapsed subtree
-    return child;
+    return compact[child];
 }
 
 // two-child 64-byte nodes in the layout rt_kernels.cuh traverses
 __global__ void emit_wide(const float4* __restrict__ pbox, const uint32_t* __restrict__ sorted_pos, uint32_t n,
                           const uint2* __restrict__ children, const uint2* __restrict__ range,
-                          const float4* __restrict__ nbox, float4* __restrict__ wnodes) {
+                          const float4* __restrict__ nbox, const uint32_t* __restrict__ compact, float4* __restrict__ wnodes) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (n < 2 || i >= n - 1) return;
     uint2 r = range[i];
@@ -192,11 +205,11 @@ __global__ void emit_wide(const float4* __restrict__ pbox, const uint32_t* __res
         lo[k] = s[0]; hi[k] = s[1];
         inflate(lo[k], hi[k]);
     }
-    float4* q = wnodes + (size_t)i * 4;
+    float4* q = wnodes + (size_t)compact[i] * 4;
     q[0] = make_float4(lo[0].x, lo[0].y, lo[0].z, hi[0].x);
     q[1] = make_float4(hi[0].y, hi[0].z, lo[1].x, lo[1].y);
     q[2] = make_float4(lo[1].z, hi[1].x, hi[1].y, hi[1].z);
-    q[3] = make_float4(__uint_as_float(emit_ref(ch.x, range)), __uint_as_float(emit_ref(ch.y, range)), 0.0f, 0.0f);
+    q[3] = make_float4(__uint_as_float(emit_ref(ch.x, range, compact)), __uint_as_float(emit_ref(ch.y, range, compact)), 0.0f, 0.0f);
 }
 
 // triangle records in sorted order; the last word carries the triangle_indices position

@@ -62,6 +62,17 @@ struct WvBuffers {
 #ifndef WV_SPEC
 #define WV_SPEC 1          // speculative descent past the first postponed leaf
 #endif
+#ifndef WV_L2_KEEP
+#define WV_L2_KEEP 0       // 1: BVH loads carry an L2 evict_last policy (measured: no effect on C3 / C4, kept for HBM-resident scenes)
+#endif
+#ifndef WV_CS_STORES
+#define WV_CS_STORES 0     // 1: path-state stores with the evict-first (.cs) hint (measured: C3 +1 %, C4 -7 %)
+#endif
+#if WV_CS_STORES
+#define WV_ST(ptr, val) __stcs((ptr), (val))
+#else
+#define WV_ST(ptr, val) (*(ptr) = (val))
+#endif
 #ifndef WV_BLOCKS
 #define WV_BLOCKS 4        // resident 256-thread blocks per SM the extend kernel is compiled for
 #endif
@@ -108,11 +119,11 @@ __global__ void __launch_bounds__(256) wv_generate(const __grid_constant__ KPara
         if (s != 0u) { jx = rng.next_f32(); jy = rng.next_f32(); }
         Ray ray = camera_ray(p, px, py, jx, jy, true);
         float4* st = w.state[0] + (size_t)slot * 4;
-        st[0] = make_float4(ray.o.x, ray.o.y, ray.o.z, __uint_as_float(rng.seed));
-        st[1] = make_float4(ray.d.x, ray.d.y, ray.d.z, __uint_as_float(0u));
-        st[2] = make_float4(1.0f, 1.0f, 1.0f, __uint_as_float(idx));
-        st[3] = make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(sl));
-        w.hit[0][slot] = wv_seed_record(p, ray);
+        WV_ST(st, make_float4(ray.o.x, ray.o.y, ray.o.z, __uint_as_float(rng.seed)));
+        WV_ST(st + 1, make_float4(ray.d.x, ray.d.y, ray.d.z, __uint_as_float(0u)));
+        WV_ST(st + 2, make_float4(1.0f, 1.0f, 1.0f, __uint_as_float(idx)));
+        WV_ST(st + 3, make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(sl)));
+        WV_ST(w.hit[0] + slot, wv_seed_record(p, ray));
     }
 }
 
@@ -131,6 +142,9 @@ __global__ void __launch_bounds__(256, WV_BLOCKS) wv_extend(const __grid_constan
     const float4* __restrict__ state = w.state[qi];
     uint2* __restrict__ hit = w.hit[qi];
     if (blockIdx.x == 0 && tid == 0) w.ctrl->n[qi ^ 1] = 0; // wv_shade of this depth appends there
+#if WV_L2_KEEP
+    const unsigned long long keep = l2_keep_policy();
+#endif
 
     uint32_t slot = EMPTY;      // queue position of the ray this lane traces
     bool exhausted = false, literal = false;
@@ -155,8 +169,8 @@ __global__ void __launch_bounds__(256, WV_BLOCKS) wv_extend(const __grid_constan
     };
     auto flush = [&]() { // store the finished ray's record
         if (slot != EMPTY) {
-            if (literal) hit[slot] = make_uint2(__float_as_uint(best_t), (WV_KIND_LITERAL << 30) | (seed_id == WV_ID_MISS ? WV_NO_SPHERE : (seed_id & WV_NO_SPHERE)));
-            else if (best_slot != EMPTY) hit[slot] = make_uint2(__float_as_uint(best_t), best_slot);
+            if (literal) WV_ST(hit + slot, make_uint2(__float_as_uint(best_t), (WV_KIND_LITERAL << 30) | (seed_id == WV_ID_MISS ? WV_NO_SPHERE : (seed_id & WV_NO_SPHERE))));
+            else if (best_slot != EMPTY) WV_ST(hit + slot, make_uint2(__float_as_uint(best_t), best_slot));
             slot = EMPTY;
         }
     };
@@ -196,7 +210,7 @@ __global__ void __launch_bounds__(256, WV_BLOCKS) wv_extend(const __grid_constan
                 else {
                     slot = q;
                     float4 a = __ldcs(state + (size_t)q * 4), b = __ldcs(state + (size_t)q * 4 + 1);
-                    uint2 seed = hit[q];
+                    uint2 seed = __ldcs(hit + q);
                     ox = a.x; oy = a.y; oz = a.z; dx = b.x; dy = b.y; dz = b.z;
                     best_t = __uint_as_float(seed.x); seed_id = seed.y;
                     limit = best_t * RT_PRUNE_SCALE + RT_PRUNE_ABS;
@@ -236,7 +250,11 @@ __global__ void __launch_bounds__(256, WV_BLOCKS) wv_extend(const __grid_constan
             if (!(cur & RT_LEAF_FLAG)) {
                 const float4* np = nodes + (uint64_t)cur * 4;
                 float4 q0, q1, q2, q3;
+#if WV_L2_KEEP
+                ldg_node_keep(np, keep, q0, q1, q2, q3);
+#else
                 ldg_node(np, q0, q1, q2, q3);
+#endif
                 uint32_t lref = __float_as_uint(q3.x), rref = __float_as_uint(q3.y);
                 float el, er;
                 bool hl, hr;
@@ -271,7 +289,11 @@ __global__ void __launch_bounds__(256, WV_BLOCKS) wv_extend(const __grid_constan
                 Ray ray; ray.o = mk(ox, oy, oz); ray.d = mk(dx, dy, dz);
                 for (;;) {
                     const float4* tpn = tris + (uint64_t)ts * 3;
+#if WV_L2_KEEP
+                    float4 a = ldg_keep(tpn, keep), c = ldg_keep(tpn + 1, keep), d = ldg_keep(tpn + 2, keep);
+#else
                     float4 a = __ldg(tpn), c = __ldg(tpn + 1), d = __ldg(tpn + 2);
+#endif
                     float t = triangle_t(ray, mk(a.x, a.y, a.z), mk(a.w, c.x, c.y), mk(c.z, c.w, d.x));
                     uint32_t pos = POLICY == 2 ? __float_as_uint(d.w) : ts;
                     if (COUNT) c_tri++;
@@ -317,7 +339,7 @@ __global__ void __launch_bounds__(256) wv_shade(const __grid_constant__ KParams 
         if (i < n) {
             const float4* st = w.state[qi] + (size_t)i * 4;
             float4 s0 = __ldcs(st), s1 = __ldcs(st + 1), s2 = __ldcs(st + 2), s3 = __ldcs(st + 3);
-            uint2 hr = w.hit[qi][i];
+            uint2 hr = __ldcs(w.hit[qi] + i);
             ray.o = mk(s0.x, s0.y, s0.z); ray.d = mk(s1.x, s1.y, s1.z);
             rng.seed = __float_as_uint(s0.w);
             depth = __float_as_uint(s1.w); idx = __float_as_uint(s2.w); sl = __float_as_uint(s3.w);
@@ -422,7 +444,7 @@ __global__ void __launch_bounds__(256) wv_shade(const __grid_constant__ KParams 
                     cont = true;
                 }
             }
-            if (end) w.lbuf[(size_t)sl * p.n_work + idx] = make_float4(L.x, L.y, L.z, 1.0f); // SPEC.md step 4, summed by wv_resolve
+            if (end) WV_ST(w.lbuf + (size_t)sl * p.n_work + idx, make_float4(L.x, L.y, L.z, 1.0f)); // SPEC.md step 4, summed by wv_resolve
         }
         // ---- survivors become the compact path list of the next depth (order within the warp kept)
         unsigned m = __ballot_sync(full, cont);
@@ -434,11 +456,11 @@ __global__ void __launch_bounds__(256) wv_shade(const __grid_constant__ KParams 
             if (cont) {
                 uint32_t ns = base + __popc(m & ((1u << lane) - 1u));
                 float4* st = w.state[qi ^ 1] + (size_t)ns * 4;
-                st[0] = make_float4(ray.o.x, ray.o.y, ray.o.z, __uint_as_float(rng.seed));
-                st[1] = make_float4(ray.d.x, ray.d.y, ray.d.z, __uint_as_float(depth));
-                st[2] = make_float4(tp.x, tp.y, tp.z, __uint_as_float(idx));
-                st[3] = make_float4(L.x, L.y, L.z, __uint_as_float(sl));
-                w.hit[qi ^ 1][ns] = wv_seed_record(p, ray);
+                WV_ST(st, make_float4(ray.o.x, ray.o.y, ray.o.z, __uint_as_float(rng.seed)));
+                WV_ST(st + 1, make_float4(ray.d.x, ray.d.y, ray.d.z, __uint_as_float(depth)));
+                WV_ST(st + 2, make_float4(tp.x, tp.y, tp.z, __uint_as_float(idx)));
+                WV_ST(st + 3, make_float4(L.x, L.y, L.z, __uint_as_float(sl)));
+                WV_ST(w.hit[qi ^ 1] + ns, wv_seed_record(p, ray));
             }
         }
     }
