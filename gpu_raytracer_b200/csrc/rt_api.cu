@@ -100,6 +100,10 @@ struct RtContext {
     DevBuf<unsigned char> lb_temp;
     DevBuf<uint2> lb_children, lb_range;
     DevBuf<float4> pbox, lb_nbox, bnodes, btris;
+    DevBuf<uint4> bqnodes;   // 32-byte quantised copy of bnodes (wave engine)
+    DevBuf<float> lb_grid;   // its grid: origin[3], cell[3]
+    float bq_grid[6] = {0, 0, 0, 1, 1, 1};
+    uint32_t lbvh_depth = 0; // levels of the internal tree (picks the wave engine's stack form)
     bool rebuilt_ok = false;
     uint32_t broot_ref = RT_CHILD_ABSENT;
     float broot_min[3] = {0, 0, 0}, broot_max[3] = {0, 0, 0};
@@ -576,7 +580,8 @@ int build_rebuilt(RtContext* c, uint32_t n) {
         c->lb_vals_sorted.reserve(n) < 0 || c->lb_temp.reserve(temp_bytes) < 0 || c->lb_children.reserve(n) < 0 ||
         c->lb_range.reserve(n) < 0 || c->lb_parent_i.reserve(n) < 0 || c->lb_parent_l.reserve(n) < 0 ||
         c->lb_visits.reserve(n) < 0 || c->lb_bounds.reserve(8) < 0 || c->lb_nbox.reserve((size_t)n * 2) < 0 ||
-        c->bnodes.reserve((size_t)n * 4) < 0 || c->btris.reserve((size_t)n * 3) < 0)
+        c->bnodes.reserve((size_t)n * 4) < 0 || c->btris.reserve((size_t)n * 3) < 0 || c->bqnodes.reserve((size_t)n * 2) < 0 ||
+        c->lb_grid.reserve(8) < 0)
         return fail(c, RT_ERR_CUDA, "LBVH cudaMalloc failed for %u triangles", n);
     const uint32_t g = (n + 255) / 256;
     const unsigned int init_bounds[8] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0u, 0u, 0u, 0u, 0u}; // [6] = tree depth
@@ -600,8 +605,11 @@ int build_rebuilt(RtContext* c, uint32_t n) {
             return fail(c, RT_ERR_CUDA, "LBVH node compaction scan failed");
         lbvh::emit_wide<<<g, 256, 0, c->stream>>>(c->pbox.ptr, c->lb_vals_sorted.ptr, n, c->lb_children.ptr, c->lb_range.ptr,
                                                   c->lb_nbox.ptr, c->lb_vals.ptr, c->bnodes.ptr);
+        lbvh::quant_grid<<<1, 1, 0, c->stream>>>(c->lb_nbox.ptr, c->lb_grid.ptr);
+        lbvh::emit_quant<<<g, 256, 0, c->stream>>>(c->pbox.ptr, c->lb_vals_sorted.ptr, n, c->lb_children.ptr, c->lb_range.ptr,
+                                                   c->lb_nbox.ptr, c->lb_vals.ptr, c->lb_grid.ptr, c->bqnodes.ptr);
         lbvh::tree_depth<<<g, 256, 0, c->stream>>>(c->lb_parent_i.ptr, c->lb_parent_l.ptr, n, c->lb_bounds.ptr + 6);
-        c->launches += 6;
+        c->launches += 8;
     }
     lbvh::gather_sorted<<<g, 256, 0, c->stream>>>(c->wtris.ptr, c->lb_vals_sorted.ptr, n, c->leaf_of_pos.ptr, c->btris.ptr);
     c->launches++;
@@ -611,6 +619,7 @@ int build_rebuilt(RtContext* c, uint32_t n) {
     CK(c, cudaMemcpyAsync(&tree_depth, c->lb_bounds.ptr + 6, 4, cudaMemcpyDeviceToHost, c->stream));
     if (n >= 2) CK(c, cudaMemcpyAsync(rb, c->lb_nbox.ptr, sizeof rb, cudaMemcpyDeviceToHost, c->stream));
     else CK(c, cudaMemcpyAsync(rb, c->pbox.ptr, sizeof rb, cudaMemcpyDeviceToHost, c->stream));
+    if (n >= 2) CK(c, cudaMemcpyAsync(c->bq_grid, c->lb_grid.ptr, sizeof c->bq_grid, cudaMemcpyDeviceToHost, c->stream));
     CK(c, cudaStreamSynchronize(c->stream));
     CK(c, cudaGetLastError());
     float m = 0.0f;
@@ -619,6 +628,8 @@ int build_rebuilt(RtContext* c, uint32_t n) {
     float pad = m * 1.52587890625e-05f + 1e-30f; // same inflation as lbvh::inflate
     for (int k = 0; k < 3; k++) { c->broot_min[k] = v[k] - pad; c->broot_max[k] = v[3 + k] + pad; }
     c->broot_ref = n <= RT_LBVH_LEAF ? (RT_LEAF_FLAG | ((n - 1u) << 28)) : 0u;
+    if (getenv("RTB200_DEBUG")) fprintf(stderr, "[rtb200] internal LBVH: %u triangles, depth %u\n", n, tree_depth);
+    c->lbvh_depth = tree_depth;
     c->rebuilt_ok = tree_depth < 60; // the traversal stacks hold 64 entries (many coincident centroids can deepen the tree)
     return RT_OK;
 }
@@ -680,6 +691,7 @@ void fill_scene(RtContext* c, KParams& k) {
     k.bnodes = c->bnodes.ptr; k.btris = c->btris.ptr; k.leaf_of_pos = c->leaf_of_pos.ptr;
     k.broot_ref = c->broot_ref;
     memcpy(k.broot_min, c->broot_min, 12); memcpy(k.broot_max, c->broot_max, 12);
+    k.bqnodes = c->bqnodes.ptr; memcpy(k.bq_origin, c->bq_grid, 12); memcpy(k.bq_scale, c->bq_grid + 3, 12);
     k.accum = c->accum.ptr; k.hits = c->hits.ptr;
     for (int i = 0; i < 3; i++) k.chan[i] = c->chan[i].ptr;
     k.composite = c->composite.ptr;
@@ -843,6 +855,23 @@ __global__ void wv_publish(const WvCtrl* ctrl, int n_sub, unsigned long long* dc
     if (count) { dcounters[0] = cc[0]; dcounters[1] = cc[1]; dcounters[2] = seg; dcounters[3] = cc[2]; dcounters[4] = cc[3]; }
 }
 
+typedef void (*WvKernel)(const KParams, WvBuffers, int);
+template <int P, bool D>
+static WvKernel wv_extend_pick(bool count, bool gen) {
+    if (count) return gen ? wv_extend<P, true, true, D> : wv_extend<P, true, false, D>;
+    return gen ? wv_extend<P, false, true, D> : wv_extend<P, false, false, D>;
+}
+static WvKernel wv_extend_kernel(int policy, bool count, bool gen, bool deep) {
+    if (policy == 2) return deep ? wv_extend_pick<2, true>(count, gen) : wv_extend_pick<2, false>(count, gen);
+    return deep ? wv_extend_pick<1, true>(count, gen) : wv_extend_pick<1, false>(count, gen);
+}
+static WvKernel wv_shade_kernel(int policy, bool count, bool gen) {
+    static const WvKernel t[2][2][2] = {
+        {{wv_shade<1, false, false>, wv_shade<1, false, true>}, {wv_shade<1, true, false>, wv_shade<1, true, true>}},
+        {{wv_shade<2, false, false>, wv_shade<2, false, true>}, {wv_shade<2, true, false>, wv_shade<2, true, true>}}};
+    return t[policy - 1][count ? 1 : 0][gen ? 1 : 0];
+}
+
 int launch_wave(RtContext* c, KParams k, uint32_t traversal) {
     if (k.n_work == 0) return RT_OK;
     int policy = pick_policy(c, k, traversal);
@@ -874,7 +903,11 @@ int launch_wave(RtContext* c, KParams k, uint32_t traversal) {
     if (!c->wv_fork) CK(c, cudaEventCreateWithFlags(&c->wv_fork, cudaEventDisableTiming));
     const bool count = k.counters != nullptr;
     int per_sm = 0, sms = 0;
-    const void* fn = policy == 2 ? (const void*)wv_extend<2, false> : (const void*)wv_extend<1, false>;
+    // the shared-memory stack holds one deferred sibling per level plus the sentinel entry
+    const uint32_t tree_levels = policy == 2 ? c->lbvh_depth : c->wide.max_depth;
+    bool deep = tree_levels + 2u > WV_STK;
+    if (const char* e = getenv("RTB200_WAVE_DEEP")) deep = deep || atoi(e) != 0; // tests: force the overflow-capable form
+    const void* fn = (const void*)wv_extend_kernel(policy, false, false, deep);
     CK(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, 256, 0));
     CK(c, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device));
     CK(c, cudaEventRecord(c->ev0, c->stream));
@@ -908,6 +941,14 @@ int launch_wave(RtContext* c, KParams k, uint32_t traversal) {
         ks.n_work = tiles_s * 4096u;
         const size_t Ps = (size_t)ks.n_work * spp_wave;
         WvBuffers w;
+        w.valid_pixels = 0; // pixels of this sub-frame's tiles that lie inside the image
+        for (uint32_t t = 0; t < tiles_s; t++) {
+            const uint32_t tile = ks.tile_phase + t * ks.tile_stride, tx = tile % ks.tiles_x, ty = tile / ks.tiles_x;
+            const uint32_t x0 = tx * RT_SPLIT_TILE, y0 = ty * RT_SPLIT_TILE;
+            const uint32_t tw = x0 >= ks.width ? 0u : (ks.width - x0 < RT_SPLIT_TILE ? ks.width - x0 : RT_SPLIT_TILE);
+            const uint32_t th = y0 >= ks.height ? 0u : (ks.height - y0 < RT_SPLIT_TILE ? ks.height - y0 : RT_SPLIT_TILE);
+            w.valid_pixels += tw * th;
+        }
         w.state[0] = c->wv_state[0].ptr + path_base * 4; w.state[1] = c->wv_state[1].ptr + path_base * 4;
         w.hit[0] = c->wv_hit[0].ptr + path_base; w.hit[1] = c->wv_hit[1].ptr + path_base;
         w.lbuf = c->wv_lbuf.ptr + path_base; w.ctrl = c->wv_ctrl.ptr + sub;
@@ -922,21 +963,23 @@ int launch_wave(RtContext* c, KParams k, uint32_t traversal) {
             w.first_wave = s0 == k.first_sample; w.last_wave = s0 + w.spp_wave == s_end;
             if (!w.first_wave) CK(c, cudaMemsetAsync(w.ctrl, 0, 16, st)); // n[0], n[1], head
             if (!w.first_wave) mark(-1);
+#if !WV_FUSE_GEN
             wv_generate<<<stream_blocks, 256, 0, st>>>(ks, w);
+            c->launches++;
+#endif
             mark(0);
             for (uint32_t d = 0; d <= k.path_max_depth; d++) {
                 const int qi = (int)(d & 1u);
-                if (policy == 2) { if (count) wv_extend<2, true><<<ext_blocks, 256, 0, st>>>(ks, w, qi); else wv_extend<2, false><<<ext_blocks, 256, 0, st>>>(ks, w, qi); }
-                else { if (count) wv_extend<1, true><<<ext_blocks, 256, 0, st>>>(ks, w, qi); else wv_extend<1, false><<<ext_blocks, 256, 0, st>>>(ks, w, qi); }
+                const bool gen = WV_FUSE_GEN && d == 0u; // depth 0 computes its primary rays from the queue position
+                wv_extend_kernel(policy, count, gen, deep)<<<ext_blocks, 256, 0, st>>>(ks, w, qi);
                 mark(1);
-                if (policy == 2) { if (count) wv_shade<2, true><<<stream_blocks, 256, 0, st>>>(ks, w, qi); else wv_shade<2, false><<<stream_blocks, 256, 0, st>>>(ks, w, qi); }
-                else { if (count) wv_shade<1, true><<<stream_blocks, 256, 0, st>>>(ks, w, qi); else wv_shade<1, false><<<stream_blocks, 256, 0, st>>>(ks, w, qi); }
+                wv_shade_kernel(policy, count, gen)<<<stream_blocks, 256, 0, st>>>(ks, w, qi);
                 mark(2);
                 c->launches += 2;
             }
             wv_resolve<<<stream_blocks, 256, 0, st>>>(ks, w);
             mark(3);
-            c->launches += 2;
+            c->launches++;
         }
         if (sub) { CK(c, cudaEventRecord(c->wv_join[sub - 1], st)); CK(c, cudaStreamWaitEvent(c->stream, c->wv_join[sub - 1], 0)); }
     }

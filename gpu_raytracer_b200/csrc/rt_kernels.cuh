@@ -66,6 +66,8 @@ struct KParams {
     const uint32_t* leaf_of_pos;   // uploaded leaf node of every triangle_indices position
     uint32_t broot_ref;
     float broot_min[3], broot_max[3];
+    const uint4* bqnodes;          // the same tree as 2 x uint4 per node: 16-bit boxes on the grid below (rt_lbvh.cuh)
+    float bq_origin[3], bq_scale[3];
     // outputs
     float4* accum;
     RtHitRecord* hits;
@@ -94,6 +96,12 @@ __device__ __forceinline__ void ldg_node(const float4* __restrict__ np, float4& 
         : "=f"(q0.x), "=f"(q0.y), "=f"(q0.z), "=f"(q0.w), "=f"(q1.x), "=f"(q1.y), "=f"(q1.z), "=f"(q1.w) : "l"(np));
     asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
         : "=f"(q2.x), "=f"(q2.y), "=f"(q2.z), "=f"(q2.w), "=f"(q3.x), "=f"(q3.y), "=f"(q3.z), "=f"(q3.w) : "l"(np + 2));
+}
+
+// One 32-byte quantised node = one 256-bit read-only load.
+__device__ __forceinline__ void ldg_qnode(const uint4* __restrict__ np, uint32_t (&w)[8]) {
+    asm("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+        : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]), "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7]) : "l"(np));
 }
 
 struct Hit {

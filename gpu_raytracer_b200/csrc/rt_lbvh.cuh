@@ -212,6 +212,55 @@ __global__ void emit_wide(const float4* __restrict__ pbox, const uint32_t* __res
     q[3] = make_float4(__uint_as_float(emit_ref(ch.x, range, compact)), __uint_as_float(emit_ref(ch.y, range, compact)), 0.0f, 0.0f);
 }
 
+// ---- 32-byte nodes with 16-bit boxes (the wave engine's extend kernel) ------------------------------------
+// ncu on wv_extend: the SM's L1 data stage is the busiest unit and every lane of a warp fetches a different
+// node, so a node should be ONE 32-byte sector instead of two.  Both child boxes are stored on a fixed grid of
+// 65000 cells per axis over the (inflated) root box: word a of a child = min_a | max_a << 16.  The boxes only
+// have to be conservative (the winner is certified against the uploaded tree afterwards): each plane is the
+// fp32 plane after lbvh::inflate, moved outwards to the next grid line and one more cell.  The first cell
+// covers the directed rounding of the division, the second the rounding of the ray-side constant
+// B2 = (O - o) / d - 2^23 S / d (half a cell, see wv_extend), the world-space pad everything the 64-byte
+// layout's pad covers.
+// grid[0..2] = origin O, grid[3..5] = cell size S
+__global__ void quant_grid(const float4* __restrict__ root_box, float* __restrict__ grid) {
+    float4 lo = root_box[0], hi = root_box[1];
+    inflate(lo, hi);
+    const float l[3] = {lo.x, lo.y, lo.z}, h[3] = {hi.x, hi.y, hi.z};
+    for (int k = 0; k < 3; k++) {
+        float s = fmaxf((h[k] - l[k]) / 65000.0f, 1e-30f);
+        grid[3 + k] = s;
+        grid[k] = l[k] - 8.0f * s;
+    }
+}
+__device__ __forceinline__ uint32_t quant_pair(float lo, float hi, float O, float S) {
+    float ql = floorf((lo - O) / S) - 1.0f, qh = ceilf((hi - O) / S) + 1.0f;
+    ql = fminf(fmaxf(ql, 0.0f), 65535.0f);
+    qh = fminf(fmaxf(qh, 0.0f), 65535.0f);
+    return (uint32_t)ql | ((uint32_t)qh << 16);
+}
+__global__ void emit_quant(const float4* __restrict__ pbox, const uint32_t* __restrict__ sorted_pos, uint32_t n,
+                           const uint2* __restrict__ children, const uint2* __restrict__ range,
+                           const float4* __restrict__ nbox, const uint32_t* __restrict__ compact,
+                           const float* __restrict__ grid, uint4* __restrict__ qnodes) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n < 2 || i >= n - 1) return;
+    uint2 r = range[i];
+    if (r.y - r.x + 1u <= RT_LBVH_LEAF) return;
+    uint2 ch = children[i];
+    uint32_t c[2] = {ch.x, ch.y}, w[6];
+    for (int k = 0; k < 2; k++) {
+        const float4* s = (c[k] & 0x80000000u) ? pbox + (size_t)sorted_pos[c[k] & 0x7FFFFFFFu] * 2 : nbox + (size_t)c[k] * 2;
+        float4 lo = s[0], hi = s[1];
+        inflate(lo, hi);
+        w[k * 3] = quant_pair(lo.x, hi.x, grid[0], grid[3]);
+        w[k * 3 + 1] = quant_pair(lo.y, hi.y, grid[1], grid[4]);
+        w[k * 3 + 2] = quant_pair(lo.z, hi.z, grid[2], grid[5]);
+    }
+    uint4* q = qnodes + (size_t)compact[i] * 2;
+    q[0] = make_uint4(w[0], w[1], w[2], w[3]);
+    q[1] = make_uint4(w[4], w[5], emit_ref(ch.x, range, compact), emit_ref(ch.y, range, compact));
+}
+
 // triangle records in sorted order; the last word carries the triangle_indices position
 __global__ void gather_sorted(const float4* __restrict__ wtris, const uint32_t* __restrict__ sorted_pos, uint32_t n,
                               const uint32_t* __restrict__ leaf_of_pos, float4* __restrict__ out) {

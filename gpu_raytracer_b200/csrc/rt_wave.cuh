@@ -38,6 +38,7 @@ struct WvBuffers {
     uint32_t s0, spp_wave; // samples [s0, s0 + spp_wave) are in this wave
     uint32_t last_wave;    // resolve writes the composite
     uint32_t first_wave;   // resolve honours reset_accum
+    uint32_t valid_pixels; // work items of this sub-frame that lie inside the image (fused generation: segment count of depth 0)
 };
 
 // hit id encoding
@@ -48,8 +49,8 @@ struct WvBuffers {
 #define WV_NO_SPHERE 0x3FFFFFFFu
 
 #ifndef WV_STK
-#define WV_STK 16          // shared-memory stack entries per thread (16 KB per 256-thread block; deeper entries spill to local memory)
-#endif
+#define WV_STK 32          // shared-memory stack entries per thread (32 KB per 256-thread block).  Trees deeper than
+#endif                     // WV_STK - 2 levels run the DEEP instantiation, whose further entries live in local memory
 #ifndef WV_REFILL
 #define WV_REFILL 10       // refill when this many lanes have finished their ray
 #endif
@@ -73,6 +74,12 @@ struct WvBuffers {
 #else
 #define WV_ST(ptr, val) (*(ptr) = (val))
 #endif
+#ifndef WV_QUANT
+#define WV_QUANT 1         // 1: REBUILT policy traverses the 32-byte nodes with 16-bit boxes (one sector per node visit)
+#endif
+#ifndef WV_FUSE_GEN
+#define WV_FUSE_GEN 1      // 1: no wv_generate launch; the depth-0 extend / shade compute the primary ray from the queue position
+#endif
 #ifndef WV_BLOCKS
 #define WV_BLOCKS 4        // resident 256-thread blocks per SM the extend kernel is compiled for
 #endif
@@ -93,6 +100,26 @@ __device__ __forceinline__ uint2 wv_seed_record(const KParams& p, const Ray& ray
     float c; uint32_t si;
     wv_sphere_seed(p, ray, &c, &si);
     return make_uint2(__float_as_uint(c), si == WV_NO_SPHERE ? WV_ID_MISS : ((WV_KIND_SPHERE << 30) | si));
+}
+
+// Position q of a wave's primary-ray list -> work item, local sample, camera ray and the rng state after the
+// jitter draws (SPEC.md steps 1-2).  Warp-sized runs of q are one 8x4 pixel group for one sample, consecutive
+// runs the samples of that group.  Used by wv_generate, or (WV_FUSE_GEN) by the depth-0 extend and shade
+// launches themselves, which then never materialise the 64-byte primary path records.
+__device__ __forceinline__ bool wv_primary(const KParams& p, const WvBuffers& w, uint32_t q, uint32_t* idx, uint32_t* sl,
+                                           Ray* ray, uint32_t* rng_seed) {
+    const uint32_t wi = q >> 5, group = wi / w.spp_wave;
+    *sl = wi - group * w.spp_wave;
+    *idx = group * 32u + (q & 31u);
+    uint32_t px = 0, py = 0;
+    if (!work_to_pixel(p, *idx, &px, &py)) return false;
+    const uint32_t s = w.s0 + *sl;
+    SimpleRng rng; rng.seed = p.base_seed + s + px + py * p.width;
+    float jx = 0.5f, jy = 0.5f;
+    if (s != 0u) { jx = rng.next_f32(); jy = rng.next_f32(); }
+    *ray = camera_ray(p, px, py, jx, jy, true);
+    *rng_seed = rng.seed;
+    return true;
 }
 
 // ---- wave start: SPEC.md steps 1-2 for every (pixel, sample) of this wave ---------------
@@ -128,17 +155,26 @@ __global__ void __launch_bounds__(256) wv_generate(const __grid_constant__ KPara
 }
 
 // ---- extend: closest triangle of every ray of the current depth ---------------------------
-template <int POLICY, bool COUNT> // POLICY 1 (ORDERED, uploaded tree) or 2 (REBUILT, internal LBVH)
+// GEN: depth 0 of a wave with fused generation; queue position q is primary ray q (wv_primary)
+// DEEP: the tree may be deeper than the shared-memory stack (otherwise every stack access is one predicated
+// shared-memory instruction and the node step has no branches)
+template <int POLICY, bool COUNT, bool GEN, bool DEEP> // POLICY 1 (ORDERED, uploaded tree) or 2 (REBUILT, internal LBVH)
 __global__ void __launch_bounds__(256, WV_BLOCKS) wv_extend(const __grid_constant__ KParams p, WvBuffers w, int qi) {
     __shared__ uint32_t s_stack[WV_STK][256];
-    uint32_t lstack[64 - WV_STK];
+    uint32_t lstack[DEEP ? 64 - WV_STK : 1];
     const uint32_t tid = threadIdx.x, lane = tid & 31u;
     const unsigned full = 0xFFFFFFFFu;
     constexpr uint32_t EMPTY = 0xFFFFFFFFu; // has RT_LEAF_FLAG set: never an internal node
     const float4* __restrict__ nodes = POLICY == 2 ? p.bnodes : p.wnodes;
     const float4* __restrict__ tris = POLICY == 2 ? p.btris : p.wtris;
+    constexpr bool QUANT = POLICY == 2 && WV_QUANT;
+    // QUANT: plane q of axis a lies at t = q * A_a + B_a with A = S / d, B = (O - o) / d.  The 16-bit q is turned
+    // into the float 2^23 + q by one byte permute (0x4B00'qqqq), so t = fma(2^23 + q, A, B - 2^23 A); the same
+    // permute picks the near or the far plane of the axis by the sign of d (selectors sn / sn ^ 0x22), which
+    // replaces the min / max of the two plane distances.  ix.. hold A, kx.. hold B - 2^23 A.
+    uint32_t snx = 0x7410u, sny = 0x7410u, snz = 0x7410u;
     const uint32_t root_ref = POLICY == 2 ? p.broot_ref : p.root_ref;
-    const uint32_t n = w.ctrl->n[qi];
+    const uint32_t n = GEN ? p.n_work * w.spp_wave : w.ctrl->n[qi];
     const float4* __restrict__ state = w.state[qi];
     uint2* __restrict__ hit = w.hit[qi];
     if (blockIdx.x == 0 && tid == 0) w.ctrl->n[qi ^ 1] = 0; // wv_shade of this depth appends there
@@ -159,11 +195,18 @@ __global__ void __launch_bounds__(256, WV_BLOCKS) wv_extend(const __grid_constan
     bool queue_done = n == 0u;
     const uint32_t chunk = n >= gridDim.x * 8u * 128u * 4u ? 128u : 32u;
 
-    auto push = [&](uint32_t v) { if (sp < WV_STK) s_stack[sp][tid] = v; else lstack[sp - WV_STK] = v; sp++; };
-    // entry 0 of every column holds EMPTY and sp starts at 1: popping the last entry yields EMPTY
-    // ("traversal finished") without an emptiness test; a finished lane is never popped again
+    // entry 0 of every column holds EMPTY and the stack starts at entry 1: popping the last entry yields EMPTY
+    // ("traversal finished") without an emptiness test; a finished lane is never popped again.
+    // !DEEP keeps the stack top as a shared-memory pointer (no index arithmetic), DEEP as an index.
     s_stack[0][tid] = EMPTY;
+    uint32_t* sptr = &s_stack[1][tid];
+    auto push = [&](uint32_t v) {
+        if (!DEEP) { *sptr = v; sptr += 256; return; }
+        if (sp < WV_STK) s_stack[sp][tid] = v; else lstack[sp - WV_STK] = v;
+        sp++;
+    };
     auto pop = [&]() -> uint32_t {
+        if (!DEEP) { sptr -= 256; return *sptr; }
         sp--;
         return sp < WV_STK ? s_stack[sp][tid] : lstack[sp - WV_STK];
     };
@@ -171,6 +214,7 @@ __global__ void __launch_bounds__(256, WV_BLOCKS) wv_extend(const __grid_constan
         if (slot != EMPTY) {
             if (literal) WV_ST(hit + slot, make_uint2(__float_as_uint(best_t), (WV_KIND_LITERAL << 30) | (seed_id == WV_ID_MISS ? WV_NO_SPHERE : (seed_id & WV_NO_SPHERE))));
             else if (best_slot != EMPTY) WV_ST(hit + slot, make_uint2(__float_as_uint(best_t), best_slot));
+            else if (GEN) WV_ST(hit + slot, make_uint2(__float_as_uint(best_t), seed_id)); // nobody seeded the record
             slot = EMPTY;
         }
     };
@@ -208,32 +252,54 @@ __global__ void __launch_bounds__(256, WV_BLOCKS) wv_extend(const __grid_constan
                 flush();
                 if (q == EMPTY) exhausted = queue_done;
                 else {
-                    slot = q;
-                    float4 a = __ldcs(state + (size_t)q * 4), b = __ldcs(state + (size_t)q * 4 + 1);
-                    uint2 seed = __ldcs(hit + q);
-                    ox = a.x; oy = a.y; oz = a.z; dx = b.x; dy = b.y; dz = b.z;
-                    best_t = __uint_as_float(seed.x); seed_id = seed.y;
-                    limit = best_t * RT_PRUNE_SCALE + RT_PRUNE_ABS;
-                    best_slot = EMPTY; best_pos = 0u; sp = 1; pend = EMPTY; literal = false;
-                    cur = root_ref == RT_CHILD_ABSENT ? EMPTY : root_ref;
-                    if (POLICY == 2) {
-                        // zero / tiny direction components: neither the certification argument nor the
-                        // FMA slab applies (closest_triangle_rebuilt) -> wv_shade runs the literal policy
-                        if (!(fabsf(dx) >= 1e-30f && fabsf(dy) >= 1e-30f && fabsf(dz) >= 1e-30f)) { literal = true; cur = EMPTY; }
-                        // boxes of the internal tree are conservative (inflated 2^-16 relative), so
-                        // the slab test may use t = b * inv - o * inv with one FMA per plane
-                        ix = 1.0f / dx; iy = 1.0f / dy; iz = 1.0f / dz;
-                        kx = ox * ix; ky = oy * iy; kz = oz * iz;
-                        float e;
-                        if (COUNT) c_box++;
-                        if (cur != EMPTY && !slab_fma(mk(ix, iy, iz), mk(kx, ky, kz), mka(p.broot_min), mka(p.broot_max), &e)) cur = EMPTY;
+                    bool valid = true;
+                    if (GEN) {
+                        uint32_t g_idx, g_sl, g_seed;
+                        Ray pr;
+                        valid = wv_primary(p, w, q, &g_idx, &g_sl, &pr, &g_seed);
+                        if (valid) {
+                            uint2 seed = wv_seed_record(p, pr);
+                            ox = pr.o.x; oy = pr.o.y; oz = pr.o.z; dx = pr.d.x; dy = pr.d.y; dz = pr.d.z;
+                            best_t = __uint_as_float(seed.x); seed_id = seed.y;
+                        }
                     } else {
-                        ix = 1.0f / dx; iy = 1.0f / dy; iz = 1.0f / dz; // exact: intersection.rs:152
-                        float e;
-                        if (COUNT) c_box++;
-                        if (cur != EMPTY && !slab(mk(ox, oy, oz), mk(ix, iy, iz), mka(p.root_min), mka(p.root_max), &e)) cur = EMPTY;
+                        float4 a = __ldcs(state + (size_t)q * 4), b = __ldcs(state + (size_t)q * 4 + 1);
+                        uint2 seed = __ldcs(hit + q);
+                        ox = a.x; oy = a.y; oz = a.z; dx = b.x; dy = b.y; dz = b.z;
+                        best_t = __uint_as_float(seed.x); seed_id = seed.y;
                     }
-                    if (cur != EMPTY && (cur & RT_LEAF_FLAG)) { pend = cur; cur = EMPTY; } // the root is a leaf
+                    if (valid) {
+                        slot = q;
+                        limit = best_t * RT_PRUNE_SCALE + RT_PRUNE_ABS;
+                        best_slot = EMPTY; best_pos = 0u; sp = 1; sptr = &s_stack[1][tid]; pend = EMPTY; literal = false;
+                        cur = root_ref == RT_CHILD_ABSENT ? EMPTY : root_ref;
+                        if (POLICY == 2) {
+                            // zero / tiny direction components: neither the certification argument nor the
+                            // FMA slab applies (closest_triangle_rebuilt) -> wv_shade runs the literal policy
+                            if (!(fabsf(dx) >= 1e-30f && fabsf(dy) >= 1e-30f && fabsf(dz) >= 1e-30f)) { literal = true; cur = EMPTY; }
+                            // boxes of the internal tree are conservative (inflated 2^-16 relative), so
+                            // the slab test may use t = b * inv - o * inv with one FMA per plane
+                            ix = 1.0f / dx; iy = 1.0f / dy; iz = 1.0f / dz;
+                            kx = ox * ix; ky = oy * iy; kz = oz * iz;
+                            float e;
+                            if (COUNT) c_box++;
+                            if (cur != EMPTY && !slab_fma(mk(ix, iy, iz), mk(kx, ky, kz), mka(p.broot_min), mka(p.broot_max), &e)) cur = EMPTY;
+                            if (QUANT) {
+                                // tiny components: 2^23 A must stay finite
+                                if (!(fabsf(dx) >= 1e-18f && fabsf(dy) >= 1e-18f && fabsf(dz) >= 1e-18f)) { literal = true; cur = EMPTY; }
+                                const float bx = (p.bq_origin[0] - ox) * ix, by = (p.bq_origin[1] - oy) * iy, bz = (p.bq_origin[2] - oz) * iz;
+                                ix = p.bq_scale[0] * ix; iy = p.bq_scale[1] * iy; iz = p.bq_scale[2] * iz;
+                                kx = __fmaf_rn(-8388608.0f, ix, bx); ky = __fmaf_rn(-8388608.0f, iy, by); kz = __fmaf_rn(-8388608.0f, iz, bz);
+                                snx = dx < 0.0f ? 0x7432u : 0x7410u; sny = dy < 0.0f ? 0x7432u : 0x7410u; snz = dz < 0.0f ? 0x7432u : 0x7410u;
+                            }
+                        } else {
+                            ix = 1.0f / dx; iy = 1.0f / dy; iz = 1.0f / dz; // exact: intersection.rs:152
+                            float e;
+                            if (COUNT) c_box++;
+                            if (cur != EMPTY && !slab(mk(ox, oy, oz), mk(ix, iy, iz), mka(p.root_min), mka(p.root_max), &e)) cur = EMPTY;
+                        }
+                        if (cur != EMPTY && (cur & RT_LEAF_FLAG)) { pend = cur; cur = EMPTY; } // the root is a leaf
+                    } // else: a work item outside the image (edge tiles); the lane stays idle and refills next round
                 }
             }
         }
@@ -248,17 +314,31 @@ __global__ void __launch_bounds__(256, WV_BLOCKS) wv_extend(const __grid_constan
         const int node_min = nl - (nl >> 2) < WV_NODE_MIN ? nl - (nl >> 2) : WV_NODE_MIN;
         for (;;) {
             if (!(cur & RT_LEAF_FLAG)) {
-                const float4* np = nodes + (uint64_t)cur * 4;
                 float4 q0, q1, q2, q3;
+                uint32_t lref, rref;
+                float el, er;
+                bool hl, hr;
+                if (COUNT) c_box += 2;
+                if (QUANT) {
+                    uint32_t qw[8];
+                    ldg_qnode(reinterpret_cast<const uint4*>(reinterpret_cast<const char*>(p.bqnodes) + (uint64_t)cur * 32u), qw);
+                    lref = qw[6]; rref = qw[7];
+#define WV_QF(word, sel) __uint_as_float(__byte_perm((word), 0x4B000000u, (sel)))
+                    el = fmaxf(fmaxf(__fmaf_rn(WV_QF(qw[0], snx), ix, kx), __fmaf_rn(WV_QF(qw[1], sny), iy, ky)), __fmaf_rn(WV_QF(qw[2], snz), iz, kz));
+                    er = fmaxf(fmaxf(__fmaf_rn(WV_QF(qw[3], snx), ix, kx), __fmaf_rn(WV_QF(qw[4], sny), iy, ky)), __fmaf_rn(WV_QF(qw[5], snz), iz, kz));
+                    const float xl = fminf(fminf(__fmaf_rn(WV_QF(qw[0], snx ^ 0x22u), ix, kx), __fmaf_rn(WV_QF(qw[1], sny ^ 0x22u), iy, ky)), __fmaf_rn(WV_QF(qw[2], snz ^ 0x22u), iz, kz));
+                    const float xr = fminf(fminf(__fmaf_rn(WV_QF(qw[3], snx ^ 0x22u), ix, kx), __fmaf_rn(WV_QF(qw[4], sny ^ 0x22u), iy, ky)), __fmaf_rn(WV_QF(qw[5], snz ^ 0x22u), iz, kz));
+#undef WV_QF
+                    hl = xl >= 0.0f && el <= xl;
+                    hr = xr >= 0.0f && er <= xr;
+                } else {
+                const float4* np = nodes + (uint64_t)cur * 4;
 #if WV_L2_KEEP
                 ldg_node_keep(np, keep, q0, q1, q2, q3);
 #else
                 ldg_node(np, q0, q1, q2, q3);
 #endif
-                uint32_t lref = __float_as_uint(q3.x), rref = __float_as_uint(q3.y);
-                float el, er;
-                bool hl, hr;
-                if (COUNT) c_box += 2;
+                lref = __float_as_uint(q3.x); rref = __float_as_uint(q3.y);
                 if (POLICY == 2) {
                     hl = slab_fma(mk(ix, iy, iz), mk(kx, ky, kz), mk(q0.x, q0.y, q0.z), mk(q0.w, q1.x, q1.y), &el);
                     hr = slab_fma(mk(ix, iy, iz), mk(kx, ky, kz), mk(q1.z, q1.w, q2.x), mk(q2.y, q2.z, q2.w), &er);
@@ -266,9 +346,18 @@ __global__ void __launch_bounds__(256, WV_BLOCKS) wv_extend(const __grid_constan
                     hl = slab(mk(ox, oy, oz), mk(ix, iy, iz), mk(q0.x, q0.y, q0.z), mk(q0.w, q1.x, q1.y), &el) && lref != RT_CHILD_ABSENT;
                     hr = slab(mk(ox, oy, oz), mk(ix, iy, iz), mk(q1.z, q1.w, q2.x), mk(q2.y, q2.z, q2.w), &er) && rref != RT_CHILD_ABSENT;
                 }
+                }
                 hl = hl && (el <= limit);
                 hr = hr && (er <= limit);
-                if (hl && hr) {
+                if (!DEEP) { // branch-free step: the stack ops are one predicated shared-memory access each
+                    const bool both = hl && hr, any = hl || hr;
+                    const bool rf = hr && (!hl || er < el); // the right child is the nearer (or the only) one
+                    const uint32_t nearc = rf ? rref : lref, farc = rf ? lref : rref;
+                    if (both) { *sptr = farc; sptr += 256; }
+                    if (!any) sptr -= 256;
+                    const uint32_t top = *sptr; // read only when nothing was hit (predicated)
+                    cur = any ? nearc : top;
+                } else if (hl && hr) {
                     bool right_first = er < el;
                     push(right_first ? lref : rref);
                     cur = right_first ? rref : lref;
@@ -322,13 +411,16 @@ __global__ void __launch_bounds__(256, WV_BLOCKS) wv_extend(const __grid_constan
 }
 
 // ---- shade: SPEC.md steps 3.2-3.8 and 4 for every path of the current depth ----------------
-template <int POLICY, bool COUNT>
+template <int POLICY, bool COUNT, bool GEN>
 __global__ void __launch_bounds__(256) wv_shade(const __grid_constant__ KParams p, WvBuffers w, int qi) {
     const unsigned full = 0xFFFFFFFFu;
     const uint32_t lane = threadIdx.x & 31u;
-    const uint32_t n = w.ctrl->n[qi];
+    const uint32_t n = GEN ? p.n_work * w.spp_wave : w.ctrl->n[qi];
     const float4* __restrict__ tris = POLICY == 2 ? p.btris : p.wtris;
-    if (blockIdx.x == 0 && threadIdx.x == 0) { w.ctrl->head = 0; w.ctrl->segments += n; } // wv_extend of this depth has finished
+    if (blockIdx.x == 0 && threadIdx.x == 0) { // wv_extend of this depth has finished
+        w.ctrl->head = 0;
+        w.ctrl->segments += GEN ? (unsigned long long)w.valid_pixels * w.spp_wave : (unsigned long long)n;
+    }
     const uint32_t n_round = (n + 31u) & ~31u;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += gridDim.x * blockDim.x) {
         bool cont = false;
@@ -336,14 +428,21 @@ __global__ void __launch_bounds__(256) wv_shade(const __grid_constant__ KParams 
         V3 tp = mk(0, 0, 0), L = mk(0, 0, 0);
         SimpleRng rng; rng.seed = 0;
         uint32_t depth = 0, idx = 0, sl = 0;
-        if (i < n) {
-            const float4* st = w.state[qi] + (size_t)i * 4;
-            float4 s0 = __ldcs(st), s1 = __ldcs(st + 1), s2 = __ldcs(st + 2), s3 = __ldcs(st + 3);
+        bool have = i < n;
+        if (GEN) { // the same primary ray the depth-0 extend traced for position i
+            if (have) have = wv_primary(p, w, i, &idx, &sl, &ray, &rng.seed);
+            tp = mk(1.0f, 1.0f, 1.0f);
+        }
+        if (have) {
             uint2 hr = __ldcs(w.hit[qi] + i);
-            ray.o = mk(s0.x, s0.y, s0.z); ray.d = mk(s1.x, s1.y, s1.z);
-            rng.seed = __float_as_uint(s0.w);
-            depth = __float_as_uint(s1.w); idx = __float_as_uint(s2.w); sl = __float_as_uint(s3.w);
-            tp = mk(s2.x, s2.y, s2.z); L = mk(s3.x, s3.y, s3.z);
+            if (!GEN) {
+                const float4* st = w.state[qi] + (size_t)i * 4;
+                float4 s0 = __ldcs(st), s1 = __ldcs(st + 1), s2 = __ldcs(st + 2), s3 = __ldcs(st + 3);
+                ray.o = mk(s0.x, s0.y, s0.z); ray.d = mk(s1.x, s1.y, s1.z);
+                rng.seed = __float_as_uint(s0.w);
+                depth = __float_as_uint(s1.w); idx = __float_as_uint(s2.w); sl = __float_as_uint(s3.w);
+                tp = mk(s2.x, s2.y, s2.z); L = mk(s3.x, s3.y, s3.z);
+            }
             // ---- rebuild the Hit from the record
             Hit h;
             h.t = FLT_MAX; h.kind = 0u; h.prim = 0xFFFFFFFFu; h.material_id = 0xFFFFFFFFu;

@@ -247,6 +247,47 @@ def test_wave_engine_multi_wave(default_ref, monkeypatch):
     compare_path(gpu, ref)
 
 
+def chain_bvh(scene):
+    """Degenerate but valid uploaded tree: internal node 2k = (leaf of triangle k, chain of the rest), so the
+    tree is len(triangles) - 1 levels deep."""
+    n = len(scene.triangles)
+    P, T = scene.vertices["position"], scene.triangles
+    corners = np.stack([P[T["v0_index"]], P[T["v1_index"]], P[T["v2_index"]]], axis=1)  # n x 3 x 3
+    lo, hi = corners.min(axis=1), corners.max(axis=1)
+    nodes = np.zeros(2 * n - 1, dtype=abi.BvhNode)
+    for k in range(n):
+        leaf = 2 * k + 1 if k < n - 1 else 2 * k
+        nodes[leaf]["bounds"]["min"], nodes[leaf]["bounds"]["max"] = lo[k], hi[k]
+        nodes[leaf]["left_child"] = nodes[leaf]["right_child"] = 0xFFFFFFFF
+        nodes[leaf]["triangle_start"], nodes[leaf]["triangle_count"] = k, 1
+        if k < n - 1:
+            nodes[2 * k]["bounds"]["min"], nodes[2 * k]["bounds"]["max"] = lo[k:].min(axis=0), hi[k:].max(axis=0)
+            nodes[2 * k]["left_child"], nodes[2 * k]["right_child"] = 2 * k + 1, 2 * k + 2
+    scene.bvh_nodes, scene.triangle_indices = nodes, np.arange(n, dtype=np.uint32)
+    return scene
+
+
+@pytest.mark.parametrize("variant", [1, 4])
+def test_path_chain_bvh_deeper_than_the_shared_stack(variant):
+    """Cornell box under a 35-level chain tree: the wave engine's extend kernel must take its DEEP form
+    (stack entries beyond the shared-memory column live in local memory)."""
+    s = chain_bvh(g.cornell_scene())
+    ref = ob.render_path(s, 128, 128, spp=4, max_depth=4, base_seed=3)
+    gpu = render_gpu_path(s, 128, 128, 4, 4, base_seed=3, traversal=abi.TRAVERSAL_ORDERED, variant=variant)
+    assert gpu["traversal"] == abi.TRAVERSAL_ORDERED
+    compare_path(gpu, ref)
+
+
+@pytest.mark.parametrize("traversal", [abi.TRAVERSAL_ORDERED, abi.TRAVERSAL_REBUILT])
+def test_wave_engine_forced_deep_form(c3_scene_and_ref, monkeypatch, traversal):
+    """Both policies through the overflow-capable stack form (normally picked only for trees deeper than 30 levels)."""
+    s, _ = c3_scene_and_ref
+    ref = ob.render_path(s, 160, 90, spp=2, max_depth=3, base_seed=8, policy=1)
+    monkeypatch.setenv("RTB200_WAVE_DEEP", "1")
+    gpu = render_gpu_path(s, 160, 90, 2, 3, base_seed=8, traversal=traversal, variant=4)
+    compare_path(gpu, ref)
+
+
 @pytest.mark.parametrize("variant", [1, 2, 3, 4])
 @pytest.mark.parametrize("traversal", [abi.TRAVERSAL_ORDERED, abi.TRAVERSAL_REBUILT])
 def test_c3_path_terrain_1m(c3_scene_and_ref, traversal, variant):
