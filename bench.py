@@ -425,7 +425,13 @@ def run_b200(args, wl, world, rank, local):
     # (the node-fetch instruction) from an L1-resident, an L2-resident and an HBM-resident set
     gather_bw = {"l1_64KiB": ctx.probe_gather_bandwidth(64 << 10), "l2_32MiB": ctx.probe_gather_bandwidth(32 << 20),
                  "hbm_4GiB": ctx.probe_gather_bandwidth(4 << 30)}
-    fetched_per_ray = 64 * (V / 2.0) + 48 * T  # bytes the re-laid-out layout actually loads: 64-B two-child nodes, 48-B triangles
+    # bytes the re-laid-out layout actually loads: two-child nodes (32 B with 16-bit boxes in the wave engine's
+    # rebuilt tree, else 64 B) and 48-B triangles
+    node_bytes = 32 if (wave and ctx.last_traversal == abi.TRAVERSAL_REBUILT) else 64
+    fetched_per_ray = node_bytes * (V / 2.0) + 48 * T
+    # DRAM bytes of the dominant kernel per step from the committed `ncu --set full` capture of this command
+    # (dram__bytes_read.sum + dram__bytes_write.sum, summed over the step's wv_extend launches like `achieved`)
+    ncu_traffic = {"c3": (3.353e9, "profiles/r5_ncu_wv_extend_c3.txt")}.get(args.workload) if (wave and stage_ms and world == 1) else None
     trav_name = {abi.TRAVERSAL_LITERAL: "literal", abi.TRAVERSAL_ORDERED: "ordered (uploaded tree)",
                  abi.TRAVERSAL_REBUILT: "rebuilt (internal LBVH, winners certified against the uploaded tree)"}
     line = {
@@ -446,7 +452,9 @@ def run_b200(args, wl, world, rank, local):
                                              "CUDA IPC) + 4-byte NCCL all-reduce as barrier" if peer is not None else
                                       "NCCL gather of the composite tiles to rank 0")) if world > 1 else "single GPU"},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": None, "kernel": kernel, "peak_source": peak_src,
+                     "traffic": ncu_traffic[0] if ncu_traffic else None,
+                     "traffic_source": ncu_traffic[1] if ncu_traffic else None,
+                     "kernel": kernel, "peak_source": peak_src,
                      "bytes_per_ray": kernel_bytes_per_ray, "step_bytes_per_ray": bytes_per_ray,
                      "box_tests_per_ray": V, "tri_tests_per_ray": T, "kernel_ms": mean_ms,
                      "kernel_share_of_step": mean_ms / (total_ms / args.steps) if world == 1 else None,
@@ -460,8 +468,11 @@ def run_b200(args, wl, world, rank, local):
                      "note": "achieved = algorithmic reference-layout bytes per ray segment of this kernel (closest hit: "
                              "48 V + 56 T + 20 S; megakernels add 128 H + 52 L H + output stores) x segments / its launch "
                              "time; V/T counted by an instrumented launch of the same kernels; the scene fits the 126 MB "
-                             "L2, so achieved can exceed the HBM copy peak: the binding unit is the SM's L1 data stage "
-                             "(one 32-B sector per lane per cycle for divergent gathers), see frac_of_l1_gather"},
+                             "L2, so achieved can exceed the HBM copy peak and DRAM traffic is far below the algorithmic "
+                             "bytes: the kernel is bound on chip.  fetched_gbs / frac_of_l1_gather compare the node and "
+                             "triangle sectors it really loads with the measured rate of divergent 32-B gathers from L1; "
+                             "with one-sector nodes ncu shows the issue slots (65-75 % active, 20 of 32 lanes per "
+                             "instruction) ahead of the L1 data stage (47-62 %), see DESIGN.md section 5"},
         "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": h2d_bytes,
                 "d2h_bytes_per_step": int(host_img.nbytes), "ms_per_step": e2e_total / args.steps},
         "gpu_launches": int(launches), "clocks": clk, "rank_frame_ms": rank_kernel_ms,

@@ -101,6 +101,7 @@ struct RtContext {
     DevBuf<uint2> lb_children, lb_range;
     DevBuf<float4> pbox, lb_nbox, bnodes, btris;
     DevBuf<uint4> bqnodes;   // 32-byte quantised copy of bnodes (wave engine)
+    DevBuf<float4> cert_box; // [2 * uploaded node]: boxes of the uploaded leaves (REBUILT certification)
     DevBuf<float> lb_grid;   // its grid: origin[3], cell[3]
     float bq_grid[6] = {0, 0, 0, 1, 1, 1};
     uint32_t lbvh_depth = 0; // levels of the internal tree (picks the wave engine's stack form)
@@ -287,12 +288,22 @@ __global__ void relayout_triangles(const uint32_t* __restrict__ meta, RtSceneMet
     if (pbox) { pbox[(uint64_t)pos * 2] = blo; pbox[(uint64_t)pos * 2 + 1] = bhi; }
 }
 // One warp per leaf: remaining[start + i] = count - i.
+// cert_box (REBUILT policy only): the leaf's uploaded box as two aligned float4 at [2 * node], the same
+// words the certification would otherwise gather one by one from the metadata buffer.
 __global__ void relayout_leaf_counts(const uint2* __restrict__ leaves, const uint32_t* __restrict__ leaf_nodes,
-                                     uint32_t n_leaves, float4* __restrict__ out, uint32_t* __restrict__ leaf_of_pos) {
+                                     uint32_t n_leaves, float4* __restrict__ out, uint32_t* __restrict__ leaf_of_pos,
+                                     const uint32_t* __restrict__ meta, uint64_t meta_len, uint32_t nodes_offset,
+                                     float4* __restrict__ cert_box) {
     uint32_t leaf = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31u;
     if (leaf >= n_leaves) return;
     uint2 l = leaves[leaf];
     uint32_t node = leaf_nodes[leaf];
+    if (cert_box && lane < 2u) {
+        uint64_t o = (uint64_t)nodes_offset + (uint64_t)node * 12 + lane * 4u;
+        float v[3];
+        for (int k = 0; k < 3; k++) v[k] = o + k < meta_len ? __uint_as_float(meta[o + k]) : 0.0f;
+        cert_box[(uint64_t)node * 2 + lane] = make_float4(v[0], v[1], v[2], 0.0f);
+    }
     for (uint32_t i = lane; i < l.y; i += 32u) {
         reinterpret_cast<uint32_t*>(out + (uint64_t)(l.x + i) * 3 + 2)[3] = l.y - i;
         leaf_of_pos[l.x + i] = node;
@@ -646,7 +657,8 @@ int prepare_relayout(RtContext* c) {
         cudaEvent_t e0 = c->ev0, e1 = c->ev1;
         CK(c, cudaEventRecord(e0, c->stream));
         if (c->wtris.reserve((size_t)ni * 3 + 3) < 0 || c->leaf_of_pos.reserve((size_t)ni + 1) < 0 ||
-            (want_rebuilt && c->pbox.reserve((size_t)ni * 2 + 2) < 0))
+            (want_rebuilt && (c->pbox.reserve((size_t)ni * 2 + 2) < 0 ||
+                              c->cert_box.reserve((size_t)c->offsets.bvh_nodes_count * 2 + 2) < 0)))
             return fail(c, RT_ERR_CUDA, "relayout cudaMalloc failed");
         CK(c, cudaMemsetAsync(c->dflag.ptr, 0, 4, c->stream));
         CK(c, cudaMemsetAsync(c->leaf_of_pos.ptr, 0xFF, ((size_t)ni + 1) * 4, c->stream));
@@ -658,7 +670,9 @@ int prepare_relayout(RtContext* c) {
             uint32_t nl = (uint32_t)c->wide.leaves.size();
             if (nl) {
                 relayout_leaf_counts<<<(nl * 32 + 255) / 256, 256, 0, c->stream>>>(c->wleaves.ptr, c->wleaf_nodes.ptr, nl,
-                                                                                   c->wtris.ptr, c->leaf_of_pos.ptr);
+                                                                                   c->wtris.ptr, c->leaf_of_pos.ptr, c->meta.ptr,
+                                                                                   c->meta_len, c->offsets.bvh_nodes_offset,
+                                                                                   want_rebuilt ? c->cert_box.ptr : nullptr);
                 c->launches++;
             }
         }
@@ -691,6 +705,7 @@ void fill_scene(RtContext* c, KParams& k) {
     k.bnodes = c->bnodes.ptr; k.btris = c->btris.ptr; k.leaf_of_pos = c->leaf_of_pos.ptr;
     k.broot_ref = c->broot_ref;
     memcpy(k.broot_min, c->broot_min, 12); memcpy(k.broot_max, c->broot_max, 12);
+    k.cert_box = c->cert_box.ptr;
     k.bqnodes = c->bqnodes.ptr; memcpy(k.bq_origin, c->bq_grid, 12); memcpy(k.bq_scale, c->bq_grid + 3, 12);
     k.accum = c->accum.ptr; k.hits = c->hits.ptr;
     for (int i = 0; i < 3; i++) k.chan[i] = c->chan[i].ptr;

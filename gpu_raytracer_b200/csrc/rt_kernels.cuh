@@ -66,6 +66,7 @@ struct KParams {
     const uint32_t* leaf_of_pos;   // uploaded leaf node of every triangle_indices position
     uint32_t broot_ref;
     float broot_min[3], broot_max[3];
+    const float4* cert_box;        // [2 * uploaded node]: (min, max) of the uploaded leaves, aligned copies of the metadata words
     const uint4* bqnodes;          // the same tree as 2 x uint4 per node: 16-bit boxes on the grid below (rt_lbvh.cuh)
     float bq_origin[3], bq_scale[3];
     // outputs

@@ -106,13 +106,17 @@ __device__ __forceinline__ uint2 wv_seed_record(const KParams& p, const Ray& ray
 // jitter draws (SPEC.md steps 1-2).  Warp-sized runs of q are one 8x4 pixel group for one sample, consecutive
 // runs the samples of that group.  Used by wv_generate, or (WV_FUSE_GEN) by the depth-0 extend and shade
 // launches themselves, which then never materialise the 64-byte primary path records.
-__device__ __forceinline__ bool wv_primary(const KParams& p, const WvBuffers& w, uint32_t q, uint32_t* idx, uint32_t* sl,
-                                           Ray* ray, uint32_t* rng_seed) {
+__device__ __forceinline__ bool wv_primary_index(const KParams& p, const WvBuffers& w, uint32_t q, uint32_t* idx, uint32_t* sl,
+                                                 uint32_t* px, uint32_t* py) {
     const uint32_t wi = q >> 5, group = wi / w.spp_wave;
     *sl = wi - group * w.spp_wave;
     *idx = group * 32u + (q & 31u);
+    return work_to_pixel(p, *idx, px, py);
+}
+__device__ __forceinline__ bool wv_primary(const KParams& p, const WvBuffers& w, uint32_t q, uint32_t* idx, uint32_t* sl,
+                                           Ray* ray, uint32_t* rng_seed) {
     uint32_t px = 0, py = 0;
-    if (!work_to_pixel(p, *idx, &px, &py)) return false;
+    if (!wv_primary_index(p, w, q, idx, sl, &px, &py)) return false;
     const uint32_t s = w.s0 + *sl;
     SimpleRng rng; rng.seed = p.base_seed + s + px + py * p.width;
     float jx = 0.5f, jy = 0.5f;
@@ -412,7 +416,7 @@ __global__ void __launch_bounds__(256, WV_BLOCKS) wv_extend(const __grid_constan
 
 // ---- shade: SPEC.md steps 3.2-3.8 and 4 for every path of the current depth ----------------
 template <int POLICY, bool COUNT, bool GEN>
-__global__ void __launch_bounds__(256) wv_shade(const __grid_constant__ KParams p, WvBuffers w, int qi) {
+__global__ void __launch_bounds__(256, 3) wv_shade(const __grid_constant__ KParams p, WvBuffers w, int qi) {
     const unsigned full = 0xFFFFFFFFu;
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t n = GEN ? p.n_work * w.spp_wave : w.ctrl->n[qi];
@@ -421,20 +425,86 @@ __global__ void __launch_bounds__(256) wv_shade(const __grid_constant__ KParams 
         w.ctrl->head = 0;
         w.ctrl->segments += GEN ? (unsigned long long)w.valid_pixels * w.spp_wave : (unsigned long long)n;
     }
+    // Paths whose ray left the scene (on open scenes most of depth >= 1) only add the sky term; if they shared
+    // warps with the hits, the shading code would run with a handful of lanes (ncu: 7 of 32 at depth 1 of C3).
+    // Every warp owns a small queue in shared memory: phase A of each 32-path chunk finishes the misses and queues
+    // the others; phase B runs the full shading on 32 queued paths at a time, in queue order.  Warps never wait
+    // for each other (a dense chunk goes straight through: 32 queued, 32 shaded).
+    // A queue entry is (path, hit record); the hit records of the next chunk are loaded before the current one is
+    // shaded, so the only global-memory wait on the dense path stays the path-state load of phase B.
+    __shared__ uint32_t s_list[8][3][64];
+    uint32_t (*const my_list)[64] = s_list[threadIdx.x >> 5];
+    uint32_t queued_now = 0; // warp-uniform
     const uint32_t n_round = (n + 31u) & ~31u;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += gridDim.x * blockDim.x) {
+    const uint32_t warp_stride = gridDim.x * 256u;
+    const uint32_t first = blockIdx.x * 256u + (threadIdx.x & ~31u);
+    uint2 hr_next = make_uint2(0u, WV_ID_MISS);
+    if (first + lane < n) hr_next = __ldcs(w.hit[qi] + first + lane);
+    for (uint32_t base = first; base < n_round; base += warp_stride) {
+        {   // ---- phase A
+            const uint32_t i = base + lane;
+            const uint2 hr = hr_next;
+            if (i + warp_stride < n && i + warp_stride > i) hr_next = __ldcs(w.hit[qi] + i + warp_stride);
+            bool heavy = false;
+            if (i < n) {
+                uint32_t idx = 0, sl = 0, px = 0, py = 0, depth = 0;
+                bool valid = true;
+                if (GEN) valid = wv_primary_index(p, w, i, &idx, &sl, &px, &py);
+                if (valid) {
+                    if (hr.y != WV_ID_MISS) heavy = true;
+                    else {
+                        V3 tp = mk(1.0f, 1.0f, 1.0f), L = mk(0.0f, 0.0f, 0.0f);
+                        if (!GEN) {
+                            const float4* st = w.state[qi] + (size_t)i * 4;
+                            const float4 s2 = __ldcs(st + 2), s3 = __ldcs(st + 3);
+                            tp = mk(s2.x, s2.y, s2.z); idx = __float_as_uint(s2.w);
+                            L = mk(s3.x, s3.y, s3.z); sl = __float_as_uint(s3.w);
+                            if (p.outputs & RT_OUT_HITS) depth = __float_as_uint(__ldcs(st + 1).w);
+                        }
+                        if (depth == 0u && w.s0 + sl == 0u && (p.outputs & RT_OUT_HITS)) {
+                            if (!GEN) work_to_pixel(p, idx, &px, &py);
+                            reinterpret_cast<uint4*>(p.hits)[(size_t)py * p.width + px] = make_uint4(0u, 0xFFFFFFFFu, __float_as_uint(FLT_MAX), 0xFFFFFFFFu);
+                        }
+                        L = L + mk(0.1f, 0.2f, 0.3f) * tp;
+                        WV_ST(w.lbuf + (size_t)sl * p.n_work + idx, make_float4(L.x, L.y, L.z, 1.0f));
+                    }
+                }
+            }
+            const unsigned hm = __ballot_sync(full, heavy);
+            if (heavy) {
+                const uint32_t e = queued_now + (uint32_t)__popc(hm & ((1u << lane) - 1u));
+                my_list[0][e] = i; my_list[1][e] = hr.x; my_list[2][e] = hr.y;
+            }
+            queued_now += (uint32_t)__popc(hm);
+            __syncwarp();
+        }
+        // ---- phase B: 32 queued paths at a time; after the warp's last chunk until its queue is empty
+        const bool last_chunk = base + warp_stride >= n_round;
+        for (;;) {
+        const uint32_t queued = queued_now;
+        if (!(queued >= 32u || (last_chunk && queued > 0u))) break;
+        const uint32_t take = queued < 32u ? queued : 32u;
+        bool have = lane < take;
+        const uint32_t i = have ? my_list[0][lane] : 0u;
+        const uint2 hr = have ? make_uint2(my_list[1][lane], my_list[2][lane]) : make_uint2(0u, WV_ID_MISS);
+        if (queued > 32u) { // the rest moves to the front
+            const bool mv = lane + 32u < queued;
+            const uint32_t m0 = mv ? my_list[0][lane + 32u] : 0u, m1 = mv ? my_list[1][lane + 32u] : 0u, m2 = mv ? my_list[2][lane + 32u] : 0u;
+            __syncwarp();
+            if (mv) { my_list[0][lane] = m0; my_list[1][lane] = m1; my_list[2][lane] = m2; }
+        }
+        queued_now = queued - take;
+        __syncwarp(); // the next chunk's phase A appends behind the moved entries
         bool cont = false;
         Ray ray; ray.o = mk(0, 0, 0); ray.d = mk(0, 0, 1);
         V3 tp = mk(0, 0, 0), L = mk(0, 0, 0);
         SimpleRng rng; rng.seed = 0;
         uint32_t depth = 0, idx = 0, sl = 0;
-        bool have = i < n;
         if (GEN) { // the same primary ray the depth-0 extend traced for position i
             if (have) have = wv_primary(p, w, i, &idx, &sl, &ray, &rng.seed);
             tp = mk(1.0f, 1.0f, 1.0f);
         }
         if (have) {
-            uint2 hr = __ldcs(w.hit[qi] + i);
             if (!GEN) {
                 const float4* st = w.state[qi] + (size_t)i * 4;
                 float4 s0 = __ldcs(st), s1 = __ldcs(st + 1), s2 = __ldcs(st + 2), s3 = __ldcs(st + 3);
@@ -459,11 +529,10 @@ __global__ void __launch_bounds__(256) wv_shade(const __grid_constant__ KParams 
                 b.mat = __float_as_uint(d.y); b.prim = __float_as_uint(d.z);
                 if (POLICY == 2) { // certification against the uploaded tree (see closest_triangle_rebuilt)
                     uint32_t leaf = __ldg(p.leaf_of_pos + __float_as_uint(d.w));
-                    uint64_t no = (uint64_t)p.off.bvh_nodes_offset + (uint64_t)leaf * 12;
+                    const float4 blo = __ldg(p.cert_box + (uint64_t)leaf * 2), bhi = __ldg(p.cert_box + (uint64_t)leaf * 2 + 1);
                     V3 inv = mk(1.0f / ray.d.x, 1.0f / ray.d.y, 1.0f / ray.d.z);
                     float entry;
-                    lit = !slab(ray.o, inv, mk(meta_f(p, no), meta_f(p, no + 1), meta_f(p, no + 2)),
-                                mk(meta_f(p, no + 4), meta_f(p, no + 5), meta_f(p, no + 6)), &entry);
+                    lit = !slab(ray.o, inv, mk(blo.x, blo.y, blo.z), mk(bhi.x, bhi.y, bhi.z), &entry);
                 }
             }
             float sphere_seed = FLT_MAX - 2.0f;
@@ -562,6 +631,7 @@ __global__ void __launch_bounds__(256) wv_shade(const __grid_constant__ KParams 
                 WV_ST(w.hit[qi ^ 1] + ns, wv_seed_record(p, ray));
             }
         }
+        } // phase B
     }
 }
 

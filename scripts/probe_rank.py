@@ -14,3 +14,5 @@ for rep in range(5):
     ctx.synchronize(); best = min(best, ctx.last_kernel_ms)
 print("stride %d phase %d spp %d split %s: %.3f ms, %d segments, %.1f Mrays/s" %
       (stride, phase, spp, os.environ.get("RTB200_WAVE_SPLIT", "default"), best, ctx.last_segments, ctx.last_segments / best / 1e3), flush=True)
+if os.environ.get("RTB200_WAVE_SPLIT") == "1":
+    print("   stages:", {k: (round(v, 3) if isinstance(v, float) else v) for k, v in ctx.last_stage_ms().items()}, flush=True)

@@ -288,6 +288,54 @@ def test_wave_engine_forced_deep_form(c3_scene_and_ref, monkeypatch, traversal):
     compare_path(gpu, ref)
 
 
+def transformed_terrain(scale=1.0, offset=(0.0, 0.0, 0.0), flatten=False, camera_back=0.0):
+    """Chunked-BVH terrain (100-triangle leaves -> REBUILT policy) under a similarity transform of the scene,
+    lights and camera: exercises the 16-bit node grid of the wave engine far from the unit-scale default."""
+    s = g.terrain_scene(120, 90, strategy=None)
+    off = np.asarray(offset, np.float32)
+    P = s.vertices["position"]
+    if flatten:
+        P[:, 1] = 0.0
+    s.vertices["position"] = P * np.float32(scale) + off
+    s.lights["position"] = s.lights["position"] * np.float32(scale) + off
+    cam = s.camera.copy()
+    pos = cam["position"] * np.float32(scale) + off
+    cam["position"] = pos - cam["direction"] * np.float32(camera_back * scale)
+    s.camera = cam
+    return s.rebuild_bvh(abi.BVH_CHUNKED)
+
+
+@pytest.mark.parametrize("name,kw", [
+    ("offset", dict(offset=(5000.0, -3000.0, 8000.0))),   # extent << |coordinates|: the pad dominates the grid cell
+    ("tiny", dict(scale=0.02)),
+    ("huge", dict(scale=1e3)),
+    ("flat", dict(flatten=True)),                          # zero extent along y: degenerate grid axis
+    ("far_camera", dict(camera_back=300.0)),               # ray origins 3 scene extents away, terrain covers 7 % of the frame
+    ("very_far_camera", dict(camera_back=1000.0)),         # 10 extents: a few dozen pixels hit
+])
+def test_rebuilt_policy_quantised_nodes_under_transforms(name, kw):
+    s = transformed_terrain(**kw)
+    assert s.bvh_nodes["triangle_count"].max() > 4
+    ref = ob.render_path(s, 160, 90, spp=2, max_depth=3, base_seed=12, policy=1)
+    gpu = render_gpu_path(s, 160, 90, 2, 3, base_seed=12, traversal=abi.TRAVERSAL_REBUILT, variant=4)
+    assert gpu["traversal"] == abi.TRAVERSAL_REBUILT
+    compare_path(gpu, ref)
+
+
+def test_wave_engine_equals_megakernel_at_scale(c3_scene_and_ref):
+    """A frame large enough that every block of the wave engine's kernels loops over many chunks (persistent
+    work fetch, queued shading, several survivors per block): segments, radiance and image must equal the
+    megakernel's (which the oracle pins at small sizes) bit for bit, run to run."""
+    s, _ = c3_scene_and_ref
+    a = render_gpu_path(s, 1280, 720, 4, 4, base_seed=3, variant=1)
+    for _ in range(2):
+        b = render_gpu_path(s, 1280, 720, 4, 4, base_seed=3, variant=4)
+        assert a["segments"] == b["segments"]
+        assert np.array_equal(a["accum"].view(np.uint32), b["accum"].view(np.uint32))
+        assert np.array_equal(a["composite"], b["composite"])
+        assert np.array_equal(a["hits"], b["hits"])
+
+
 @pytest.mark.parametrize("variant", [1, 2, 3, 4])
 @pytest.mark.parametrize("traversal", [abi.TRAVERSAL_ORDERED, abi.TRAVERSAL_REBUILT])
 def test_c3_path_terrain_1m(c3_scene_and_ref, traversal, variant):
