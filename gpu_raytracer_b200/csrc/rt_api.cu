@@ -880,11 +880,14 @@ static WvKernel wv_extend_kernel(int policy, bool count, bool gen, bool deep) {
     if (policy == 2) return deep ? wv_extend_pick<2, true>(count, gen) : wv_extend_pick<2, false>(count, gen);
     return deep ? wv_extend_pick<1, true>(count, gen) : wv_extend_pick<1, false>(count, gen);
 }
-static WvKernel wv_shade_kernel(int policy, bool count, bool gen) {
-    static const WvKernel t[2][2][2] = {
-        {{wv_shade<1, false, false>, wv_shade<1, false, true>}, {wv_shade<1, true, false>, wv_shade<1, true, true>}},
-        {{wv_shade<2, false, false>, wv_shade<2, false, true>}, {wv_shade<2, true, false>, wv_shade<2, true, true>}}};
-    return t[policy - 1][count ? 1 : 0][gen ? 1 : 0];
+template <int P, bool S>
+static WvKernel wv_shade_pick(bool count, bool gen) {
+    if (count) return gen ? wv_shade<P, true, true, S> : wv_shade<P, true, false, S>;
+    return gen ? wv_shade<P, false, true, S> : wv_shade<P, false, false, S>;
+}
+static WvKernel wv_shade_kernel(int policy, bool count, bool gen, bool split) {
+    if (policy == 2) return split ? wv_shade_pick<2, true>(count, gen) : wv_shade_pick<2, false>(count, gen);
+    return split ? wv_shade_pick<1, true>(count, gen) : wv_shade_pick<1, false>(count, gen);
 }
 
 int launch_wave(RtContext* c, KParams k, uint32_t traversal) {
@@ -988,9 +991,11 @@ int launch_wave(RtContext* c, KParams k, uint32_t traversal) {
                 const bool gen = WV_FUSE_GEN && d == 0u; // depth 0 computes its primary rays from the queue position
                 wv_extend_kernel(policy, count, gen, deep)<<<ext_blocks, 256, 0, st>>>(ks, w, qi);
                 mark(1);
-                wv_shade_kernel(policy, count, gen)<<<stream_blocks, 256, 0, st>>>(ks, w, qi);
+                // both forms are launched; the one that does not match the depth's miss ratio returns at once
+                wv_shade_kernel(policy, count, gen, false)<<<stream_blocks, 256, 0, st>>>(ks, w, qi);
+                wv_shade_kernel(policy, count, gen, true)<<<stream_blocks, 256, 0, st>>>(ks, w, qi);
                 mark(2);
-                c->launches += 2;
+                c->launches += 3;
             }
             wv_resolve<<<stream_blocks, 256, 0, st>>>(ks, w);
             mark(3);

@@ -84,6 +84,12 @@ typedef struct RtFrameParams {
                             * wavefront, 3 state-machine megakernel, 4 streaming wavefront); [1]: 0 */
 } RtFrameParams;
 
+/* Environment switches read by rt_render_frame (tuning and tests only; results never change):
+ *   RTB200_WAVE_SPLIT=1..4  sub-frames of the streaming wavefront engine (default 2; 1 enables rt_last_stage_ms)
+ *   RTB200_WAVE_PATHS=N     paths in flight per wave (default 40 M)
+ *   RTB200_WAVE_DEEP=1      force the traversal-stack form used for trees deeper than 30 levels
+ *   RTB200_DEBUG=1          print the internal tree's size and depth at upload */
+
 /* ---- context: stands in for RenderState.device/queue + the three output
  * textures (src/renderer.rs:93-246, 452-475) and BufferManager::new
  * (src/buffers.rs:66-154). */
