@@ -431,7 +431,7 @@ def run_b200(args, wl, world, rank, local):
     fetched_per_ray = node_bytes * (V / 2.0) + 48 * T
     # DRAM bytes of the dominant kernel per step from the committed `ncu --set full` capture of this command
     # (dram__bytes_read.sum + dram__bytes_write.sum, summed over the step's wv_extend launches like `achieved`)
-    ncu_traffic = {"c3": (3.353e9, "profiles/r5_ncu_wv_extend_c3.txt")}.get(args.workload) if (wave and stage_ms and world == 1) else None
+    ncu_traffic = {"c3": (3.356e9, "profiles/r8_ncu_wv_extend_c3.txt")}.get(args.workload) if (wave and stage_ms and world == 1) else None
     trav_name = {abi.TRAVERSAL_LITERAL: "literal", abi.TRAVERSAL_ORDERED: "ordered (uploaded tree)",
                  abi.TRAVERSAL_REBUILT: "rebuilt (internal LBVH, winners certified against the uploaded tree)"}
     line = {
