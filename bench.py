@@ -39,6 +39,9 @@ WORKLOADS = {
     "c3-primary-smallleaf": dict(nx=1000, nz=500, w=1920, h=1080, bvh="small_leaf", mode="primary", spp=1, depth=0,
                                  desc="C3 scene, primary rays + direct shading, small-leaf BVH (<=4 tris/leaf) in "
                                       "the reference node format"),
+    "c3-smallleaf": dict(nx=1000, nz=500, w=1920, h=1080, bvh="small_leaf", mode="path", spp=16, depth=4,
+                         desc="C3 with the scene uploaded as a small-leaf BVH (<=4 tris/leaf, binned SAH, reference node "
+                              "format; SURVEY 8f #1): 1M-triangle terrain, 1920x1080, 4 bounces, 16 spp (EXTENSION semantics)"),
     "c4": dict(scene="cornell", w=1024, h=1024, bvh="auto", mode="path", spp=64, depth=8,
                desc="C4: Cornell box (36 triangles), 1024x1024, diffuse bounces to depth 8, 64 spp (EXTENSION "
                     "semantics, SPEC.md) - divergence stress"),
