@@ -18,6 +18,9 @@
 #ifndef RT_LBVH_LEAF
 #define RT_LBVH_LEAF 2u
 #endif
+#ifndef RT_LBVH_FLAT
+#define RT_LBVH_FLAT 0.125f // an axis whose centroid extent is below this fraction of the largest one is left out of the Morton code (0: never)
+#endif
 // REBUILT leaf ref: bit31 | (count-1) << 28 | first sorted slot (28 bits)
 #define RT_LBVH_MAX_PRIMS (1u << 28)
 
@@ -70,15 +73,30 @@ __global__ void morton_keys(const float4* __restrict__ pbox, uint32_t n, const u
     // flat scene (terrain: y extent << x, z extents) is split in x/z only until the cells are as
     // small as its height range.  Per-axis normalisation would spend every third split on height
     // slices that overlap completely in x/z (measured on C3: 92.6 -> see DESIGN.md box tests/ray).
-    float ext = 0.0f;
-    for (int k = 0; k < 3; k++) ext = fmaxf(ext, ord2f(bounds[3 + k]) - ord2f(bounds[k]));
+    float ext = 0.0f, ek[3];
+    for (int k = 0; k < 3; k++) { ek[k] = ord2f(bounds[3 + k]) - ord2f(bounds[k]); ext = fmaxf(ext, ek[k]); }
+    uint32_t axes = 0u; // axes that take part in the code
     for (int k = 0; k < 3; k++) {
         float mn = ord2f(bounds[k]);
         float u = ext > 0.0f ? (c[k] - mn) / ext : 0.0f;
         u = fminf(fmaxf(u, 0.0f), 1.0f);
         q[k] = (unsigned long long)min(2097151.0f, u * 2097152.0f);
+        if (ek[k] >= ext * RT_LBVH_FLAT) axes |= 1u << k;
     }
-    keys[i] = expand21(q[0]) << 2 | expand21(q[1]) << 1 | expand21(q[2]);
+    if (axes == 7u) keys[i] = expand21(q[0]) << 2 | expand21(q[1]) << 1 | expand21(q[2]);
+    else {
+        // A sheet-like scene (terrain: the height range is a small fraction of the ground extents) is a 2-D
+        // manifold: inside a Morton cell of side s the surface spans much less than s in the thin axis, so a
+        // split across that axis leaves two children with the same footprint (SAH: worse than halving the
+        // footprint as long as the cell is wider than its content is tall).  Such axes are left out of the
+        // code altogether; the remaining ones interleave as before.  Oracle-counted on the terrain scenes:
+        // 7 % fewer box tests per ray at the same triangle tests (scripts/tree_study.py).
+        unsigned long long key = 0ull;
+        for (int b = 20; b >= 0; b--)
+            for (int k = 0; k < 3; k++)
+                if (axes >> k & 1u) key = key << 1 | (q[k] >> b & 1ull);
+        keys[i] = key;
+    }
     vals[i] = i;
 }
 
