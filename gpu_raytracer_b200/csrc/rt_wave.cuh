@@ -88,15 +88,6 @@ struct WvBuffers {
 #ifndef WV_BLOCKS
 #define WV_BLOCKS 4        // resident 256-thread blocks per SM the extend kernel is compiled for
 #endif
-#ifndef WV_SHADE_BLOCKS
-#define WV_SHADE_BLOCKS 3  // resident 256-thread blocks per SM wv_shade is compiled for
-#endif
-#ifndef WV_TRI_PAIR
-#define WV_TRI_PAIR 0      // 1: REBUILT leaves load two triangles before the first test (one exposed load latency per pair)
-#endif
-#ifndef WV_TRI_PREFETCH
-#define WV_TRI_PREFETCH 0  // 1: a lane that postpones a leaf prefetches its first triangle into L1
-#endif
 
 // spheres first (shader/src/lib.rs:183-190, 252-269): returns the seed t and the sphere index
 __device__ __forceinline__ void wv_sphere_seed(const KParams& p, const Ray& ray, float* closest, uint32_t* sphere_idx) {
@@ -386,12 +377,7 @@ __global__ void __launch_bounds__(256, WV_BLOCKS) wv_extend(const __grid_constan
                 } else if (hl) cur = lref;
                 else if (hr) cur = rref;
                 else cur = pop();
-                if (WV_SPEC && (cur & RT_LEAF_FLAG) && cur != EMPTY && pend == EMPTY) {
-                    pend = cur; cur = pop();
-#if WV_TRI_PREFETCH
-                    asm volatile("prefetch.global.L1 [%0];" :: "l"(tris + (uint64_t)(POLICY == 2 ? (pend & 0x0FFFFFFFu) : (pend & ~RT_LEAF_FLAG)) * 3));
-#endif
-                }
+                if (WV_SPEC && (cur & RT_LEAF_FLAG) && cur != EMPTY && pend == EMPTY) { pend = cur; cur = pop(); }
             }
             if (__popc(__ballot_sync(full, !(cur & RT_LEAF_FLAG))) < node_min) break;
         }
@@ -403,28 +389,7 @@ __global__ void __launch_bounds__(256, WV_BLOCKS) wv_extend(const __grid_constan
                 uint32_t ts = POLICY == 2 ? (leaf & 0x0FFFFFFFu) : (leaf & ~RT_LEAF_FLAG);
                 uint32_t rem = POLICY == 2 ? ((leaf >> 28) & 7u) + 1u : 0u;
                 Ray ray; ray.o = mk(ox, oy, oz); ray.d = mk(dx, dy, dz);
-                // strict `t < closest` in visit order; with re-ordered visits the equal-t winner is
-                // the smaller triangle_indices position (== first in the reference's DFS order)
-                auto accept = [&](float t, uint32_t tslot, uint32_t pos) {
-                    if (t > 0.0f && (t < best_t || (t == best_t && best_slot != EMPTY && pos < best_pos))) {
-                        best_t = t; best_slot = tslot; best_pos = pos;
-                        limit = best_t * RT_PRUNE_SCALE + RT_PRUNE_ABS;
-                    }
-                };
-                if (POLICY == 2 && WV_TRI_PAIR) for (;;) { // same tests in the same order, loads of a pair issued together
-                    const float4* tpn = tris + (uint64_t)ts * 3;
-                    const bool two = rem > 1u;
-                    float4 a = __ldg(tpn), c = __ldg(tpn + 1), d = __ldg(tpn + 2);
-                    float4 a2 = a, c2 = c, d2 = d;
-                    if (two) { a2 = __ldg(tpn + 3); c2 = __ldg(tpn + 4); d2 = __ldg(tpn + 5); }
-                    if (COUNT) c_tri += two ? 2u : 1u;
-                    accept(triangle_t(ray, mk(a.x, a.y, a.z), mk(a.w, c.x, c.y), mk(c.z, c.w, d.x)), ts, __float_as_uint(d.w));
-                    if (!two) break;
-                    accept(triangle_t(ray, mk(a2.x, a2.y, a2.z), mk(a2.w, c2.x, c2.y), mk(c2.z, c2.w, d2.x)), ts + 1u, __float_as_uint(d2.w));
-                    if (rem <= 2u) break;
-                    rem -= 2u; ts += 2u;
-                }
-                else for (;;) {
+                for (;;) {
                     const float4* tpn = tris + (uint64_t)ts * 3;
 #if WV_L2_KEEP
                     float4 a = ldg_keep(tpn, keep), c = ldg_keep(tpn + 1, keep), d = ldg_keep(tpn + 2, keep);
@@ -434,7 +399,12 @@ __global__ void __launch_bounds__(256, WV_BLOCKS) wv_extend(const __grid_constan
                     float t = triangle_t(ray, mk(a.x, a.y, a.z), mk(a.w, c.x, c.y), mk(c.z, c.w, d.x));
                     uint32_t pos = POLICY == 2 ? __float_as_uint(d.w) : ts;
                     if (COUNT) c_tri++;
-                    accept(t, ts, pos);
+                    // strict `t < closest` in visit order; with re-ordered visits the equal-t winner is
+                    // the smaller triangle_indices position (== first in the reference's DFS order)
+                    if (t > 0.0f && (t < best_t || (t == best_t && best_slot != EMPTY && pos < best_pos))) {
+                        best_t = t; best_slot = ts; best_pos = pos;
+                        limit = best_t * RT_PRUNE_SCALE + RT_PRUNE_ABS;
+                    }
                     if (POLICY == 2) { if (--rem == 0u) break; }
                     else if (__float_as_uint(d.w) <= 1u) break;
                     ts++;
@@ -461,7 +431,7 @@ __global__ void __launch_bounds__(256, WV_BLOCKS) wv_extend(const __grid_constan
 // quarter of the rays left the scene.  Results are identical either way; on a closed scene the queueing only
 // costs (Cornell box: 5 % of the frame), on the open terrain it saves a sixth of the shading time.
 template <int POLICY, bool COUNT, bool GEN, bool SPLIT>
-__global__ void __launch_bounds__(256, WV_SHADE_BLOCKS) wv_shade(const __grid_constant__ KParams p, WvBuffers w, int qi) {
+__global__ void __launch_bounds__(256, 3) wv_shade(const __grid_constant__ KParams p, WvBuffers w, int qi) {
     const unsigned full = 0xFFFFFFFFu;
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t n = GEN ? p.n_work * w.spp_wave : w.ctrl->n[qi];

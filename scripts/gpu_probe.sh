@@ -9,9 +9,13 @@ O=gpurun_out/$TAG
 mkdir -p $O
 P=$O/probe.log
 : > $P
-for v in $BASE $VARIANTS $BASE; do
-    RTB200_LIB=$PWD/build/tune/$v.so timeout 240 python scripts/probe.py $WORK >> $P 2>&1
+# a variant whose probe fails or hangs (PROBE_TIMEOUT seconds) ends the variant loop: the rest share its code
+for v in $BASE $VARIANTS; do
+    RTB200_LIB=$PWD/build/tune/$v.so timeout ${PROBE_TIMEOUT:-40} python scripts/probe.py $WORK >> $P 2>&1
+    rc=$?
+    if [ $rc -ne 0 ]; then echo "probe $v exit $rc: skipping the remaining variants" | tee -a $P; break; fi
 done
+RTB200_LIB=$PWD/build/tune/$BASE.so timeout ${PROBE_TIMEOUT:-40} python scripts/probe.py $WORK >> $P 2>&1
 cat $P
 # fastest variant on c3 that is not slower than base on c4 by more than 1 %
 BEST=$(python - $P $BASE <<'EOF'
@@ -34,7 +38,7 @@ EOF
 )
 echo "best variant: $BEST" | tee $O/best.txt
 if [ "$BEST" != "$BASE" ]; then
-    RTB200_LIB=$PWD/build/tune/$BEST.so timeout 420 python -m pytest tests -m gpu -x -q > $O/pytest_$BEST.log 2>&1
+    RTB200_LIB=$PWD/build/tune/$BEST.so timeout ${PYTEST_TIMEOUT:-420} python -m pytest tests -m gpu -x -q > $O/pytest_$BEST.log 2>&1
     echo "pytest($BEST) exit $?" | tee -a $O/best.txt
     tail -3 $O/pytest_$BEST.log
     if grep -q " passed" $O/pytest_$BEST.log && ! grep -q "failed" $O/pytest_$BEST.log; then
@@ -43,6 +47,6 @@ if [ "$BEST" != "$BASE" ]; then
     fi
 fi
 for b in $BENCHES; do
-    timeout 300 python bench.py --workload $b > $O/bench_${b}_n1.json 2> $O/bench_${b}_n1.err; echo "bench $b exit $?"; cut -c1-200 $O/bench_${b}_n1.json
+    timeout ${BENCH_TIMEOUT:-300} python bench.py --workload $b > $O/bench_${b}_n1.json 2> $O/bench_${b}_n1.err; echo "bench $b exit $?"; cut -c1-200 $O/bench_${b}_n1.json
 done
 if [ -z "${RTB200_LIB:-}" ] && [ -n "${FINAL_PYTEST:-}" ]; then timeout 420 python -m pytest tests -m gpu -x -q > $O/pytest_final.log 2>&1; echo "pytest(in-tree lib) exit $?"; tail -3 $O/pytest_final.log; fi
