@@ -14,6 +14,7 @@
 #include <string>
 #include <vector>
 
+#include "../../include/rtb200_host.h"
 #include "rt_kernels.cuh"
 #include "rt_lbvh.cuh"
 #include "rt_path_kernel.cuh"
@@ -438,6 +439,8 @@ int rt_update_scene_metadata(RtContext* c, const RtSphere* spheres, uint32_t ns,
             return fail(c, RT_ERR_CUDA, "scene metadata cudaMalloc(%zu) failed", c->scene_metadata_capacity_bytes);
     }
     if (c->meta_dirty || needs_resize || any_changed) { // src/buffers.rs:212-255
+        if (rt_bvh_has_cycle(nodes, nn))
+            return fail(c, RT_ERR_INVALID_ARGUMENT, "BVH child links form a cycle: the reference traversal would not terminate");
         char* d = reinterpret_cast<char*>(c->meta.ptr);
         size_t o = 0;
         if (ss) CK(c, cudaMemcpyAsync(d + o, spheres, ss, cudaMemcpyHostToDevice, c->stream)); o += ss;

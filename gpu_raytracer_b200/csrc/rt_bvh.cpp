@@ -213,3 +213,33 @@ int rt_bvh_build(const RtTriangle* tris, uint64_t n, const RtVertex* verts, uint
 }
 
 } // extern "C"
+
+// A BVH whose child links form a cycle reachable from the root makes the reference traversal
+// (shader/src/bvh.rs:40-85: pop, test, push both children) run forever as long as the boxes on the
+// cycle are hit; on this device that is a hung context, so rt_update_scene_metadata refuses such an upload.  A DAG (a node
+// reachable twice without a cycle) terminates and is served by the LITERAL policy like in the reference.
+extern "C" int rt_bvh_has_cycle(const RtBvhNode* nodes, uint32_t n_nodes) {
+    if (n_nodes == 0 || !nodes) return 0;
+    std::vector<uint8_t> state(n_nodes, 0); // 0 new, 1 on the DFS path, 2 finished
+    struct Frame { uint32_t node; uint8_t next; };
+    std::vector<Frame> path;
+    path.push_back({0u, 0});
+    state[0] = 1;
+    while (!path.empty()) {
+        Frame& f = path.back();
+        const RtBvhNode& nd = nodes[f.node];
+        uint32_t child = RT_INVALID_INDEX;
+        if (nd.left_child != RT_INVALID_INDEX) { // internal node (bvh.rs:60)
+            while (f.next < 2 && child == RT_INVALID_INDEX) {
+                const uint32_t c = f.next == 0 ? nd.left_child : nd.right_child;
+                f.next++;
+                if (c != RT_INVALID_INDEX && c < n_nodes) child = c;
+            }
+        }
+        if (child == RT_INVALID_INDEX) { state[f.node] = 2; path.pop_back(); continue; }
+        if (state[child] == 1) return 1;
+        if (state[child] == 0) { state[child] = 1; path.push_back({child, 0}); }
+    }
+    return 0;
+}
+

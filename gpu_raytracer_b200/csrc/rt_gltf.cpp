@@ -22,6 +22,7 @@
 #include <string.h>
 
 #include <map>
+#include <exception>
 #include <memory>
 #include <string>
 #include <unordered_map>
@@ -252,7 +253,9 @@ struct Loader {
     const JVal* arr(const char* key) const { const JVal* v = doc.get(key); return (v && v->kind == JVal::Arr) ? v : nullptr; }
     static bool get_index(const JVal* o, const char* key, size_t* idx) {
         const JVal* v = o ? o->get(key) : nullptr;
-        if (!v || !v->is_num() || v->num < 0) return false;
+        // file-controlled number: NaN, negative and anything past 2^53 (not an exact integer in a JSON
+        // double, and large enough to overflow offset arithmetic) is "absent / invalid"
+        if (!v || !v->is_num() || !(v->num >= 0.0) || v->num > 9007199254740992.0) return false;
         *idx = (size_t)v->num;
         return true;
     }
@@ -327,12 +330,13 @@ struct Loader {
     bool read_positions(size_t acc_index, std::vector<float>& out3) {
         View v;
         if (!accessor_view(acc_index, &v)) return false;
+        // the whole range is checked before anything is allocated (count, offsets and stride come from the file)
+        const size_t size = v.data->size();
+        if (v.elem_size < 12) return fail("Buffer access out of bounds");
+        if (v.count && (v.start > size || v.elem_size > size - v.start || (v.count - 1) > (size - v.start - v.elem_size) / v.stride))
+            return fail("Buffer access out of bounds");
         out3.resize(v.count * 3);
-        for (size_t i = 0; i < v.count; i++) {
-            size_t off = v.start + i * v.stride;
-            if (off + v.elem_size > v.data->size() || v.elem_size < 12) return fail("Buffer access out of bounds");
-            memcpy(&out3[i * 3], v.data->data() + off, 12);
-        }
+        for (size_t i = 0; i < v.count; i++) memcpy(&out3[i * 3], v.data->data() + v.start + i * v.stride, 12);
         return true;
     }
     // get_indices_data, gltf_loader.rs:545-590: tightly packed u8/u16/u32; entries past the buffer end are skipped
@@ -342,12 +346,14 @@ struct Loader {
         size_t w = v.component == 5121 ? 1 : v.component == 5123 ? 2 : v.component == 5125 ? 4 : 0;
         if (!w) return fail("Unsupported index data type");
         out.clear();
-        out.reserve(v.count);
-        for (size_t i = 0; i < v.count; i++) {
-            size_t off = v.start + i * w;
-            if (off + w > v.data->size()) continue;
+        // packed entries: the ones past the buffer end form a tail, so "skipped" = the count is clipped
+        const size_t size = v.data->size();
+        size_t n_ok = (v.start <= size && w <= size - v.start) ? (size - v.start - w) / w + 1 : 0;
+        if (n_ok > v.count) n_ok = v.count;
+        out.reserve(n_ok);
+        for (size_t i = 0; i < n_ok; i++) {
             uint32_t x = 0;
-            memcpy(&x, v.data->data() + off, w);
+            memcpy(&x, v.data->data() + v.start + i * w, w);
             out.push_back(x);
         }
         return true;
@@ -408,6 +414,11 @@ struct Loader {
             uint32_t w = 0, h = 0;
             if (!image_bytes(imgs->arr[src], bytes) || !image_size(bytes, &w, &h)) {
                 out->warnings.push_back("image " + std::to_string(src) + ": payload unreadable, texture recorded as 0x0");
+                w = h = 0;
+            }
+            if ((uint64_t)w * h * 4u > (1ull << 30) || out->texture_data.size() + (uint64_t)w * h * 4u > 0xFFFFFFFFull) {
+                // offsets and sizes are u32 (TextureInfo); a header claiming more is not given a zero-filled block
+                out->warnings.push_back("image " + std::to_string(src) + ": " + std::to_string(w) + "x" + std::to_string(h) + " exceeds the texture block limits, texture recorded as 0x0");
                 w = h = 0;
             }
             RtTextureInfo ti;
@@ -694,8 +705,20 @@ int load_impl(const uint8_t* data, uint64_t n, const char* base_dir, int scene_i
 
 extern "C" {
 
+// no exception crosses the C ABI: allocation failures and anything else thrown become an error string
+static int load_guarded(const uint8_t* data, uint64_t n, const char* base_dir, int scene_index, RtGltfScene** out, char* err, size_t err_len) {
+    try {
+        return load_impl(data, n, base_dir, scene_index, out, err, err_len);
+    } catch (const std::exception& e) {
+        if (err && err_len) snprintf(err, err_len, "glTF load failed: %s", e.what());
+    } catch (...) {
+        if (err && err_len) snprintf(err, err_len, "glTF load failed");
+    }
+    return -1;
+}
+
 int rt_gltf_load_memory(const uint8_t* data, uint64_t n, const char* base_dir, int scene_index, RtGltfScene** out, char* err, uint64_t err_len) {
-    return load_impl(data, n, base_dir, scene_index, out, err, (size_t)err_len);
+    return load_guarded(data, n, base_dir, scene_index, out, err, (size_t)err_len);
 }
 
 int rt_gltf_load_file(const char* path, int scene_index, RtGltfScene** out, char* err, uint64_t err_len) {
@@ -707,7 +730,7 @@ int rt_gltf_load_file(const char* path, int scene_index, RtGltfScene** out, char
     std::string p(path);
     size_t slash = p.find_last_of('/');
     std::string dir = slash == std::string::npos ? "." : p.substr(0, slash);
-    return load_impl(data.data(), data.size(), dir.c_str(), scene_index, out, err, (size_t)err_len);
+    return load_guarded(data.data(), data.size(), dir.c_str(), scene_index, out, err, (size_t)err_len);
 }
 
 void rt_gltf_free(RtGltfScene* s) { delete s; }

@@ -131,6 +131,13 @@ def build_bvh(triangles, vertices, strategy=abi.BVH_AUTO):
     return nodes[:nn.value].copy(), idx[:ni.value].copy()
 
 
+def bvh_has_cycle(nodes):
+    """True if the child links reachable from node 0 form a cycle (such an upload is refused: the reference
+    traversal, shader/src/bvh.rs:40-85, would not terminate on it)."""
+    nodes = np.ascontiguousarray(nodes, dtype=abi.BvhNode)
+    return bool(load().rt_bvh_has_cycle(_p(nodes), len(nodes)))
+
+
 def default_scene(strategy=abi.BVH_AUTO):
     """SceneBuilder::build_default_scene + SceneState::new (shared/src/lib.rs:1242-1286, src/scene.rs:20-40)."""
     s = np.zeros(6, dtype=abi.Sphere)

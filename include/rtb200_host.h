@@ -64,6 +64,10 @@ uint64_t rt_bvh_max_nodes(uint64_t n_triangles);
 int rt_bvh_build(const RtTriangle* triangles, uint64_t n_triangles, const RtVertex* vertices, uint64_t n_vertices,
                  int strategy, RtBvhNode* nodes, uint32_t* n_nodes, uint32_t* indices, uint32_t* n_indices);
 
+/* 1 if the child links reachable from node 0 form a cycle (the reference traversal, shader/src/bvh.rs:40-85,
+ * would never terminate on such a tree; rt_update_scene_metadata refuses it), else 0. */
+int rt_bvh_has_cycle(const RtBvhNode* nodes, uint32_t n_nodes);
+
 /* ---- procedural scenes (bench / test inputs) */
 /* Terrain(nx, nz, seed): (nx+1)(nz+1) vertices, 2*nx*nz triangles row-major, materials striped by row
  * (diffuse / metallic / glass).  vertices: (nx+1)*(nz+1); triangles: 2*nx*nz; materials: 3; lights: 2. */

@@ -409,3 +409,24 @@ def test_peer_frame_epilogue_assembles_frame(mode):
         g.ComputeRenderer(one).render_frame(s.camera, outputs=abi.OUT_COMPOSITE | abi.OUT_PEER)  # no peer frame opened
     one.close()
     root.close()
+
+
+@pytest.mark.gpu
+def test_upload_refuses_cyclic_bvh():
+    """A BVH whose child links loop would hang the reference traversal (shader/src/bvh.rs:40-85) and this
+    device; the upload reports it instead, and the context stays usable."""
+    s = g.default_scene()
+    ctx = g.Context(0, 64, 36)
+    bm = g.BufferManager(ctx)
+    bad = s.bvh_nodes.copy()
+    internal = np.flatnonzero(bad["left_child"] != 0xFFFFFFFF)
+    assert len(internal)
+    bad["right_child"][internal[-1]] = 0  # a link back to the root
+    assert g.bvh_has_cycle(bad) and not g.bvh_has_cycle(s.bvh_nodes)
+    with pytest.raises(g.RtError):
+        bm.update_scene_metadata(s.spheres, s.lights, bad, s.triangle_indices, s.vertices)
+    bm.upload_scene(s)
+    g.ComputeRenderer(ctx).render_frame(s.camera, outputs=abi.OUT_HITS)
+    hits = ctx.read_hits()
+    assert int((hits["kind"] != 0).sum()) > 0
+    ctx.close()

@@ -221,3 +221,36 @@ def test_pack_scene_metadata_offsets():
     assert off["triangle_indices_offset"] == 43 + 3 * 12 and off["vertices_offset"] == 79 + 2
     assert meta.size == 81 + 18 and off["vertices_count"] == 6
     assert meta[30 + 3] == 1 and meta[79] == s.triangle_indices[0]
+
+
+def test_bvh_cycle_detection():
+    """rt_bvh_has_cycle: the upload refuses trees on which shader/src/bvh.rs:40-85 would never terminate."""
+    NONE = 0xFFFFFFFF
+    for strat in (abi.BVH_STANDARD, abi.BVH_CHUNKED, abi.BVH_SMALL_LEAF):
+        sc = g.terrain_scene(40, 33, strategy=strat)
+        assert not g.bvh_has_cycle(sc.bvh_nodes)
+    assert not g.bvh_has_cycle(g.default_scene().bvh_nodes)
+    assert not g.bvh_has_cycle(np.zeros(0, abi.BvhNode))
+
+    def node(l, r):
+        n = np.zeros(1, abi.BvhNode)
+        n["left_child"], n["right_child"] = l, r
+        return n
+    leaf = node(NONE, NONE)
+    # self loop, two-node loop, loop through the right child only
+    assert g.bvh_has_cycle(np.concatenate([node(0, NONE)]))
+    assert g.bvh_has_cycle(np.concatenate([node(1, 2), node(0, NONE), leaf]))
+    assert g.bvh_has_cycle(np.concatenate([node(1, 2), leaf, node(1, 0)]))
+    # a DAG (node 2 reachable twice) and links that the traversal ignores (out of range, leaf's right child) are fine
+    assert not g.bvh_has_cycle(np.concatenate([node(1, 2), node(2, NONE), leaf]))
+    assert not g.bvh_has_cycle(np.concatenate([node(1, 7), node(NONE, 0)]))
+    # an unreachable cycle does not matter
+    assert not g.bvh_has_cycle(np.concatenate([node(1, NONE), leaf, node(3, NONE), node(2, NONE)]))
+    # a 100 000-node chain must not overflow any stack
+    n = 100000
+    chain = np.zeros(n, abi.BvhNode)
+    chain["left_child"] = np.arange(1, n + 1); chain["right_child"] = NONE
+    chain["left_child"][-1] = NONE
+    assert not g.bvh_has_cycle(chain)
+    chain["left_child"][-1] = 5
+    assert g.bvh_has_cycle(chain)
