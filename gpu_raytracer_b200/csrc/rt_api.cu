@@ -657,6 +657,12 @@ int prepare_relayout(RtContext* c) {
         uint32_t ni = c->offsets.triangle_indices_count;
         // REBUILT is worth it (and certifiable) only for big-leaf, properly nested trees
         bool want_rebuilt = c->wide.nested_ok && c->wide.max_leaf > 2 * RT_LBVH_LEAF && ni < RT_LBVH_MAX_PRIMS;
+        // experiment switch (off unless set): rebuild small-leaf uploads of at least this many triangles too
+        // (one-sector nodes + 2-triangle leaves against the uploaded tree's fp32 nodes)
+        if (const char* e = getenv("RTB200_REBUILD_MIN_TRIANGLES")) {
+            const long long m = atoll(e);
+            if (m > 0 && (long long)ni >= m && c->wide.nested_ok && ni < RT_LBVH_MAX_PRIMS) want_rebuilt = true;
+        }
         cudaEvent_t e0 = c->ev0, e1 = c->ev1;
         CK(c, cudaEventRecord(e0, c->stream));
         if (c->wtris.reserve((size_t)ni * 3 + 3) < 0 || c->leaf_of_pos.reserve((size_t)ni + 1) < 0 ||
