@@ -218,6 +218,9 @@ def main():
     nx, nz, w, h = a
     sc = g.terrain_scene(nx, nz, seed=1, strategy=abi.BVH_SMALL_LEAF)
     evaluate(sc, sc.bvh_nodes, sc.triangle_indices, w, h, "binned SAH <=4 (rt_bvh_build)")
+    if len(sc.triangles) <= 100000:
+        n, i = g.build_bvh(sc.triangles, sc.vertices, abi.BVH_STANDARD)
+        evaluate(sc, n, i, w, h, "standard format, 1 tri/leaf")
     lo, hi = tri_boxes(sc)
     for name, axes in (("morton3", (0, 1, 2)), ("morton2-xz", (0, 2))):
         keys = morton(lo, hi, axes)
