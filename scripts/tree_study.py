@@ -49,6 +49,21 @@ def morton(lo, hi, axes=(0, 1, 2)):
     return e2(q[:, a]) << np.uint64(1) | e2(q[:, b])
 
 
+def morton_hybrid(lo, hi, yb):
+    """x/z code whose levels b <= yb (cells of side extent / 2^(20 - b) and finer) also carry the y bit."""
+    c = 0.5 * (lo + hi)
+    mn, mx = c.min(0), c.max(0)
+    ext = float((mx - mn).max())
+    q = np.minimum(2097151.0, np.clip((c - mn) / ext, 0, 1) * 2097152.0).astype(np.uint64)
+    key = np.zeros(len(q), np.uint64)
+    one = np.uint64(1)
+    for b in range(20, -1, -1):
+        for k in (0, 1, 2):
+            if k == 1 and b > yb: continue
+            key = key << one | (q[:, k] >> np.uint64(b) & one)
+    return key
+
+
 def radix_tree(keys):
     """children[i] = (left, right), leaves encoded as ~slot (negative).  Top-down highest-differing-bit splits:
     the same tree Karras' construction yields."""
@@ -222,12 +237,15 @@ def main():
         n, i = g.build_bvh(sc.triangles, sc.vertices, abi.BVH_STANDARD)
         evaluate(sc, n, i, w, h, "standard format, 1 tri/leaf")
     lo, hi = tri_boxes(sc)
-    for name, axes in (("morton3", (0, 1, 2)), ("morton2-xz", (0, 2))):
-        keys = morton(lo, hi, axes)
+    cands = [("morton3", (0, 1, 2)), ("morton2-xz", (0, 2))]
+    cands += [("hybrid-y<=%s" % b, int(b)) for b in os.environ.get("STUDY_HYBRID", "").split(",") if b]
+    if os.environ.get("STUDY_ONLY"): cands = [c for c in cands if c[0].startswith(tuple(os.environ["STUDY_ONLY"].split(",")))]
+    for name, axes in cands:
+        keys = morton_hybrid(lo, hi, axes) if isinstance(axes, int) else morton(lo, hi, axes)
         order = np.argsort(keys, kind="stable")
         ks = keys[order]
         ch, rg = radix_tree(ks)
-        for L in (2, 4):
+        for L in [int(x) for x in os.environ.get("STUDY_LEAF", "2,4").split(",")]:
             tr = Tree(ch, rg, lo[order], hi[order])
             n, i = tr.flatten(order, L)
             evaluate(sc, n, i, w, h, "%s leaf<=%d  sah %.1f" % (name, L, tr.sah(L)))
