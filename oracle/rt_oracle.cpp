@@ -593,20 +593,30 @@ static V3 path_sample(const Bind& b, uint32_t px, uint32_t py, uint32_t s, const
     return L;
 }
 
+/* Work items are 64-pixel spans of a row (not whole rows): a band of 2 rows still
+ * feeds 60 items to the pool at 1080p, so a short cpu_baseline sample uses every
+ * host thread it is given. */
+static const uint32_t SPAN = 64;
 template <class F>
-static void parallel_rows(uint32_t rows, int threads, F fn) {
-    if (threads <= 1 || rows <= 1) {
-        for (uint32_t r = 0; r < rows; r++) fn(r, 0);
+static void parallel_spans(uint32_t rows, uint32_t width, int threads, F fn) {
+    const uint32_t per_row = (width + SPAN - 1) / SPAN;
+    const uint64_t items = (uint64_t)rows * per_row;
+    auto run = [&](uint64_t it, int t) {
+        uint32_t r = (uint32_t)(it / per_row), x0 = (uint32_t)(it % per_row) * SPAN;
+        fn(r, x0, x0 + SPAN < width ? x0 + SPAN : width, t);
+    };
+    if (threads <= 1 || items <= 1) {
+        for (uint64_t it = 0; it < items; it++) run(it, 0);
         return;
     }
-    std::atomic<uint32_t> next(0);
+    std::atomic<uint64_t> next(0);
     std::vector<std::thread> pool;
     for (int t = 0; t < threads; t++)
         pool.emplace_back([&, t]() {
             for (;;) {
-                uint32_t r = next.fetch_add(1);
-                if (r >= rows) break;
-                fn(r, t);
+                uint64_t it = next.fetch_add(1);
+                if (it >= items) break;
+                run(it, t);
             }
         });
     for (auto& th : pool) th.join();
@@ -655,10 +665,10 @@ int orc_dispatch_policy(const OrcBindings* ob, const RtPushConstants* pc, uint8_
     uint32_t channel = rt_pc_color_channel(pc);
     if (threads < 1) threads = 1;
     std::vector<Counters> cs((size_t)threads);
-    parallel_rows(gh, threads, [&](uint32_t iy, int tid) {
+    parallel_spans(gh, gw, threads, [&](uint32_t iy, uint32_t ix0, uint32_t ix1, int tid) {
         Counters& c = cs[(size_t)tid];
         g_policy = policy;
-        for (uint32_t ix = 0; ix < gw; ix++) {
+        for (uint32_t ix = ix0; ix < ix1; ix++) {
             uint32_t px = pc->tile_offset[0] + ix, py = pc->tile_offset[1] + iy;
             if (!(ix < tw && iy < th && px < width && py < height)) continue; /* lib.rs:152-163 */
             Hit h;
@@ -710,11 +720,11 @@ int orc_render_path(const OrcBindings* ob, const RtPushConstants* pc, uint32_t s
     if (threads < 1) threads = 1;
     PathParams pp{spp, first_sample, max_depth, base_seed};
     std::vector<Counters> cs((size_t)threads);
-    parallel_rows(y1 - y0, threads, [&](uint32_t iy, int tid) {
+    parallel_spans(y1 - y0, width, threads, [&](uint32_t iy, uint32_t px0, uint32_t px1, int tid) {
         Counters& c = cs[(size_t)tid];
         g_policy = policy;
         uint32_t py = y0 + iy;
-        for (uint32_t px = 0; px < width; px++) {
+        for (uint32_t px = px0; px < px1; px++) {
             size_t p = (size_t)py * width + px;
             float* a = accum + p * 4;
             if (reset) a[0] = a[1] = a[2] = a[3] = 0.0f;

@@ -54,24 +54,43 @@ def hardware_threads():
     return int(lib().orc_hardware_threads())
 
 
+def materials_capacity(n, capacity=64):
+    """BufferManager::update_materials growth rule (src/buffers.rs:339-352) for a fresh manager."""
+    return capacity if n <= capacity else max(n * 2, 64)
+
+
 class BoundScene:
-    """The reference's bound buffers for one scene (bindings 1-5), split over <=3
-    triangle buffers like BufferManager::update_triangles (src/buffers.rs:311-325)."""
+    """The reference's bound buffers for one scene (bindings 1-5), as a fresh BufferManager + bind group
+    would hold them:
+      * triangles: max(1, ceil(n / tpb)) buffers of exactly `tpb` zero-initialised entries each
+        (src/buffers.rs:93-99, 274-325; wgpu zero-fills new buffers); binding k = buffer k if it exists,
+        else buffer 0 again (src/renderer.rs:680-693 `.unwrap_or(&buffers.triangle_buffers[0])`);
+      * materials: one buffer of `materials_capacity` entries (64, doubled on growth), zero-filled past
+        the uploaded count — `materials.len()` in the shader is that bound length (shader/src/lib.rs:307)."""
 
     def __init__(self, scene, triangles_per_buffer=abi.MAX_TRIANGLES_PER_BUFFER):
         self.scene = scene
         self.meta, self.offsets = pack_scene_metadata(scene)
         self.tpb = triangles_per_buffer
         tris = np.ascontiguousarray(scene.triangles, abi.Triangle)
-        self.tri_parts = [np.ascontiguousarray(tris[i * self.tpb:(i + 1) * self.tpb]) for i in range(3)]
-        self.materials = np.ascontiguousarray(scene.materials, abi.Material)
+        n_buf = max(1, (len(tris) + self.tpb - 1) // self.tpb)
+        self.tri_buffers = []
+        for i in range(n_buf):
+            buf = np.zeros(self.tpb, abi.Triangle)  # calloc: untouched pages stay virtual
+            part = tris[i * self.tpb:(i + 1) * self.tpb]
+            buf[:len(part)] = part
+            self.tri_buffers.append(buf)
+        mats = np.ascontiguousarray(scene.materials, abi.Material)
+        self.materials = np.zeros(materials_capacity(len(mats)), abi.Material)
+        self.materials[:len(mats)] = mats
         b = OrcBindings()
         b.scene_metadata = self.meta.ctypes.data
         b.scene_metadata_len = self.meta.size
         for i in range(3):
-            b.triangles[i] = self.tri_parts[i].ctypes.data if len(self.tri_parts[i]) else None
-            b.triangles_len[i] = len(self.tri_parts[i])
-        b.materials = self.materials.ctypes.data if len(self.materials) else None
+            buf = self.tri_buffers[i] if i < n_buf else self.tri_buffers[0]
+            b.triangles[i] = buf.ctypes.data
+            b.triangles_len[i] = len(buf)
+        b.materials = self.materials.ctypes.data
         b.materials_len = len(self.materials)
         self.bindings = b
 
