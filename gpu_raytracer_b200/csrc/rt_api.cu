@@ -17,8 +17,6 @@
 #include "../../include/rtb200_host.h"
 #include "rt_kernels.cuh"
 #include "rt_lbvh.cuh"
-#include "rt_path_kernel.cuh"
-#include "rt_wavefront.cuh"
 #include "rt_wave.cuh"
 
 namespace {
@@ -31,12 +29,16 @@ struct DevBuf {
     size_t capacity = 0; // elements
     ~DevBuf() { if (ptr) cudaFree(ptr); }
     // returns 1 if reallocated, 0 if not, <0 cuda error
+    // The new buffer is allocated before the old one is released: a failed growth leaves the
+    // previous contents (and capacity) in place.  Contents are NOT carried over.
     int reserve(size_t n) {
         if (n <= capacity && ptr) return 0;
-        if (ptr) { cudaFree(ptr); ptr = nullptr; capacity = 0; }
         size_t cap = n ? n : 1;
-        cudaError_t e = cudaMalloc((void**)&ptr, cap * sizeof(T));
-        if (e != cudaSuccess) return -1;
+        T* np = nullptr;
+        cudaError_t e = cudaMalloc((void**)&np, cap * sizeof(T));
+        if (e != cudaSuccess) { cudaGetLastError(); return -1; }
+        if (ptr) cudaFree(ptr);
+        ptr = np;
         capacity = cap;
         return 1;
     }
@@ -75,6 +77,7 @@ struct RtContext {
     DevBuf<RtTriangle> tris;
     size_t n_tris = 0;
     size_t tri_buffers = 1; // reference starts with one bound buffer (src/buffers.rs:92-99)
+    uint32_t tpb = RT_MAX_TRIANGLES_PER_BUFFER; // BufferManager.triangles_per_buffer (src/buffers.rs:49-53, 73)
     DevBuf<RtMaterial> mats;
     size_t n_mats = 0, mats_capacity = 64;
     DevBuf<RtTextureInfo> textures;
@@ -109,12 +112,8 @@ struct RtContext {
     bool rebuilt_ok = false;
     uint32_t broot_ref = RT_CHILD_ABSENT;
     float broot_min[3] = {0, 0, 0}, broot_max[3] = {0, 0, 0};
+    float rebuilt_far = 0.0f; // rays whose origin has a coordinate beyond this take the literal policy (rt_lbvh.cuh)
     float last_build_ms = -1.0f;
-    // wavefront path tracing (rt_wavefront.cuh)
-    DevBuf<float4> wf_state;
-    DevBuf<uint4> wf_hit;
-    DevBuf<uint32_t> wf_queue[2];
-    DevBuf<WfCtrl> wf_ctrl;
     bool last_was_wavefront = false;
     // streaming wavefront engine (rt_wave.cuh)
     DevBuf<float4> wv_state[2], wv_lbuf;
@@ -252,7 +251,7 @@ void build_wide(const RtBvhNode* nodes, uint32_t n_nodes, uint32_t n_indices, Wi
 // (v0, e1, e2, material, index).  e1 = v1 - v0 and e2 = v2 - v0 are the same two
 // IEEE subtractions intersection.rs:102-103 performs per test, hoisted to upload.
 __global__ void relayout_triangles(const uint32_t* __restrict__ meta, RtSceneMetadataOffsets off,
-                                   const RtTriangle* __restrict__ tris, uint64_t n_tris, uint32_t tpb,
+                                   const RtTriangle* __restrict__ tris, uint64_t n_tris, uint32_t tpb, uint32_t n_buffers,
                                    float4* __restrict__ out, float4* __restrict__ pbox, uint32_t* __restrict__ flag) {
     uint32_t pos = blockIdx.x * blockDim.x + threadIdx.x;
     if (pos >= off.triangle_indices_count) return;
@@ -260,10 +259,13 @@ __global__ void relayout_triangles(const uint32_t* __restrict__ meta, RtSceneMet
     float4 a = make_float4(0, 0, 0, 0), b = a, c = a;
     float4 blo = a, bhi = a;
     c.z = __uint_as_float(ti);
-    // triangle_access.rs:26-48: valid iff it falls inside one of the <=3 bound buffers
-    bool valid = ti < n_tris && (ti / tpb) <= 2u;
+    // triangle_access.rs:26-48 over the bound buffers (resolve_bound_triangle): an index that resolves to the
+    // zero-filled tail of a buffer is a degenerate triangle the Möller–Trumbore test always rejects (a == 0),
+    // so it is stored like an invalid one (all zero: never hit)
+    uint64_t gi;
+    bool valid = resolve_bound_triangle(ti, tpb, tpb, n_buffers, &gi) && gi < n_tris;
     if (valid) {
-        RtTriangle t = tris[ti];
+        RtTriangle t = tris[gi];
         if (t.v0_index >= off.vertices_count || t.v1_index >= off.vertices_count || t.v2_index >= off.vertices_count) {
             atomicOr(flag, 1u); // the reference would read out of bounds
         } else {
@@ -364,6 +366,13 @@ int rt_create(int device, RtContext** out) {
         delete c;
         return RT_ERR_CUDA;
     }
+    // wgpu zero-initialises new buffers; the shader's materials.len() is the bound capacity, so ids in
+    // [uploaded count, capacity) index zero materials (src/buffers.rs:100-106, src/renderer.rs:698)
+    if (cudaMemsetAsync(c->mats.ptr, 0, c->mats_capacity * sizeof(RtMaterial), c->stream) != cudaSuccess) {
+        fail(nullptr, RT_ERR_CUDA, "rt_create: cudaMemset failed");
+        delete c;
+        return RT_ERR_CUDA;
+    }
     *out = c;
     return RT_OK;
 }
@@ -429,18 +438,40 @@ int rt_update_scene_metadata(RtContext* c, const RtSphere* spheres, uint32_t ns,
     bool needs_resize = total > c->scene_metadata_capacity_bytes;
     bool any_changed = ns != c->last_spheres || nl != c->last_lights || nn != c->last_nodes || ni != c->last_indices ||
                        nv != c->last_vertices;
+    const bool upload = c->meta_dirty || needs_resize || any_changed; // src/buffers.rs:212
+    // Everything that can refuse the upload runs BEFORE any device buffer or bookkeeping is touched, so a
+    // refused upload leaves the previously uploaded scene fully in place (buffers, offsets, re-layout).
+    WideBvh wide;
+    if (upload) {
+        if (rt_bvh_has_cycle(nodes, nn))
+            return fail(c, RT_ERR_INVALID_ARGUMENT, "BVH child links form a cycle: the reference traversal would not terminate");
+        build_wide(nodes, nn, ni, wide); // validation + node re-layout while the host arrays are borrowed
+    }
+    size_t new_capacity = c->scene_metadata_capacity_bytes;
     if (needs_resize) { // src/buffers.rs:186-204: double, with the default floors
         size_t sc = (size_t)ns * 2 > 64 ? (size_t)ns * 2 : 64, lc = (size_t)nl * 2 > 32 ? (size_t)nl * 2 : 32,
                bc = (size_t)nn * 2 > 256 ? (size_t)nn * 2 : 256, ic = (size_t)ni * 2 > 1024 ? (size_t)ni * 2 : 1024,
                vc = (size_t)nv * 2 > 1024 ? (size_t)nv * 2 : 1024;
-        c->scene_metadata_capacity_bytes = sc * sizeof(RtSphere) + lc * sizeof(RtLight) + bc * sizeof(RtBvhNode) + ic * 4 +
-                                           vc * sizeof(RtVertex);
-        if (c->meta.reserve(c->scene_metadata_capacity_bytes / 4) < 0)
-            return fail(c, RT_ERR_CUDA, "scene metadata cudaMalloc(%zu) failed", c->scene_metadata_capacity_bytes);
+        new_capacity = sc * sizeof(RtSphere) + lc * sizeof(RtLight) + bc * sizeof(RtBvhNode) + ic * 4 + vc * sizeof(RtVertex);
     }
-    if (c->meta_dirty || needs_resize || any_changed) { // src/buffers.rs:212-255
-        if (rt_bvh_has_cycle(nodes, nn))
-            return fail(c, RT_ERR_INVALID_ARGUMENT, "BVH child links form a cycle: the reference traversal would not terminate");
+    if (upload) {
+        // the context's stream may still be reading the buffers a growth is about to replace
+        if (needs_resize || (wide.ordered_ok && (wide.nodes.size() > c->wnodes.capacity || wide.leaves.size() > c->wleaves.capacity ||
+                                                 wide.leaf_nodes.size() > c->wleaf_nodes.capacity)))
+            CK(c, cudaStreamSynchronize(c->stream));
+        // DevBuf::reserve keeps the old buffer when the new allocation fails: nothing is lost on these paths
+        if (wide.ordered_ok && (c->wnodes.reserve(wide.nodes.size()) < 0 || c->wleaves.reserve(wide.leaves.size()) < 0 ||
+                                c->wleaf_nodes.reserve(wide.leaf_nodes.size()) < 0)) {
+            c->relayout_dirty = true; // the auxiliary buffers may be half-grown: rebuild them before the next ordered launch
+            return fail(c, RT_ERR_CUDA, "wide BVH cudaMalloc failed");
+        }
+        if (needs_resize && c->meta.reserve(new_capacity / 4) < 0)
+            return fail(c, RT_ERR_CUDA, "scene metadata cudaMalloc(%zu) failed", new_capacity);
+        c->scene_metadata_capacity_bytes = new_capacity;
+        // from here on the previous scene is being overwritten: any failure below leaves no scene
+        c->have_meta = false;
+        c->relayout_dirty = true; c->relayout_ok = false; c->rebuilt_ok = false;
+        c->wide = std::move(wide);
         char* d = reinterpret_cast<char*>(c->meta.ptr);
         size_t o = 0;
         if (ss) CK(c, cudaMemcpyAsync(d + o, spheres, ss, cudaMemcpyHostToDevice, c->stream)); o += ss;
@@ -448,12 +479,7 @@ int rt_update_scene_metadata(RtContext* c, const RtSphere* spheres, uint32_t ns,
         if (bs) CK(c, cudaMemcpyAsync(d + o, nodes, bs, cudaMemcpyHostToDevice, c->stream)); o += bs;
         if (is) CK(c, cudaMemcpyAsync(d + o, tri_idx, is, cudaMemcpyHostToDevice, c->stream)); o += is;
         if (vs) CK(c, cudaMemcpyAsync(d + o, verts, vs, cudaMemcpyHostToDevice, c->stream));
-        // validation + node re-layout while the host arrays are still borrowed
-        build_wide(nodes, nn, ni, c->wide);
         if (c->wide.ordered_ok) {
-            if (c->wnodes.reserve(c->wide.nodes.size()) < 0 || c->wleaves.reserve(c->wide.leaves.size()) < 0 ||
-                c->wleaf_nodes.reserve(c->wide.leaf_nodes.size()) < 0)
-                return fail(c, RT_ERR_CUDA, "wide BVH cudaMalloc failed");
             if (!c->wide.nodes.empty())
                 CK(c, cudaMemcpyAsync(c->wnodes.ptr, c->wide.nodes.data(), c->wide.nodes.size() * sizeof(float4),
                                       cudaMemcpyHostToDevice, c->stream));
@@ -464,12 +490,12 @@ int rt_update_scene_metadata(RtContext* c, const RtSphere* spheres, uint32_t ns,
                                       cudaMemcpyHostToDevice, c->stream));
             }
         }
-        // pageable host memory: the copies above are staged before return, but the
-        // std::vectors must outlive the DMA -> wait here (upload is not the hot path)
+        // Borrowed host memory (src/buffers.rs:236 `queue.write_buffer` copy semantics): cudaMemcpyAsync from
+        // pageable memory returns once the source has been staged; from pinned memory it is a true async DMA,
+        // so the caller's arrays must stay valid until the stream reaches this point -> wait here.
         CK(c, cudaStreamSynchronize(c->stream));
         c->meta_len = total / 4;
         c->meta_dirty = false;
-        c->relayout_dirty = true;
         c->last_spheres = ns; c->last_lights = nl; c->last_nodes = nn; c->last_indices = ni; c->last_vertices = nv;
     }
     // src/buffers.rs:257-268
@@ -488,14 +514,15 @@ int rt_update_scene_metadata(RtContext* c, const RtSphere* spheres, uint32_t ns,
 int rt_update_triangles(RtContext* c, const RtTriangle* tris, uint64_t n) {
     if (!c || (n && !tris)) return c ? fail(c, RT_ERR_INVALID_ARGUMENT, "rt_update_triangles: NULL") : RT_ERR_INVALID_ARGUMENT;
     CK(c, cudaSetDevice(c->device));
-    // src/buffers.rs:274-303: one more bound buffer per RT_MAX_TRIANGLES_PER_BUFFER
-    size_t needed = (size_t)((n + RT_MAX_TRIANGLES_PER_BUFFER - 1) / RT_MAX_TRIANGLES_PER_BUFFER);
+    // src/buffers.rs:274-303: one more bound buffer per triangles_per_buffer triangles (never released)
+    size_t needed = (size_t)((n + c->tpb - 1) / c->tpb);
     if (needed < 1) needed = 1;
-    bool needs_resize = false;
-    if (c->tri_buffers < needed) { c->tri_buffers = needed; needs_resize = true; }
+    const bool needs_resize = c->tri_buffers < needed;
     bool changed = n != c->last_tris;
     if (c->tris_dirty || needs_resize || changed) {
+        if ((size_t)n > c->tris.capacity) CK(c, cudaStreamSynchronize(c->stream)); // kernels may still read the old array
         if (c->tris.reserve((size_t)n) < 0) return fail(c, RT_ERR_CUDA, "triangle cudaMalloc(%llu) failed", (unsigned long long)n);
+        if (needs_resize) c->tri_buffers = needed;
         if (n) CK(c, cudaMemcpyAsync(c->tris.ptr, tris, (size_t)n * sizeof(RtTriangle), cudaMemcpyHostToDevice, c->stream));
         CK(c, cudaStreamSynchronize(c->stream));
         c->n_tris = (size_t)n;
@@ -511,8 +538,12 @@ int rt_update_materials(RtContext* c, const RtMaterial* mats, uint64_t n) {
     CK(c, cudaSetDevice(c->device));
     bool needs_resize = n > c->mats_capacity; // src/buffers.rs:339-352
     if (needs_resize) {
-        c->mats_capacity = (size_t)n * 2 > 64 ? (size_t)n * 2 : 64;
-        if (c->mats.reserve(c->mats_capacity) < 0) return fail(c, RT_ERR_CUDA, "materials cudaMalloc failed");
+        const size_t cap = (size_t)n * 2 > 64 ? (size_t)n * 2 : 64;
+        CK(c, cudaStreamSynchronize(c->stream)); // kernels may still read the old buffer
+        if (c->mats.reserve(cap) < 0) return fail(c, RT_ERR_CUDA, "materials cudaMalloc failed");
+        c->mats_capacity = cap;
+        // a new wgpu buffer is zero-initialised; entries [n, capacity) stay zero materials the shader can index
+        CK(c, cudaMemsetAsync(c->mats.ptr, 0, cap * sizeof(RtMaterial), c->stream));
     }
     if (c->mats_dirty || needs_resize || n != c->last_mats) {
         if (n) CK(c, cudaMemcpyAsync(c->mats.ptr, mats, (size_t)n * sizeof(RtMaterial), cudaMemcpyHostToDevice, c->stream));
@@ -570,7 +601,17 @@ void rt_mark_all_dirty(RtContext* c) {
 int rt_needs_update(const RtContext* c) {
     return c && (c->meta_dirty || c->tris_dirty || c->mats_dirty || c->tex_dirty || c->texdata_dirty) ? 1 : 0;
 }
-uint32_t rt_triangles_per_buffer(const RtContext*) { return RT_MAX_TRIANGLES_PER_BUFFER; }
+uint32_t rt_triangles_per_buffer(const RtContext* c) { return c ? c->tpb : RT_MAX_TRIANGLES_PER_BUFFER; }
+int rt_set_triangles_per_buffer(RtContext* c, uint32_t n) {
+    if (!c) return RT_ERR_INVALID_ARGUMENT;
+    if (n == 0) return fail(c, RT_ERR_INVALID_ARGUMENT, "rt_set_triangles_per_buffer: 0");
+    // the reference fixes the value when the BufferManager is constructed (src/buffers.rs:73): only before the first upload
+    if (c->last_tris != 0 || c->n_tris != 0 || c->tri_buffers != 1)
+        return fail(c, RT_ERR_INVALID_ARGUMENT, "rt_set_triangles_per_buffer: triangles were already uploaded");
+    c->tpb = n;
+    c->tris_dirty = true; c->relayout_dirty = true;
+    return RT_OK;
+}
 int rt_get_metadata_offsets(const RtContext* c, RtSceneMetadataOffsets* out) {
     if (!c || !out || !c->have_meta) return RT_ERR_NOT_READY;
     *out = c->offsets;
@@ -617,9 +658,9 @@ int build_rebuilt(RtContext* c, uint32_t n) {
         lbvh::mark_emitted<<<g, 256, 0, c->stream>>>(c->lb_range.ptr, n, c->lb_visits.ptr);
         if (cub::DeviceScan::ExclusiveSum(c->lb_temp.ptr, temp_bytes, c->lb_visits.ptr, c->lb_vals.ptr, (int)n, c->stream) != cudaSuccess)
             return fail(c, RT_ERR_CUDA, "LBVH node compaction scan failed");
-        lbvh::emit_wide<<<g, 256, 0, c->stream>>>(c->pbox.ptr, c->lb_vals_sorted.ptr, n, c->lb_children.ptr, c->lb_range.ptr,
-                                                  c->lb_nbox.ptr, c->lb_vals.ptr, c->bnodes.ptr);
         lbvh::quant_grid<<<1, 1, 0, c->stream>>>(c->lb_nbox.ptr, c->lb_grid.ptr);
+        lbvh::emit_wide<<<g, 256, 0, c->stream>>>(c->pbox.ptr, c->lb_vals_sorted.ptr, n, c->lb_children.ptr, c->lb_range.ptr,
+                                                  c->lb_nbox.ptr, c->lb_vals.ptr, c->lb_grid.ptr, c->bnodes.ptr);
         lbvh::emit_quant<<<g, 256, 0, c->stream>>>(c->pbox.ptr, c->lb_vals_sorted.ptr, n, c->lb_children.ptr, c->lb_range.ptr,
                                                    c->lb_nbox.ptr, c->lb_vals.ptr, c->lb_grid.ptr, c->bqnodes.ptr);
         lbvh::tree_depth<<<g, 256, 0, c->stream>>>(c->lb_parent_i.ptr, c->lb_parent_l.ptr, n, c->lb_bounds.ptr + 6);
@@ -636,15 +677,18 @@ int build_rebuilt(RtContext* c, uint32_t n) {
     if (n >= 2) CK(c, cudaMemcpyAsync(c->bq_grid, c->lb_grid.ptr, sizeof c->bq_grid, cudaMemcpyDeviceToHost, c->stream));
     CK(c, cudaStreamSynchronize(c->stream));
     CK(c, cudaGetLastError());
-    float m = 0.0f;
     const float v[6] = {rb[0].x, rb[0].y, rb[0].z, rb[1].x, rb[1].y, rb[1].z};
-    for (float x : v) m = fmaxf(m, fabsf(x));
-    float pad = m * 1.52587890625e-05f + 1e-30f; // same inflation as lbvh::inflate
+    const float pad = lbvh::scene_pad(rb[0], rb[1]); // the same scene-wide inflation every box of the tree got
     for (int k = 0; k < 3; k++) { c->broot_min[k] = v[k] - pad; c->broot_max[k] = v[3 + k] + pad; }
+    bool finite = true;
+    for (float x : v) finite = finite && isfinite(x);
+    c->rebuilt_far = RT_REBUILT_FAR * (pad * 65536.0f); // RT_REBUILT_FAR scene magnitudes
     c->broot_ref = n <= RT_LBVH_LEAF ? (RT_LEAF_FLAG | ((n - 1u) << 28)) : 0u;
     if (getenv("RTB200_DEBUG")) fprintf(stderr, "[rtb200] internal LBVH: %u triangles, depth %u\n", n, tree_depth);
     c->lbvh_depth = tree_depth;
-    c->rebuilt_ok = tree_depth < 60; // the traversal stacks hold 64 entries (many coincident centroids can deepen the tree)
+    // the traversal stacks hold 64 entries (many coincident centroids can deepen the tree); a scene with
+    // non-finite coordinates has no usable grid or pad: such uploads keep the ORDERED / LITERAL policies
+    c->rebuilt_ok = tree_depth < 60 && finite;
     return RT_OK;
 }
 
@@ -673,7 +717,7 @@ int prepare_relayout(RtContext* c) {
         CK(c, cudaMemsetAsync(c->leaf_of_pos.ptr, 0xFF, ((size_t)ni + 1) * 4, c->stream));
         if (ni) {
             relayout_triangles<<<(ni + 255) / 256, 256, 0, c->stream>>>(c->meta.ptr, c->offsets, c->tris.ptr, c->n_tris,
-                                                                        RT_MAX_TRIANGLES_PER_BUFFER, c->wtris.ptr,
+                                                                        c->tpb, (uint32_t)c->tri_buffers, c->wtris.ptr,
                                                                         want_rebuilt ? c->pbox.ptr : nullptr, c->dflag.ptr);
             c->launches++;
             uint32_t nl = (uint32_t)c->wide.leaves.size();
@@ -706,15 +750,16 @@ int prepare_relayout(RtContext* c) {
 void fill_scene(RtContext* c, KParams& k) {
     k.meta = c->meta.ptr; k.meta_len = c->meta_len; k.off = c->offsets;
     k.tris = c->tris.ptr; k.n_tris = c->n_tris;
-    k.ctx_triangles_per_buffer = RT_MAX_TRIANGLES_PER_BUFFER;
-    k.mats = c->mats.ptr; k.n_mats = (uint32_t)c->n_mats;
+    k.ctx_triangles_per_buffer = c->tpb; k.n_tri_buffers = (uint32_t)c->tri_buffers;
+    // materials.len() in the shader is the bound buffer's length = capacity (lib.rs:307, src/renderer.rs:698)
+    k.mats = c->mats.ptr; k.n_mats = (uint32_t)c->mats_capacity;
     k.wnodes = c->wnodes.ptr; k.wtris = c->wtris.ptr;
     k.root_ref = c->wide.root_ref;
     memcpy(k.root_min, c->wide.root_min, 12); memcpy(k.root_max, c->wide.root_max, 12);
     k.bnodes = c->bnodes.ptr; k.btris = c->btris.ptr; k.leaf_of_pos = c->leaf_of_pos.ptr;
     k.broot_ref = c->broot_ref;
     memcpy(k.broot_min, c->broot_min, 12); memcpy(k.broot_max, c->broot_max, 12);
-    k.cert_box = c->cert_box.ptr;
+    k.cert_box = c->cert_box.ptr; k.rebuilt_far = c->rebuilt_far;
     k.bqnodes = c->bqnodes.ptr; memcpy(k.bq_origin, c->bq_grid, 12); memcpy(k.bq_scale, c->bq_grid + 3, 12);
     k.accum = c->accum.ptr; k.hits = c->hits.ptr;
     for (int i = 0; i < 3; i++) k.chan[i] = c->chan[i].ptr;
@@ -739,7 +784,7 @@ int launch(RtContext* c, const KParams& k, uint32_t blocks, uint32_t traversal) 
     if (blocks == 0) return RT_OK;
     // the re-laid-out buffers bake in the uploaded offsets and the context's buffer
     // split; a dispatch whose push constants differ from them takes the literal path
-    bool same_scene = k.off.bvh_nodes_count > 0 && k.triangles_per_buffer == RT_MAX_TRIANGLES_PER_BUFFER &&
+    bool same_scene = k.off.bvh_nodes_count > 0 && k.triangles_per_buffer == c->tpb &&
                       memcmp(&k.off, &c->offsets, sizeof(RtSceneMetadataOffsets)) == 0;
     bool can_ordered = c->relayout_ok && same_scene, can_rebuilt = c->rebuilt_ok && same_scene;
     int policy;
@@ -765,7 +810,7 @@ int launch(RtContext* c, const KParams& k, uint32_t blocks, uint32_t traversal) 
 }
 
 int pick_policy(RtContext* c, const KParams& k, uint32_t traversal) {
-    bool same_scene = k.off.bvh_nodes_count > 0 && k.triangles_per_buffer == RT_MAX_TRIANGLES_PER_BUFFER &&
+    bool same_scene = k.off.bvh_nodes_count > 0 && k.triangles_per_buffer == c->tpb &&
                       memcmp(&k.off, &c->offsets, sizeof(RtSceneMetadataOffsets)) == 0;
     bool can_ordered = c->relayout_ok && same_scene, can_rebuilt = c->rebuilt_ok && same_scene;
     if (traversal == RT_TRAVERSAL_LITERAL) return 0;
@@ -775,13 +820,11 @@ int pick_policy(RtContext* c, const KParams& k, uint32_t traversal) {
 }
 
 // EXTENSION path tracing: persistent grid, one resident wave of 256-thread blocks
-int launch_path(RtContext* c, const KParams& k, uint32_t traversal, uint32_t variant) {
+int launch_path(RtContext* c, const KParams& k, uint32_t traversal) {
     if (k.n_work == 0) return RT_OK;
     int policy = pick_policy(c, k, traversal);
     if (policy < 0) return fail(c, RT_ERR_INVALID_SCENE, "requested traversal unavailable for this scene");
-    const bool v2 = policy >= 1 && variant == 3;
-    const void* fn = v2 ? (policy == 2 ? (const void*)rt_path_trace_v2<2, false> : (const void*)rt_path_trace_v2<1, false>)
-                        : policy == 2 ? (const void*)rt_path_trace<2, false> : policy == 1 ? (const void*)rt_path_trace<1, false> : (const void*)rt_path_trace<0, false>;
+    const void* fn = policy == 2 ? (const void*)rt_path_trace<2, false> : policy == 1 ? (const void*)rt_path_trace<1, false> : (const void*)rt_path_trace<0, false>;
     int per_sm = 0, sms = 0;
     CK(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, 256, 0));
     CK(c, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device));
@@ -789,15 +832,7 @@ int launch_path(RtContext* c, const KParams& k, uint32_t traversal, uint32_t var
     uint32_t need = (k.n_work + 255u) / 256u;
     if (blocks > need) blocks = need;
     CK(c, cudaEventRecord(c->ev0, c->stream));
-    if (v2) {
-        if (k.counters) {
-            if (policy == 2) rt_path_trace_v2<2, true><<<blocks, 256, 0, c->stream>>>(k);
-            else rt_path_trace_v2<1, true><<<blocks, 256, 0, c->stream>>>(k);
-        } else {
-            if (policy == 2) rt_path_trace_v2<2, false><<<blocks, 256, 0, c->stream>>>(k);
-            else rt_path_trace_v2<1, false><<<blocks, 256, 0, c->stream>>>(k);
-        }
-    } else if (k.counters) {
+    if (k.counters) {
         if (policy == 2) rt_path_trace<2, true><<<blocks, 256, 0, c->stream>>>(k);
         else if (policy == 1) rt_path_trace<1, true><<<blocks, 256, 0, c->stream>>>(k);
         else rt_path_trace<0, true><<<blocks, 256, 0, c->stream>>>(k);
@@ -812,60 +847,6 @@ int launch_path(RtContext* c, const KParams& k, uint32_t traversal, uint32_t var
     c->launches++;
     c->last_traversal = policy == 2 ? RT_TRAVERSAL_REBUILT : (policy == 1 ? RT_TRAVERSAL_ORDERED : RT_TRAVERSAL_LITERAL);
     c->count_next = false;
-    return RT_OK;
-}
-
-// EXTENSION path tracing as a wavefront: per sample one generate, per depth one extend +
-// one shade launch; queue lengths stay on the device (no host sync inside the frame).
-int launch_wavefront(RtContext* c, KParams k, uint32_t traversal) {
-    if (k.n_work == 0) return RT_OK;
-    int policy = pick_policy(c, k, traversal);
-    if (policy < 1) return -100; // not available for the literal policy: caller falls back to the megakernel
-    size_t P = k.n_work;
-    if (c->wf_state.reserve(P * 4) < 0 || c->wf_hit.reserve(P) < 0 || c->wf_queue[0].reserve(P) < 0 ||
-        c->wf_queue[1].reserve(P) < 0 || c->wf_ctrl.reserve(1) < 0)
-        return fail(c, RT_ERR_CUDA, "wavefront cudaMalloc failed for %zu paths", P);
-    WfBuffers w;
-    w.state = c->wf_state.ptr; w.hit = c->wf_hit.ptr; w.queue[0] = c->wf_queue[0].ptr; w.queue[1] = c->wf_queue[1].ptr;
-    w.ctrl = c->wf_ctrl.ptr;
-    k.wf_rebuilt = policy == 2 ? 1u : 0u;
-    const bool count = k.counters != nullptr;
-    int per_sm = 0, sms = 0;
-    const void* fn = policy == 2 ? (const void*)wf_extend<2, false> : (const void*)wf_extend<1, false>;
-    CK(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, 256, 0));
-    CK(c, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device));
-    uint32_t ext_blocks = (uint32_t)(per_sm > 0 ? per_sm : 1) * (uint32_t)sms;
-    uint32_t full_blocks = (uint32_t)((P + 255) / 256);
-    if (ext_blocks > full_blocks) ext_blocks = full_blocks;
-    CK(c, cudaEventRecord(c->ev0, c->stream));
-    CK(c, cudaMemsetAsync(c->wf_ctrl.ptr, 0, sizeof(WfCtrl), c->stream));
-    for (uint32_t s = k.first_sample; s < k.first_sample + k.spp; s++) {
-        if (s != k.first_sample) CK(c, cudaMemsetAsync(c->wf_ctrl.ptr, 0, 16, c->stream)); // n[0], n[1], head
-        wf_generate<<<full_blocks, 256, 0, c->stream>>>(k, w, s);
-        for (uint32_t d = 0; d <= k.path_max_depth; d++) {
-            int qi = (int)(d & 1u);
-            if (policy == 2) { if (count) wf_extend<2, true><<<ext_blocks, 256, 0, c->stream>>>(k, w, qi); else wf_extend<2, false><<<ext_blocks, 256, 0, c->stream>>>(k, w, qi); }
-            else { if (count) wf_extend<1, true><<<ext_blocks, 256, 0, c->stream>>>(k, w, qi); else wf_extend<1, false><<<ext_blocks, 256, 0, c->stream>>>(k, w, qi); }
-            if (count) wf_shade<true><<<full_blocks, 256, 0, c->stream>>>(k, w, qi, s);
-            else wf_shade<false><<<full_blocks, 256, 0, c->stream>>>(k, w, qi, s);
-            c->launches += 2;
-        }
-        c->launches++;
-    }
-    CK(c, cudaGetLastError());
-    // publish the segment count (and instrumentation) where rt_last_segments / rt_read_counters look
-    CK(c, cudaMemcpyAsync(c->dcounters.ptr + 6, &c->wf_ctrl.ptr->segments, 8, cudaMemcpyDeviceToDevice, c->stream));
-    if (count) {
-        CK(c, cudaMemcpyAsync(c->dcounters.ptr + 0, &c->wf_ctrl.ptr->c[0], 16, cudaMemcpyDeviceToDevice, c->stream)); // box, tri
-        CK(c, cudaMemcpyAsync(c->dcounters.ptr + 2, &c->wf_ctrl.ptr->segments, 8, cudaMemcpyDeviceToDevice, c->stream));
-        CK(c, cudaMemcpyAsync(c->dcounters.ptr + 3, &c->wf_ctrl.ptr->c[2], 16, cudaMemcpyDeviceToDevice, c->stream)); // shaded, fallbacks
-        CK(c, cudaMemcpyAsync(c->dcounters.ptr + 8, &c->wf_ctrl.ptr->c[4], 8, cudaMemcpyDeviceToDevice, c->stream));  // refills
-    }
-    CK(c, cudaEventRecord(c->ev1, c->stream));
-    c->timed = true;
-    c->last_traversal = policy == 2 ? RT_TRAVERSAL_REBUILT : RT_TRAVERSAL_ORDERED;
-    c->count_next = false;
-    c->last_was_wavefront = true;
     return RT_OK;
 }
 
@@ -1087,7 +1068,6 @@ int rt_dispatch(RtContext* c, const RtPushConstants* pc) {
     k.channel = channel;
     k.triangles_per_buffer = pc->triangles_per_buffer;
     k.triangle_count = pc->triangle_count;
-    k.n_mats = (uint32_t)c->n_mats; // materials.len() is the bound buffer's length (lib.rs:307)
     uint32_t bw = (k.rect_w + 15u) / 16u, bh = (k.rect_h + 15u) / 16u; // src/compute.rs:248-250
     return launch(c, k, bw * bh, RT_TRAVERSAL_AUTO);
 }
@@ -1099,6 +1079,8 @@ int rt_render_frame(RtContext* c, const RtCamera* cam, const RtFrameParams* fp) 
     if (fp->mode > RT_MODE_PATH) return fail(c, RT_ERR_INVALID_ARGUMENT, "rt_render_frame: mode %u unknown", fp->mode);
     if (fp->mode == RT_MODE_PATH && (fp->spp == 0 || fp->max_depth > 255))
         return fail(c, RT_ERR_INVALID_ARGUMENT, "rt_render_frame: path mode needs spp >= 1 and max_depth <= 255");
+    if (fp->mode == RT_MODE_PATH && fp->_reserved[0] != 0 && fp->_reserved[0] != 1 && fp->_reserved[0] != 4)
+        return fail(c, RT_ERR_INVALID_ARGUMENT, "rt_render_frame: path engine %u unknown (0 auto, 1 megakernel, 4 streaming wavefront)", fp->_reserved[0]);
     CK(c, cudaSetDevice(c->device));
     if ((r = prepare_relayout(c)) != RT_OK) return r;
     KParams k;
@@ -1118,7 +1100,7 @@ int rt_render_frame(RtContext* c, const RtCamera* cam, const RtFrameParams* fp) 
     }
     k.cur_depth = 0; k.max_depth = 4; // PushConstants::new, shared/src/lib.rs:1088
     k.reset_accum = fp->reset_accum;
-    k.triangles_per_buffer = RT_MAX_TRIANGLES_PER_BUFFER;
+    k.triangles_per_buffer = c->tpb;
     k.triangle_count = (uint32_t)c->n_tris;
     uint32_t my_tiles = k.n_tiles_total > k.tile_phase ? (k.n_tiles_total - k.tile_phase + k.tile_stride - 1) / k.tile_stride : 0;
     if (fp->mode == RT_MODE_PATH) {
@@ -1129,18 +1111,15 @@ int rt_render_frame(RtContext* c, const RtCamera* cam, const RtFrameParams* fp) 
         CK(c, cudaMemsetAsync(c->dcounters.ptr + 6, 0, 2 * sizeof(unsigned long long), c->stream));
         c->last_was_wavefront = false;
         c->wv_event_stage.clear();
-        // _reserved[0] selects the path-tracing engine: 0 auto = 4 where a re-laid-out traversal policy is
-        // available (fastest measured on C3 and C4), else 1; 1 megakernel with path regeneration;
-        // 2 per-sample wavefront pipeline; 3 state-machine megakernel; 4 streaming wavefront (rt_wave.cuh)
-        if (fp->_reserved[0] == 2) {
-            int wr = launch_wavefront(c, k, fp->traversal);
-            if (wr != -100) return wr;
-        }
+        // _reserved[0] selects the path-tracing engine: 0 auto = the streaming wavefront engine (rt_wave.cuh)
+        // where a re-laid-out traversal policy is available, else the megakernel; 1 megakernel with path
+        // regeneration (rt_path_trace: the LITERAL policy's engine and the cross-check of the wave engine);
+        // 4 streaming wavefront, megakernel if unavailable
         if (fp->_reserved[0] == 4 || fp->_reserved[0] == 0) {
             int wr = launch_wave(c, k, fp->traversal);
             if (wr != -100) return wr;
         }
-        return launch_path(c, k, fp->traversal, fp->_reserved[0]);
+        return launch_path(c, k, fp->traversal);
     }
     return launch(c, k, my_tiles * 16u, fp->traversal);
 }
@@ -1172,7 +1151,7 @@ int rt_run_compute(RtContext* c, const RtCamera* cam, int needs_recompute) {
             pc.tile_offset[0] = ox; pc.tile_offset[1] = oy;
             pc.tile_size_packed = rt_pack_tile_size(tw, th);
             pc.total_tiles[0] = c->tiles_x; pc.total_tiles[1] = c->tiles_y;
-            pc.triangles_per_buffer = RT_MAX_TRIANGLES_PER_BUFFER;
+            pc.triangles_per_buffer = c->tpb; // buffer_manager.triangles_per_buffer, src/compute.rs:239
             pc.metadata_offsets = c->offsets;
             pc.packed_flags = rt_pack_flags(ch, 0, 4, 0);
             pc.frame_seed = 0;

@@ -51,7 +51,8 @@ struct KParams {
     const RtTriangle* tris;
     uint64_t n_tris;
     uint32_t triangles_per_buffer;     // value in the push constants
-    uint32_t ctx_triangles_per_buffer; // actual split of the bound buffers
+    uint32_t ctx_triangles_per_buffer; // length of every bound triangle buffer (BufferManager.triangles_per_buffer)
+    uint32_t n_tri_buffers;            // bound buffers that exist; binding k >= this aliases buffer 0 (src/renderer.rs:680-693)
     uint32_t triangle_count;           // push_constants.triangle_count (brute-force loop bound)
     const RtMaterial* mats;
     uint32_t n_mats;
@@ -66,6 +67,7 @@ struct KParams {
     const uint32_t* leaf_of_pos;   // uploaded leaf node of every triangle_indices position
     uint32_t broot_ref;
     float broot_min[3], broot_max[3];
+    float rebuilt_far;             // REBUILT: ray origins with a coordinate beyond this take the literal policy
     const float4* cert_box;        // [2 * uploaded node]: (min, max) of the uploaded leaves, aligned copies of the metadata words
     const uint4* bqnodes;          // the same tree as 2 x uint4 per node: 16-bit boxes on the grid below (rt_lbvh.cuh)
     float bq_origin[3], bq_scale[3];
@@ -82,7 +84,6 @@ struct KParams {
     uint32_t n_work;                 // pixels in this launch's work list (4096 per assigned split tile)
     unsigned int* work_counter;      // persistent-thread work fetch
     unsigned long long* seg_counter; // ray segments traced (the Mrays/s numerator)
-    uint32_t wf_rebuilt;             // wavefront: hit slots index btris (REBUILT) rather than wtris
 };
 
 struct Ray {
@@ -223,21 +224,28 @@ __device__ __forceinline__ bool slab_fma(V3 inv, V3 oinv, V3 bmin, V3 bmax, floa
 }
 
 // ------------------------------------------------- LITERAL closest-hit policy
-// shader/src/triangle_access.rs:18-61.  The reference binds the flat triangle
-// array as <=3 buffers of ctx_triangles_per_buffer; index arithmetic uses the
-// push-constant value.
+// shader/src/triangle_access.rs:18-61 over the buffers the reference binds: max(1, ceil(n / B)) buffers of
+// exactly B = BufferManager.triangles_per_buffer zero-initialised entries each (src/buffers.rs:93-99, 274-325),
+// binding k = buffer k if it exists, else buffer 0 again (src/renderer.rs:680-693).  The buffer index / local
+// index arithmetic uses the push-constant value `tpb_pc`.  Returns false for "invalid" (buffer > 2 or local
+// index past the bound length); otherwise *flat is the position in the flat uploaded array (it may lie past the
+// uploaded count: the zero-filled tail of a buffer).
+__host__ __device__ __forceinline__ bool resolve_bound_triangle(uint32_t index, uint32_t tpb_pc, uint32_t tpb_ctx,
+                                                                uint32_t n_buffers, uint64_t* flat) {
+    if (tpb_pc == 0u) return false; // the reference would trap on the division; uploads never send 0
+    uint32_t bi = index / tpb_pc;
+    uint64_t li = index % tpb_pc;
+    if (bi > 2u || li >= tpb_ctx) return false;
+    if (bi >= n_buffers) bi = 0u;
+    *flat = (uint64_t)bi * tpb_ctx + li;
+    return true;
+}
 __device__ __forceinline__ bool fetch_triangle_ref(const KParams& p, uint32_t index, V3* v0, V3* v1, V3* v2,
                                                    uint32_t* mat) {
-    uint32_t tpb = p.triangles_per_buffer;
-    if (tpb == 0u) return false;
-    uint32_t bi = index / tpb;
-    uint64_t li = index % tpb;
-    if (bi > 2u) return false;
-    uint64_t base = (uint64_t)bi * p.ctx_triangles_per_buffer;
-    uint64_t len = p.n_tris > base ? p.n_tris - base : 0;
-    if (len > p.ctx_triangles_per_buffer) len = p.ctx_triangles_per_buffer;
-    if (li >= len) return false;
-    const uint4 t = __ldg(reinterpret_cast<const uint4*>(p.tris) + base + li);
+    uint64_t gi;
+    if (!resolve_bound_triangle(index, p.triangles_per_buffer, p.ctx_triangles_per_buffer, p.n_tri_buffers, &gi)) return false;
+    uint4 t = make_uint4(0u, 0u, 0u, 0u); // zero-initialised tail of a bound buffer
+    if (gi < p.n_tris) t = __ldg(reinterpret_cast<const uint4*>(p.tris) + gi);
     uint64_t vo = p.off.vertices_offset;
     *v0 = mk(meta_f(p, vo + (uint64_t)t.x * 3), meta_f(p, vo + (uint64_t)t.x * 3 + 1), meta_f(p, vo + (uint64_t)t.x * 3 + 2));
     *v1 = mk(meta_f(p, vo + (uint64_t)t.y * 3), meta_f(p, vo + (uint64_t)t.y * 3 + 1), meta_f(p, vo + (uint64_t)t.y * 3 + 2));
@@ -394,7 +402,9 @@ __device__ void closest_triangle_ordered(const KParams& p, const Ray& ray, float
 __device__ void closest_triangle_rebuilt(const KParams& p, const Ray& ray, float max_t, TriBest& b) {
     // zero (or so tiny that o/d overflows) direction components: certification argument and the
     // FMA slab do not apply -> literal policy
-    if (!(fabsf(ray.d.x) >= 1e-30f && fabsf(ray.d.y) >= 1e-30f && fabsf(ray.d.z) >= 1e-30f)) { closest_triangle_literal(p, ray, max_t, b); b.n_fallback = 1; return; }
+    // origins far outside the scene: the rounding of the exact tests outgrows the boxes' pad (rt_lbvh.cuh)
+    if (!(fabsf(ray.d.x) >= 1e-30f && fabsf(ray.d.y) >= 1e-30f && fabsf(ray.d.z) >= 1e-30f) ||
+        !(fmaxf(fmaxf(fabsf(ray.o.x), fabsf(ray.o.y)), fabsf(ray.o.z)) <= p.rebuilt_far)) { closest_triangle_literal(p, ray, max_t, b); b.n_fallback = 1; return; }
     b.t = max_t; b.hit = false; b.prim = 0xFFFFFFFFu; b.mat = 0xFFFFFFFFu; b.n_box = 1; b.n_tri = 0;
     uint32_t best_pos = 0u;
     uint32_t cur = p.broot_ref;
@@ -650,6 +660,12 @@ __global__ void __launch_bounds__(256) rt_trace_shade(const __grid_constant__ KP
         else if (channel == 1u) o.y = (unsigned char)unorm8(color.y);
         else o.z = (unsigned char)unorm8(color.z);
         p.chan[channel][pix] = o;
+        {   // main_fs (lib.rs:368-391) samples the three channel textures: component c of the composite is
+            // whatever the last channel-c dispatch wrote, so the dispatch itself keeps it up to date
+            unsigned char* cp = reinterpret_cast<unsigned char*>(p.composite + pix);
+            cp[channel] = channel == 0u ? o.x : (channel == 1u ? o.y : o.z);
+            cp[3] = 255;
+        }
         if (p.outputs & RT_OUT_ACCUM) {
             float4 a = p.accum[pix];
             if (channel == 0u) a.x = color.x; else if (channel == 1u) a.y = color.y; else a.z = color.z;
@@ -702,6 +718,61 @@ struct SimpleRng { // shader/src/wavefront.rs:46-72
     __device__ __forceinline__ float next_f32() { return (float)(next_u32() >> 8) / 16777216.0f; }
     __device__ __forceinline__ float next_f32_signed() { return next_f32() * 2.0f - 1.0f; }
 };
+
+// SPEC.md steps 3.2-3.8 for one path segment whose closest hit is `h` — the ONE definition of the extension's
+// bounce semantics on the device (rt_path_trace and wv_shade both call it; the oracle's twin is path_sample in
+// oracle/rt_oracle.cpp).  Adds the segment's radiance to L; returns true when the path ends here, else ray /
+// throughput / depth describe the continuation segment.
+__device__ __forceinline__ bool path_bounce(const KParams& p, const Hit& h, Ray& ray, V3& tp, V3& L, SimpleRng& rng,
+                                            uint32_t& depth) {
+    if (h.kind == 0u) { L = L + mk(0.1f, 0.2f, 0.3f) * tp; return true; }              // 3.2 miss: sky
+    if (h.material_id >= p.n_mats) { L = L + mk(1.0f, 0.0f, 1.0f) * tp; return true; } // 3.3 invalid material
+    MatEval m = load_material(p, h.material_id);
+    L = L + shade_hit_m(p, h, m, 0xFFu) * tp;                                          // 3.3
+    if (depth == p.path_max_depth) return true;                                        // 3.4
+    if (depth >= 3u) {                                                                 // 3.5 Russian roulette
+        float pr = fminf(fmaxf(fmaxf(fmaxf(tp.x, tp.y), tp.z), 0.05f), 1.0f);
+        float r = rng.next_f32();
+        if (r > pr) return true;
+        tp = mk(tp.x / pr, tp.y / pr, tp.z / pr);
+    }
+    float r0 = rng.next_f32();                                                         // 3.6
+    V3 u = mk(0.0f, 0.0f, 0.0f);
+    for (int k = 0; k < 8; k++) {
+        float a = rng.next_f32_signed(), bb = rng.next_f32_signed(), cc = rng.next_f32_signed();
+        float q = a * a + bb * bb + cc * cc;
+        if (q > 1e-6f && q <= 1.0f) { u = mk(a, bb, cc) * (1.0f / sqrtf(q)); break; }
+    }
+    V3 d = ray.d, n = h.normal;                                                        // 3.7
+    float cosi = dot3(n, d);
+    V3 nf = cosi < 0.0f ? n : -n;
+    V3 w = nf + u;
+    if (dot3(w, w) < 1e-8f) w = nf;
+    w = normalize3(w);
+    float T = fminf(fmaxf(m.transmission, 0.0f), 1.0f);                                // 3.8
+    V3 dir;
+    float side = 1.0f;
+    if (T > 0.0f && r0 < T) {
+        float eta = cosi < 0.0f ? 1.0f / m.ior : m.ior;
+        float c1 = -dot3(d, nf);
+        float k = 1.0f - eta * eta * (1.0f - c1 * c1);
+        if (k < 0.0f) dir = d - nf * (2.0f * dot3(d, nf));
+        else { dir = d * eta + nf * (eta * c1 - sqrtf(k)); side = -1.0f; }
+        dir = normalize3(dir);
+    } else if (m.metallic > 0.5f) {
+        V3 mr = d - nf * (2.0f * dot3(d, nf));
+        dir = mr * (1.0f - m.roughness) + w * m.roughness;
+        if (dot3(dir, dir) < 1e-8f || dot3(dir, nf) <= 0.0f) dir = w;
+        dir = normalize3(dir);
+    } else {
+        dir = w;
+    }
+    tp = tp * m.albedo;
+    ray.o = h.point + nf * (side * 1e-3f);
+    ray.d = dir;
+    depth++;
+    return false;
+}
 
 __device__ __forceinline__ bool work_to_pixel(const KParams& p, uint32_t idx, uint32_t* px, uint32_t* py) {
     uint32_t tile_local = idx >> 12, within = idx & 4095u; // 4096 work items per 64x64 split tile
@@ -763,57 +834,7 @@ __global__ void __launch_bounds__(256) rt_path_trace(const __grid_constant__ KPa
         if (depth == 0u && s == 0u && (p.outputs & RT_OUT_HITS))
             reinterpret_cast<uint4*>(p.hits)[(size_t)py * p.width + px] =
                 make_uint4(h.kind, h.prim, __float_as_uint(h.t), h.material_id);
-        bool end = false;
-        if (h.kind == 0u) { L = L + mk(0.1f, 0.2f, 0.3f) * tp; end = true; }
-        else if (h.material_id >= p.n_mats) { L = L + mk(1.0f, 0.0f, 1.0f) * tp; end = true; }
-        else {
-            MatEval m = load_material(p, h.material_id);
-            L = L + shade_hit_m(p, h, m, 0xFFu) * tp;
-            if (depth == p.path_max_depth) end = true;
-            if (!end && depth >= 3u) { // Russian roulette
-                float pr = fminf(fmaxf(fmaxf(fmaxf(tp.x, tp.y), tp.z), 0.05f), 1.0f);
-                float r = rng.next_f32();
-                if (r > pr) end = true;
-                else tp = mk(tp.x / pr, tp.y / pr, tp.z / pr);
-            }
-            if (!end) {
-                float r0 = rng.next_f32();
-                V3 u = mk(0.0f, 0.0f, 0.0f);
-                for (int k = 0; k < 8; k++) {
-                    float a = rng.next_f32_signed(), bb = rng.next_f32_signed(), cc = rng.next_f32_signed();
-                    float q = a * a + bb * bb + cc * cc;
-                    if (q > 1e-6f && q <= 1.0f) { u = mk(a, bb, cc) * (1.0f / sqrtf(q)); break; }
-                }
-                V3 d = ray.d, n = h.normal;
-                float cosi = dot3(n, d);
-                V3 nf = cosi < 0.0f ? n : -n;
-                V3 w = nf + u;
-                if (dot3(w, w) < 1e-8f) w = nf;
-                w = normalize3(w);
-                float T = fminf(fmaxf(m.transmission, 0.0f), 1.0f);
-                V3 dir;
-                float side = 1.0f;
-                if (T > 0.0f && r0 < T) {
-                    float eta = cosi < 0.0f ? 1.0f / m.ior : m.ior;
-                    float c1 = -dot3(d, nf);
-                    float k = 1.0f - eta * eta * (1.0f - c1 * c1);
-                    if (k < 0.0f) dir = d - nf * (2.0f * dot3(d, nf));
-                    else { dir = d * eta + nf * (eta * c1 - sqrtf(k)); side = -1.0f; }
-                    dir = normalize3(dir);
-                } else if (m.metallic > 0.5f) {
-                    V3 mr = d - nf * (2.0f * dot3(d, nf));
-                    dir = mr * (1.0f - m.roughness) + w * m.roughness;
-                    if (dot3(dir, dir) < 1e-8f || dot3(dir, nf) <= 0.0f) dir = w;
-                    dir = normalize3(dir);
-                } else {
-                    dir = w;
-                }
-                tp = tp * m.albedo;
-                ray.o = h.point + nf * (side * 1e-3f);
-                ray.d = dir;
-                depth++;
-            }
-        }
+        const bool end = path_bounce(p, h, ray, tp, L, rng, depth); // steps 3.2-3.8
         if (end) { // step 4
             sum = sum + L; wsum = wsum + 1.0f; s++;
             if (s == s_end) {

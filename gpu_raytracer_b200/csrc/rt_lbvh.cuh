@@ -23,6 +23,8 @@
 #endif
 // REBUILT leaf ref: bit31 | (count-1) << 28 | first sorted slot (28 bits)
 #define RT_LBVH_MAX_PRIMS (1u << 28)
+// rays starting further than this many scene magnitudes from the coordinate origin take the literal policy
+#define RT_REBUILT_FAR 16.0f
 
 namespace lbvh {
 
@@ -179,11 +181,18 @@ __global__ void tree_depth(const uint32_t* __restrict__ parent_internal, const u
     if ((threadIdx.x & 31u) == 0 && d) atomicMax(out_max, d);
 }
 
-__device__ __forceinline__ void inflate(float4& lo, float4& hi) {
-    // conservative boxes: a Möller–Trumbore hit implies the true ray passes within a few
-    // ulps (relative to coordinate magnitude) of the triangle; 2^-16 relative is ~100x that
+// Conservative boxes.  A Möller–Trumbore hit implies that the true ray passes within a few ulps of the triangle,
+// where the ulp is that of the LARGEST coordinate the test handles: the scene's coordinates and the ray origin
+// (s = o - v0, the cross and dot products over it), not the box's own.  Every box is therefore padded by the same
+// scene-wide amount, 2^-16 of the scene magnitude M = max |coordinate| of the root box, and rays whose origin lies
+// further than RT_REBUILT_FAR * M from the coordinate origin do not use this tree at all (they take the literal
+// policy; see closest_triangle_rebuilt / wv_extend): inside that range the rounding of the exact test (a few
+// 2^-24 * 17 M) and of the FMA slab test (2^-23 * 16 M) stay below 2^-18 M, a quarter of the pad.
+__host__ __device__ __forceinline__ float scene_pad(float4 lo, float4 hi) {
     float m = fmaxf(fmaxf(fmaxf(fabsf(lo.x), fabsf(hi.x)), fmaxf(fabsf(lo.y), fabsf(hi.y))), fmaxf(fabsf(lo.z), fabsf(hi.z)));
-    float pad = m * 1.52587890625e-05f + 1e-30f;
+    return m * 1.52587890625e-05f + 1e-30f;
+}
+__device__ __forceinline__ void inflate(float4& lo, float4& hi, float pad) {
     lo.x -= pad; lo.y -= pad; lo.z -= pad; hi.x += pad; hi.y += pad; hi.z += pad;
 }
 
@@ -210,18 +219,20 @@ __device__ __forceinline__ uint32_t emit_ref(uint32_t child, const uint2* __rest
 // two-child 64-byte nodes in the layout rt_kernels.cuh traverses
 __global__ void emit_wide(const float4* __restrict__ pbox, const uint32_t* __restrict__ sorted_pos, uint32_t n,
                           const uint2* __restrict__ children, const uint2* __restrict__ range,
-                          const float4* __restrict__ nbox, const uint32_t* __restrict__ compact, float4* __restrict__ wnodes) {
+                          const float4* __restrict__ nbox, const uint32_t* __restrict__ compact,
+                          const float* __restrict__ grid, float4* __restrict__ wnodes) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (n < 2 || i >= n - 1) return;
     uint2 r = range[i];
     if (r.y - r.x + 1u <= RT_LBVH_LEAF) return; // inside / is a collapsed leaf: never visited
     uint2 ch = children[i];
+    const float pad = grid[6];
     float4 lo[2], hi[2];
     uint32_t c[2] = {ch.x, ch.y};
     for (int k = 0; k < 2; k++) {
         const float4* s = (c[k] & 0x80000000u) ? pbox + (size_t)sorted_pos[c[k] & 0x7FFFFFFFu] * 2 : nbox + (size_t)c[k] * 2;
         lo[k] = s[0]; hi[k] = s[1];
-        inflate(lo[k], hi[k]);
+        inflate(lo[k], hi[k], pad);
     }
     float4* q = wnodes + (size_t)compact[i] * 4;
     q[0] = make_float4(lo[0].x, lo[0].y, lo[0].z, hi[0].x);
@@ -239,10 +250,12 @@ __global__ void emit_wide(const float4* __restrict__ pbox, const uint32_t* __res
 // covers the directed rounding of the division, the second the rounding of the ray-side constant
 // B2 = (O - o) / d - 2^23 S / d (half a cell, see wv_extend), the world-space pad everything the 64-byte
 // layout's pad covers.
-// grid[0..2] = origin O, grid[3..5] = cell size S
+// grid[0..2] = origin O, grid[3..5] = cell size S, grid[6] = the scene-wide pad (scene_pad of the root box)
 __global__ void quant_grid(const float4* __restrict__ root_box, float* __restrict__ grid) {
     float4 lo = root_box[0], hi = root_box[1];
-    inflate(lo, hi);
+    const float pad = scene_pad(lo, hi);
+    grid[6] = pad;
+    inflate(lo, hi, pad);
     const float l[3] = {lo.x, lo.y, lo.z}, h[3] = {hi.x, hi.y, hi.z};
     for (int k = 0; k < 3; k++) {
         float s = fmaxf((h[k] - l[k]) / 65000.0f, 1e-30f);
@@ -265,11 +278,12 @@ __global__ void emit_quant(const float4* __restrict__ pbox, const uint32_t* __re
     uint2 r = range[i];
     if (r.y - r.x + 1u <= RT_LBVH_LEAF) return;
     uint2 ch = children[i];
+    const float pad = grid[6];
     uint32_t c[2] = {ch.x, ch.y}, w[6];
     for (int k = 0; k < 2; k++) {
         const float4* s = (c[k] & 0x80000000u) ? pbox + (size_t)sorted_pos[c[k] & 0x7FFFFFFFu] * 2 : nbox + (size_t)c[k] * 2;
         float4 lo = s[0], hi = s[1];
-        inflate(lo, hi);
+        inflate(lo, hi, pad);
         w[k * 3] = quant_pair(lo.x, hi.x, grid[0], grid[3]);
         w[k * 3 + 1] = quant_pair(lo.y, hi.y, grid[1], grid[4]);
         w[k * 3 + 2] = quant_pair(lo.z, hi.z, grid[2], grid[5]);

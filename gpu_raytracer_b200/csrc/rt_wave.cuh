@@ -287,7 +287,9 @@ __global__ void __launch_bounds__(256, WV_BLOCKS) wv_extend(const __grid_constan
                         if (POLICY == 2) {
                             // zero / tiny direction components: neither the certification argument nor the
                             // FMA slab applies (closest_triangle_rebuilt) -> wv_shade runs the literal policy
-                            if (!(fabsf(dx) >= 1e-30f && fabsf(dy) >= 1e-30f && fabsf(dz) >= 1e-30f)) { literal = true; cur = EMPTY; }
+                            // origins far outside the scene: the exact tests' rounding outgrows the boxes' pad (rt_lbvh.cuh)
+                            if (!(fabsf(dx) >= 1e-30f && fabsf(dy) >= 1e-30f && fabsf(dz) >= 1e-30f) ||
+                                !(fmaxf(fmaxf(fabsf(ox), fabsf(oy)), fabsf(oz)) <= p.rebuilt_far)) { literal = true; cur = EMPTY; }
                             // boxes of the internal tree are conservative (inflated 2^-16 relative), so
                             // the slab test may use t = b * inv - o * inv with one FMA per plane
                             ix = 1.0f / dx; iy = 1.0f / dy; iz = 1.0f / dz;
@@ -585,58 +587,8 @@ __global__ void __launch_bounds__(256, 3) wv_shade(const __grid_constant__ KPara
                 work_to_pixel(p, idx, &px, &py);
                 reinterpret_cast<uint4*>(p.hits)[(size_t)py * p.width + px] = make_uint4(h.kind, h.prim, __float_as_uint(h.t), h.material_id);
             }
-            bool end = false;
-            if (h.kind == 0u) { L = L + mk(0.1f, 0.2f, 0.3f) * tp; end = true; }
-            else if (h.material_id >= p.n_mats) { L = L + mk(1.0f, 0.0f, 1.0f) * tp; end = true; }
-            else {
-                MatEval m = load_material(p, h.material_id);
-                L = L + shade_hit_m(p, h, m, 0xFFu) * tp;
-                if (depth == p.path_max_depth) end = true;
-                if (!end && depth >= 3u) { // Russian roulette
-                    float pr = fminf(fmaxf(fmaxf(fmaxf(tp.x, tp.y), tp.z), 0.05f), 1.0f);
-                    float r = rng.next_f32();
-                    if (r > pr) end = true;
-                    else tp = mk(tp.x / pr, tp.y / pr, tp.z / pr);
-                }
-                if (!end) {
-                    float r0 = rng.next_f32();
-                    V3 u = mk(0.0f, 0.0f, 0.0f);
-                    for (int k = 0; k < 8; k++) {
-                        float a = rng.next_f32_signed(), bb = rng.next_f32_signed(), cc = rng.next_f32_signed();
-                        float q = a * a + bb * bb + cc * cc;
-                        if (q > 1e-6f && q <= 1.0f) { u = mk(a, bb, cc) * (1.0f / sqrtf(q)); break; }
-                    }
-                    V3 d = ray.d, nn = h.normal;
-                    float cosi = dot3(nn, d);
-                    V3 nf = cosi < 0.0f ? nn : -nn;
-                    V3 wv = nf + u;
-                    if (dot3(wv, wv) < 1e-8f) wv = nf;
-                    wv = normalize3(wv);
-                    float T = fminf(fmaxf(m.transmission, 0.0f), 1.0f);
-                    V3 dir;
-                    float side = 1.0f;
-                    if (T > 0.0f && r0 < T) {
-                        float eta = cosi < 0.0f ? 1.0f / m.ior : m.ior;
-                        float c1 = -dot3(d, nf);
-                        float k = 1.0f - eta * eta * (1.0f - c1 * c1);
-                        if (k < 0.0f) dir = d - nf * (2.0f * dot3(d, nf));
-                        else { dir = d * eta + nf * (eta * c1 - sqrtf(k)); side = -1.0f; }
-                        dir = normalize3(dir);
-                    } else if (m.metallic > 0.5f) {
-                        V3 mr = d - nf * (2.0f * dot3(d, nf));
-                        dir = mr * (1.0f - m.roughness) + wv * m.roughness;
-                        if (dot3(dir, dir) < 1e-8f || dot3(dir, nf) <= 0.0f) dir = wv;
-                        dir = normalize3(dir);
-                    } else {
-                        dir = wv;
-                    }
-                    tp = tp * m.albedo;
-                    ray.o = h.point + nf * (side * 1e-3f);
-                    ray.d = dir;
-                    depth++;
-                    cont = true;
-                }
-            }
+            const bool end = path_bounce(p, h, ray, tp, L, rng, depth); // SPEC.md steps 3.2-3.8 (rt_kernels.cuh)
+            cont = !end;
             if (end) WV_ST(w.lbuf + (size_t)sl * p.n_work + idx, make_float4(L.x, L.y, L.z, 1.0f)); // SPEC.md step 4, summed by wv_resolve
         }
         // ---- survivors become the compact path list of the next depth (order within the warp kept)

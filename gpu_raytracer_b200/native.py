@@ -12,6 +12,7 @@ API_SYMBOLS = [
     "rt_update_triangles", "rt_update_materials", "rt_update_textures", "rt_update_texture_data",
     "rt_mark_scene_metadata_dirty", "rt_mark_triangles_dirty", "rt_mark_materials_dirty", "rt_mark_textures_dirty",
     "rt_mark_texture_data_dirty", "rt_mark_all_dirty", "rt_needs_update", "rt_triangles_per_buffer",
+    "rt_set_triangles_per_buffer",
     "rt_get_metadata_offsets", "rt_dispatch", "rt_run_compute", "rt_render_frame", "rt_read_channel_rgba8",
     "rt_read_composite_rgba8", "rt_read_accum_f32", "rt_write_accum_f32", "rt_read_hit_records", "rt_device_accum",
     "rt_device_composite", "rt_count_next_launch", "rt_read_counters", "rt_last_kernel_ms", "rt_launch_count",
@@ -53,6 +54,7 @@ def load():
         "rt_mark_materials_dirty": (None, [vp]), "rt_mark_textures_dirty": (None, [vp]),
         "rt_mark_texture_data_dirty": (None, [vp]), "rt_mark_all_dirty": (None, [vp]),
         "rt_needs_update": (i32, [vp]), "rt_triangles_per_buffer": (u32, [vp]),
+        "rt_set_triangles_per_buffer": (i32, [vp, u32]),
         "rt_get_metadata_offsets": (i32, [vp, vp]), "rt_dispatch": (i32, [vp, vp]),
         "rt_run_compute": (i32, [vp, vp, i32]), "rt_render_frame": (i32, [vp, vp, vp]),
         "rt_read_channel_rgba8": (i32, [vp, u32, vp]), "rt_read_composite_rgba8": (i32, [vp, vp]),

@@ -162,8 +162,12 @@ class Context:
 class BufferManager:
     """src/buffers.rs — same method names, same return values (`resized` bools)."""
 
-    def __init__(self, ctx):
+    def __init__(self, ctx, triangles_per_buffer=None):
+        """`triangles_per_buffer`: BufferManager::max_triangles_per_buffer (src/buffers.rs:49-53) for a host
+        built with another buffer-size limit; only before the first triangle upload."""
         self.ctx = ctx
+        if triangles_per_buffer is not None:
+            ctx._ck(ctx.lib.rt_set_triangles_per_buffer(ctx.handle, int(triangles_per_buffer)))
         self.triangles_per_buffer = int(ctx.lib.rt_triangles_per_buffer(ctx.handle))
 
     def update_scene_metadata(self, spheres, lights, bvh_nodes, triangle_indices, vertices):
@@ -248,6 +252,6 @@ class ComputeRenderer:
         fp["mode"], fp["outputs"], fp["spp"], fp["first_sample"] = mode, outputs, spp, first_sample
         fp["max_depth"], fp["base_seed"], fp["reset_accum"] = max_depth, base_seed, int(reset_accum)
         fp["tile_stride"], fp["tile_phase"], fp["traversal"] = tile_stride, tile_phase, traversal
-        fp["_reserved"][0] = variant  # path mode engine: 0 megakernel, 2 wavefront, 3 state-machine megakernel, 4 streaming wavefront (wave)
+        fp["_reserved"][0] = variant  # path mode engine: 0 auto, 1 megakernel, 4 streaming wavefront (wave)
         self.ctx._ck(self.ctx.lib.rt_render_frame(self.ctx.handle, cam.ctypes.data_as(C.c_void_p),
                                                   fp.ctypes.data_as(C.c_void_p)))

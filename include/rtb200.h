@@ -80,8 +80,8 @@ typedef struct RtFrameParams {
     uint32_t tile_stride;  /* multi-GPU tile split: this context renders the RT_SPLIT_TILE^2 */
     uint32_t tile_phase;   /*   tiles i with i % tile_stride == tile_phase (0,0 = all) */
     uint32_t traversal;    /* RT_TRAVERSAL_* */
-    uint32_t _reserved[2]; /* [0]: RT_MODE_PATH engine (0 auto; tuning/tests: 1 megakernel, 2 per-sample
-                            * wavefront, 3 state-machine megakernel, 4 streaming wavefront); [1]: 0 */
+    uint32_t _reserved[2]; /* [0]: RT_MODE_PATH engine (0 auto = streaming wavefront where a re-laid-out policy is
+                            * available, else megakernel; tuning/tests: 1 megakernel, 4 streaming wavefront); [1]: 0 */
 } RtFrameParams;
 
 /* Environment switches read by rt_render_frame (tuning and tests only; results never change):
@@ -124,8 +124,15 @@ void rt_mark_textures_dirty(RtContext* ctx);
 void rt_mark_texture_data_dirty(RtContext* ctx);
 void rt_mark_all_dirty(RtContext* ctx);
 int rt_needs_update(const RtContext* ctx);
-/* BufferManager.triangles_per_buffer (src/buffers.rs:49-53, 103) */
+/* BufferManager.triangles_per_buffer (src/buffers.rs:49-53, 103): length of every bound triangle buffer and the
+ * divisor run_compute puts into the push constants (src/compute.rs:239).  The reference derives it from a
+ * 128 MB buffer limit when the manager is constructed (8 388 608); rt_set_triangles_per_buffer stands for
+ * constructing the manager with another limit and is only accepted before the first triangle upload.  The
+ * flat device array keeps the reference's binding rule as index arithmetic: buffer k of max(1, ceil(n / B))
+ * holds triangles [k B, (k+1) B), zero-filled past n; a binding whose buffer does not exist aliases buffer 0
+ * (src/renderer.rs:680-693); buffer index > 2 is invalid (shader/src/triangle_access.rs:26-48). */
 uint32_t rt_triangles_per_buffer(const RtContext* ctx);
+int rt_set_triangles_per_buffer(RtContext* ctx, uint32_t triangles_per_buffer);
 /* offsets of the last metadata upload (what run_compute passes on, src/compute.rs:109-134) */
 int rt_get_metadata_offsets(const RtContext* ctx, RtSceneMetadataOffsets* out);
 
