@@ -143,6 +143,35 @@ def render(scene, width, height, wavefront=None, threads=None, camera=None, chan
                               sphere_tests=counters.sphere_tests, rays=counters.rays))
 
 
+def render_rects(scene, width, height, rects, camera=None, channels=(0, 1, 2), threads=None, policy=0, wavefront=None,
+                 triangles_per_buffer=None, offsets=None):
+    """Reference dispatches over arbitrary pixel rectangles [(x, y, w, h), ...] of the frame (each one
+    `process_color_channel` call per channel with that tile offset / size, src/compute.rs:212-251): lets a test
+    check a sparse set of rows or patches of a frame that is too large for the oracle as a whole.
+    `triangles_per_buffer` / `offsets` override what goes into the push constants (the shader trusts them)."""
+    bound = scene if isinstance(scene, BoundScene) else BoundScene(scene)
+    sc = bound.scene
+    cam = sc.camera if camera is None else camera
+    chans = [np.zeros((height, width, 4), np.uint8) for _ in range(3)]
+    radiance = np.zeros((height, width, 3), np.float32)
+    hits = np.zeros((height, width), abi.HitRecord)
+    mask = np.zeros((height, width), bool)
+    counters = OrcCounters()
+    for (x, y, w, h) in rects:
+        mask[y:y + h, x:x + w] = True
+        for ch in channels:
+            pc = push_constants_new([width, height], cam, len(sc.triangles), len(sc.materials), [x, y], [w, h], [1, 1],
+                                    bound.tpb if triangles_per_buffer is None else triangles_per_buffer,
+                                    bound.offsets if offsets is None else offsets, ch, wavefront=wavefront)
+            dispatch(bound, pc, chans[ch], radiance, hits, threads, counters, policy)
+    comp = np.zeros((height, width, 4), np.uint8)
+    lib().orc_composite(chans[0].ctypes.data, chans[1].ctypes.data, chans[2].ctypes.data, comp.ctypes.data,
+                        width * height)
+    return dict(channels=chans, composite=comp, radiance=radiance, hits=hits, mask=mask,
+                counters=dict(aabb_tests=counters.aabb_tests, tri_tests=counters.tri_tests,
+                              sphere_tests=counters.sphere_tests, rays=counters.rays))
+
+
 def render_path(scene, width, height, spp=1, max_depth=0, base_seed=1, first_sample=0, accum=None, rows=None,
                 threads=None, camera=None, policy=0, want_hits=True):
     """EXTENSION (SPEC.md): path-traced accumulation on the CPU.  Returns dict(accum HxWx4 f32,
