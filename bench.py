@@ -12,6 +12,7 @@ ranks.  `e2e`: the same frames through the C ABI with HOST buffers — scene
 upload from pinned host memory + render + composite read-back, wall clock.
 """
 import argparse
+import hashlib
 import json
 import os
 import subprocess
@@ -51,6 +52,40 @@ WORKLOADS = {
 }
 
 
+# The bounded CPU sample of each workload (cpu_baseline leg AND the --impl reference arm use the same one, so the two
+# figures are the same measurement): a centred band of rows of the workload's own frame, full spp and depth.
+# Sized for ~2-6 s on 16 host threads; the oracle hands 64-pixel spans to its pool, so even 2 rows keep every
+# thread busy.  Primary workloads: whole 128-row tile bands, three channel passes (the reference's own loop).
+CPU_SAMPLE_ROWS = {"c3": 8, "c3-smallleaf": 64, "c4": 48, "c5": 1, "c3-primary": 128, "c3-primary-smallleaf": 1080,
+                   "c2": 1080}
+
+
+def source_hash():
+    """sha256 over the native sources: ties an ncu summary under profiles/ to the build it was captured from."""
+    hsh = hashlib.sha256()
+    for d, exts in (("gpu_raytracer_b200/csrc", (".cu", ".cuh", ".cpp", "Makefile")), ("include", (".h",))):
+        for name in sorted(os.listdir(os.path.join(ROOT, d))):
+            if name.endswith(exts):
+                with open(os.path.join(ROOT, d, name), "rb") as f:
+                    hsh.update(name.encode() + b"\0" + f.read())
+    return hsh.hexdigest()[:16]
+
+
+def ncu_summary_for(workload):
+    """profiles/ncu_summary.json: {workload: {"src_hash": ..., "file": ..., per-kernel counters}} written by
+    scripts/ncu_extract.py from an `ncu --set full` capture.  Used only when it was captured from THIS build."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_summary.json")) as f:
+            rec = json.load(f).get(workload)
+    except Exception:
+        return None, "no profiles/ncu_summary.json"
+    if not rec:
+        return None, "no ncu capture of this workload in profiles/ncu_summary.json"
+    if rec.get("src_hash") != source_hash():
+        return None, "profiles/ncu_summary.json was captured from another build (src_hash %s != %s)" % (rec.get("src_hash"), source_hash())
+    return rec, rec.get("file")
+
+
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -58,10 +93,11 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
-    ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU work for the cpu_baseline sample")
+    ap.add_argument("--cpu-seconds", type=float, default=10.0,
+                    help="GPU arm: repeat the fixed cpu_baseline sample (CPU_SAMPLE_ROWS) until this much CPU time has passed")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--variant", type=int, default=0, help="path mode engine: 0 auto = streaming wavefront (default), 1 megakernel, "
-                                                           "2 per-sample wavefront, 3 state-machine megakernel")
+                                                           "4 streaming wavefront")
     ap.add_argument("--traversal", default="auto", choices=["auto", "literal", "ordered", "rebuilt"])
     ap.add_argument("--gather", default="peer", choices=["peer", "nccl"],
                     help="N > 1: how finished tiles reach rank 0: peer = P2P stores from the render kernels into rank 0's "
@@ -123,48 +159,59 @@ def measured_peaks():
         return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
-def cpu_baseline_sample(scene, wl, target_seconds):
-    """Times the oracle on a bounded band of rows of the same frame, all host threads.
-    Primary workloads: the reference's own loop (literal traversal, 3 channel passes per
-    tile).  Path workloads: the extension oracle (SPEC.md) with the literal traversal."""
+def cpu_sample_rows(args, wl):
+    n = min(CPU_SAMPLE_ROWS.get(args.workload, 8), wl["h"])
+    if wl["mode"] != "path":  # whole tile bands (src/compute.rs:194-209)
+        bands = max(1, n // 128)
+        total = (wl["h"] + 127) // 128
+        first = max(0, (total - bands) // 2)
+        return first * 128, min(wl["h"], (first + bands) * 128)
+    y0 = max(0, (wl["h"] - n) // 2)
+    return y0, y0 + n
+
+
+def cpu_baseline_sample(scene, wl, rows, bound=None, min_seconds=0.0):
+    """Times the oracle on a fixed band of rows of the same frame on all host threads, repeating the band until
+    `min_seconds` have passed.  Primary workloads: the reference's own loop (literal traversal, 3 channel passes
+    per tile).  Path workloads: the extension oracle (SPEC.md) with the literal traversal.  Returns the record
+    and the rendered rows (kept: the GPU frame is compared with them)."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import oracle_binding as ob
-    bound = ob.BoundScene(scene)
+    bound = bound or ob.BoundScene(scene)
     w, h = wl["w"], wl["h"]
     threads = ob.hardware_threads()
+    y0, y1 = rows
+    reps, dt, r = 0, 0.0, None
+    while reps == 0 or dt < min_seconds:
+        t0 = time.perf_counter()
+        if wl["mode"] == "path":
+            r = ob.render_path(bound, w, h, spp=wl["spp"], max_depth=wl["depth"], base_seed=1, rows=(y0, y1), threads=threads)
+        else:
+            r = ob.render(bound, w, h, rows=(y0, y1), threads=threads)
+        dt += time.perf_counter() - t0
+        reps += 1
     if wl["mode"] == "path":
-        spp, depth = wl["spp"], wl["depth"]
-        y = h // 2
-        t0 = time.perf_counter()
-        ob.render_path(bound, w, h, spp=1, max_depth=depth, rows=(y, y + 2), threads=threads, want_hits=False)
-        per_row_sample = max((time.perf_counter() - t0) / 2.0, 1e-4)  # one row, one sample
-        # prefer full spp on fewer rows so the sample is the workload's own mix of samples
-        nrows = int(max(2, min(h, target_seconds / (per_row_sample * spp))))
-        y0 = max(0, (h - nrows) // 2)
-        t0 = time.perf_counter()
-        r = ob.render_path(bound, w, h, spp=spp, max_depth=depth, rows=(y0, y0 + nrows), threads=threads, want_hits=False)
-        dt = time.perf_counter() - t0
-        return {"value": r["counters"]["rays"] / dt / 1e6, "unit": "Mrays/s", "cores": threads, "kind": "port",
-                "sample": "rows %d-%d of the %dx%d frame, %d spp, depth %d, literal traversal, %d ray segments, %.1f s"
-                          % (y0, y0 + nrows, w, h, spp, depth, r["counters"]["rays"], dt), "seconds": dt}
-    # probe: one 128-row band centred vertically, one channel, to size the sample
-    mid = (h // 2) // 128 * 128
-    t0 = time.perf_counter()
-    ob.render(bound, w, h, channels=(0,), rows=(mid, mid + 1), threads=threads)
-    band_cost = (time.perf_counter() - t0) * 3.0
-    n_bands_total = (h + 127) // 128
-    n_bands = int(max(1, min(n_bands_total, target_seconds // max(band_cost, 1e-3))))
-    first = max(0, (n_bands_total - n_bands) // 2)
-    rows = (first * 128, min(h, (first + n_bands) * 128))
-    t0 = time.perf_counter()
-    ob.render(bound, w, h, rows=rows, threads=threads)
-    dt = time.perf_counter() - t0
-    pixels = (rows[1] - rows[0]) * w
-    # the reference traces every pixel three times (one dispatch per colour channel);
-    # the metric counts one camera ray per pixel, like the GPU arm
-    return {"value": pixels / dt / 1e6, "unit": "Mrays/s", "cores": threads, "kind": "port",
-            "sample": "rows %d-%d of the %dx%d frame (%d of %d tile bands), 3 channel passes, literal traversal, %.1f s"
-                      % (rows[0], rows[1], w, h, n_bands, n_bands_total, dt), "seconds": dt}
+        rays = r["counters"]["rays"]
+        what = "%d spp, depth %d, literal traversal, %d ray segments" % (wl["spp"], wl["depth"], rays)
+        pixels = dict(accum=r["accum"][y0:y1].copy(), resolved=r["resolved"][y0:y1].copy())
+    else:
+        # the reference traces every pixel three times (one dispatch per colour channel);
+        # the metric counts one camera ray per pixel, like the GPU arm
+        rays = (y1 - y0) * w
+        what = "3 channel passes per 128x128 tile, literal traversal, %d pixels" % rays
+        pixels = dict(radiance=r["radiance"][y0:y1].copy(), composite=r["composite"][y0:y1].copy())
+    rec = {"value": rays * reps / dt / 1e6, "unit": "Mrays/s", "cores": threads, "threads_used": threads, "kind": "port",
+           "sample": "rows %d-%d of the %dx%d frame, %s, %.2f s per pass x %d" % (y0, y1, w, h, what, dt / reps, reps),
+           "seconds": dt / reps}
+    return rec, pixels
+
+
+def workload_config(wl, scene):
+    """The `config` both arms print: the workload only, nothing arm-specific."""
+    return {"workload": wl["desc"], "width": wl["w"], "height": wl["h"], "triangles": int(len(scene.triangles)),
+            "bvh_nodes": int(len(scene.bvh_nodes)), "spp": wl["spp"], "max_depth": wl["depth"],
+            "semantics": "extension (SPEC.md; the reference stubs bounces/spp)" if wl["mode"] == "path" else "reference",
+            "l2": "GPU arm: flushed between timed steps (512 MiB memset)"}
 
 
 def dist_setup(args):
@@ -199,34 +246,34 @@ def barrier(world):
 
 
 def run_reference(args, wl, world, rank):
-    """Reference arm: the reference's CPU implementation of the path.  The Rust crate
-    cannot be built here (no rustc; rust-gpu nightly + crates.io), so this is the
-    oracle port — literal traversal, three channel passes per tile — on all host
-    threads.  Each step is a bounded sample of the frame.  Rank 0 only."""
+    """Reference arm: the reference's CPU implementation of the path.  The Rust crate cannot be built here (no
+    rustc; rust-gpu nightly + crates.io), so this is the oracle port (literal traversal; primary workloads: three
+    channel passes per tile) on all host threads.  Each step is the SAME bounded sample the GPU arm's cpu_baseline
+    leg times (cpu_sample_rows).  Rank 0 only."""
     if rank != 0:
         return
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_binding as ob
     scene = build_scene(wl)
-    per_step = max(2.0, min(args.cpu_seconds, 120.0 / max(1, args.steps + args.warmup)))
+    bound = ob.BoundScene(scene)
+    rows = cpu_sample_rows(args, wl)
     vals, last = [], None
     for i in range(args.warmup + args.steps):
-        last = cpu_baseline_sample(scene, wl, per_step)
+        last, _ = cpu_baseline_sample(scene, wl, rows, bound)
         if i >= args.warmup:
             vals.append(last)
-    v = float(np.mean([x["value"] for x in vals]))
-    secs = float(np.mean([x["seconds"] for x in vals]))
+    secs = float(np.sum([x["seconds"] for x in vals]))
+    v = float(np.sum([x["value"] * x["seconds"] for x in vals]) / secs)  # total rays / total time
     line = {"impl": "reference", "metric": "Mrays/s", "value": v, "unit": "Mrays/s", "n_gpus": args.gpus,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": secs * 1e3, "higher_is_better": True,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": secs / len(vals) * 1e3, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": wl["desc"], "width": wl["w"], "height": wl["h"], "spp": wl["spp"],
-                       "max_depth": wl["depth"],
-                       "semantics": "extension (SPEC.md)" if wl["mode"] == "path" else "reference"},
-            "cpu_baseline": {"value": v, "unit": "Mrays/s", "cores": last["cores"], "kind": "port",
-                             "sample": last["sample"]},
+            "config": workload_config(wl, scene),
+            "traversal": "literal (the reference's own unordered, un-pruned DFS over the uploaded tree)",
+            "cpu_baseline": {"value": v, "unit": "Mrays/s", "cores": last["cores"], "threads_used": last["threads_used"],
+                             "kind": "port", "sample": last["sample"]},
             "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
-
-
 
 
 def sum_over_ranks(x, world):
@@ -400,7 +447,61 @@ def run_b200(args, wl, world, rank, local):
     if rank != 0:
         ctx.close()
         return
-    # ---- roofline of the dominant kernel: algorithmic bytes per launch / mean launch time (rank 0)
+
+    # ---- rank 0, N = 1: the reference-semantics primary frame of the same scene as a sub-record (north_star's
+    # ">= 1 Grays/s primary-ray throughput" target), device-timed and end to end like the main figure
+    primary = None
+    if world == 1 and path and args.workload == "c3":
+        pk = dict(outputs=abi.OUT_ACCUM | abi.OUT_COMPOSITE, traversal=trav)
+        for _ in range(3):
+            cr.render_frame(ps.camera, **pk)
+        ctx.synchronize()
+        p_ms = []
+        for _ in range(args.steps):
+            with torch.cuda.stream(stream):
+                flush.zero_()
+            cr.render_frame(ps.camera, **pk)
+            ctx.synchronize()
+            p_ms.append(ctx.last_kernel_ms)
+        p_e2e = []
+        for i in range(3 + args.steps):
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            bm.mark_all_dirty()
+            bm.upload_scene(ps)
+            cr.render_frame(ps.camera, **pk)
+            ctx.read_composite(host_img)
+            if i >= 3:
+                p_e2e.append((time.perf_counter() - t0) * 1e3)
+        primary = {"workload": WORKLOADS["c3-primary"]["desc"], "rays_per_frame": w * h,
+                   "value": w * h / (float(np.mean(p_ms)) * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_frame": float(np.mean(p_ms)),
+                   "e2e": {"value": w * h / (float(np.mean(p_e2e)) * 1e-3) / 1e6, "unit": "Mrays/s",
+                           "ms_per_step": float(np.mean(p_e2e)), "h2d_bytes_per_step": h2d_bytes,
+                           "d2h_bytes_per_step": int(host_img.nbytes)},
+                   "kernel": "rt_trace_shade", "traversal": trav_name(ctx.last_traversal)}
+        # leave the path frame in the context's buffers for the parity check below
+        render()
+        ctx.synchronize()
+
+    # ---- parity at the configured size: the cpu_baseline leg renders a band of rows of this very frame with the
+    # literal oracle; its pixels must equal the GPU frame's bit for bit
+    cpu_rec, parity = None, None
+    if world == 1 and not args.no_cpu_baseline:
+        rows = cpu_sample_rows(args, wl)
+        cpu_rec, px = cpu_baseline_sample(scene, wl, rows, min_seconds=args.cpu_seconds)
+        y0, y1 = rows
+        if path:
+            acc = ctx.read_accum()[y0:y1]
+            ok = bool(np.array_equal(acc.view(np.uint32), px["accum"].view(np.uint32)) and
+                      np.array_equal(ctx.read_composite()[y0:y1], px["resolved"]))
+        else:
+            acc = ctx.read_accum()[y0:y1, :, :3]
+            ok = bool(np.array_equal(acc.view(np.uint32), px["radiance"].view(np.uint32)) and
+                      np.array_equal(ctx.read_composite()[y0:y1], px["composite"]))
+        parity = {"parity_rows_checked": int(y1 - y0), "rows": [int(y0), int(y1)], "bit_exact": ok,
+                  "against": "literal-traversal oracle (oracle/rt_oracle.cpp), fp32 accumulation bits + rgba8 pixels"}
+
+    # ---- roofline of the dominant kernel (rank 0)
     n_lights = len(scene.lights)
     seg = max(cnt["segments"], 1)
     V, T, H = cnt["box_tests"] / seg, cnt["tri_tests"] / seg, cnt["shaded"] / seg
@@ -408,7 +509,7 @@ def run_b200(args, wl, world, rank, local):
     trav_bytes_per_ray = 48 * V + 56 * T + 20 * len(scene.spheres)            # closest hit (48 V + 56 T + 20 S)
     shade_bytes_per_ray = 128 * H + 52 * n_lights * H + out_bytes_per_pixel * my_pixels / seg  # 128 H + 52 L H + O
     bytes_per_ray = trav_bytes_per_ray + shade_bytes_per_ray
-    peak, peak_src = measured_peaks()
+    hbm_peak, hbm_src = measured_peaks()
     wave = path and args.variant in (0, 4) and ctx.last_traversal != abi.TRAVERSAL_LITERAL
     if wave and stage_ms:
         # streaming wavefront engine: the dominant kernel is wv_extend (closest hit of every ray segment);
@@ -420,71 +521,106 @@ def run_b200(args, wl, world, rank, local):
     else:
         mean_ms = float(np.mean(kernel_ms))
         stages = None
-        kernel = ("wave engine frame: wv_generate + wv_extend + wv_shade + wv_resolve on overlapped sub-frame streams"
+        kernel = ("wave engine frame: wv_extend + wv_shade + wv_resolve on overlapped sub-frame streams"
                   if wave else ("rt_path_trace" if path else "rt_trace_shade"))
         kernel_bytes_per_ray = bytes_per_ray
-    achieved = kernel_bytes_per_ray * seg_per_frame_rank / (mean_ms * 1e-3) / 1e9
+    algorithmic_gbs = kernel_bytes_per_ray * seg_per_frame_rank / (mean_ms * 1e-3) / 1e9
     # measured denominators of the traversal itself: random independent 32-byte sector gathers
     # (the node-fetch instruction) from an L1-resident, an L2-resident and an HBM-resident set
     gather_bw = {"l1_64KiB": ctx.probe_gather_bandwidth(64 << 10), "l2_32MiB": ctx.probe_gather_bandwidth(32 << 20),
                  "hbm_4GiB": ctx.probe_gather_bandwidth(4 << 30)}
-    # bytes the re-laid-out layout actually loads: two-child nodes (32 B with 16-bit boxes in the wave engine's
-    # rebuilt tree, else 64 B) and 48-B triangles
+    # bytes the re-laid-out layout actually loads per ray segment: two-child nodes (32 B with 16-bit boxes in the
+    # wave engine's rebuilt tree, else 64 B) and 48-B triangles
     node_bytes = 32 if (wave and ctx.last_traversal == abi.TRAVERSAL_REBUILT) else 64
     fetched_per_ray = node_bytes * (V / 2.0) + 48 * T
-    # DRAM bytes of the dominant kernel per step from the committed `ncu --set full` capture of this command
-    # (dram__bytes_read.sum + dram__bytes_write.sum, summed over the step's wv_extend launches like `achieved`)
-    ncu_traffic = {"c3": (3.356e9, "profiles/r8_ncu_wv_extend_c3.txt")}.get(args.workload) if (wave and stage_ms and world == 1) else None
-    trav_name = {abi.TRAVERSAL_LITERAL: "literal", abi.TRAVERSAL_ORDERED: "ordered (uploaded tree)",
-                 abi.TRAVERSAL_REBUILT: "rebuilt (internal LBVH, winners certified against the uploaded tree)"}
+    fetched_gbs = fetched_per_ray * seg_per_frame_rank / (mean_ms * 1e-3) / 1e9
+    # where the traversal's working set lives decides the roof: the re-laid-out scene of C2 / C3 / C4
+    # fits the 126 MB L2 (and mostly L1), C5's does not
+    scene_bytes = 32 * len(scene.triangles) + 48 * len(scene.triangles) + 48 * len(scene.bvh_nodes)
+    on_chip = scene_bytes < 100e6
+    ncu, ncu_src = ncu_summary_for(args.workload) if world == 1 else (None, "multi-GPU run")
+    krec = (ncu or {}).get("kernels", {}).get(kernel) if ncu else None
+    if on_chip:
+        # achieved = node + triangle sectors really fetched per second; peak = this run's measured rate of divergent
+        # 32-byte gathers from an L2-resident set (with the capture's L1 hit rate h: the harmonic mix of the L1 and L2 rates)
+        peak = gather_bw["l2_32MiB"]
+        peak_src = "measured in this run: random 32-B sector gathers (ld.global.nc.v8) over a 32 MiB L2-resident set"
+        if krec and krec.get("l1_hit_rate") is not None:
+            hit = krec["l1_hit_rate"]
+            peak = 1.0 / (hit / gather_bw["l1_64KiB"] + (1.0 - hit) / gather_bw["l2_32MiB"])
+            peak_src = ("measured in this run: random 32-B sector gathers, L1-resident (64 KiB) and L2-resident (32 MiB) sets "
+                        "mixed by the ncu L1 sector hit rate %.3f of this kernel (%s)" % (hit, ncu_src))
+        bound, achieved = "l2", fetched_gbs
+    else:
+        bound, achieved, peak = "hbm", fetched_gbs, gather_bw["hbm_4GiB"]
+        peak_src = ("measured in this run: random 32-B sector gathers over a 4 GiB HBM-resident set (the access pattern of "
+                    "the traversal); the copy peak %.0f GB/s (%s) is what a streaming kernel could reach" % (hbm_peak, hbm_src))
+    roof = {"bound": bound, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+            "traffic": krec.get("dram_bytes_per_step") if krec else None,
+            "traffic_source": ncu_src,
+            "kernel": kernel, "peak_source": peak_src,
+            "what": "achieved = node and triangle bytes the kernel fetches per second (%d-B two-child nodes, 48-B triangles; "
+                    "V/2 node visits and T triangle tests per ray segment counted by an instrumented launch of the same "
+                    "kernels) over its CUDA-event launch time" % node_bytes,
+            "algorithmic_gbs": algorithmic_gbs,
+            "algorithmic_note": "SURVEY 8d figure in reference-layout bytes (48 V + 56 T + 20 S per segment; megakernels add "
+                                "128 H + 52 L H + output stores): context only; it charges 96 B per node pair where the kernel "
+                                "loads one 32-B sector, and the scene is served from L1 / L2, so it may exceed the HBM copy peak",
+            "hbm_copy_peak_gbs": hbm_peak, "hbm_copy_peak_source": hbm_src,
+            "bytes_per_ray": kernel_bytes_per_ray, "step_bytes_per_ray": bytes_per_ray,
+            "fetched_bytes_per_ray": fetched_per_ray,
+            "box_tests_per_ray": V, "tri_tests_per_ray": T, "kernel_ms": mean_ms,
+            "kernel_share_of_step": mean_ms / (total_ms / args.steps) if world == 1 else None,
+            "stage_ms": stages,
+            "stage_ms_note": "second timed pass, one sub-frame, CUDA events between consecutive launches; the headline "
+                             "pass overlaps two sub-frames on two streams" if stages else None,
+            "gather_gbs_measured": gather_bw,
+            "frac_of_l1_gather": fetched_gbs / gather_bw["l1_64KiB"], "frac_of_l2_gather": fetched_gbs / gather_bw["l2_32MiB"]}
+    if krec:
+        # the second roof of a divergent traversal: instruction issue.  issue_active x lanes / 32 = useful lane-slots
+        roof["issue"] = {"issue_active_pct": krec.get("issue_active_pct"), "lanes_per_inst": krec.get("lanes_per_inst"),
+                         "useful_lane_slot_frac": (krec["issue_active_pct"] / 100.0 * krec["lanes_per_inst"] / 32.0)
+                         if krec.get("issue_active_pct") and krec.get("lanes_per_inst") else None,
+                         "warp_execution_efficiency_pct": (krec["lanes_per_inst"] / 32.0 * 100.0) if krec.get("lanes_per_inst") else None,
+                         "alu_pipe_pct": krec.get("alu_pipe_pct"), "fma_pipe_pct": krec.get("fma_pipe_pct"),
+                         "source": ncu_src}
+    cfg = workload_config(wl, scene)
     line = {
         "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": total_ms / args.steps, "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": wl["desc"], "width": w, "height": h, "triangles": int(len(scene.triangles)),
-                   "bvh_nodes": int(len(scene.bvh_nodes)), "spp": wl["spp"], "max_depth": wl["depth"],
-                   "ray_segments_per_frame": int(seg_per_frame),
-                   "semantics": "extension (SPEC.md; the reference stubs bounces/spp)" if path else "reference",
-                   "traversal": trav_name[ctx.last_traversal],
-                   "engine": ("streaming wavefront (generate / extend / shade per depth / resolve)" if wave else
-                              ("megakernel" if path else "fused trace+shade kernel")), "literal_fallback_rays": cnt["literal_fallbacks"],
-                   "upload_relayout_build_ms": ctx.last_build_ms,
-                   "l2": "flushed between timed steps (512 MiB memset)", "tiles_per_rank": my_tiles,
-                   "parallelism": ("64x64 tile split x%d (tile i -> rank i %% N), scene replicated, %s inside the timed step"
-                                   % (world, "composite pixels stored into rank 0's frame by the render kernels (P2P over NVLink, "
-                                             "CUDA IPC) + 4-byte NCCL all-reduce as barrier" if peer is not None else
-                                      "NCCL gather of the composite tiles to rank 0")) if world > 1 else "single GPU"},
-        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": ncu_traffic[0] if ncu_traffic else None,
-                     "traffic_source": ncu_traffic[1] if ncu_traffic else None,
-                     "kernel": kernel, "peak_source": peak_src,
-                     "bytes_per_ray": kernel_bytes_per_ray, "step_bytes_per_ray": bytes_per_ray,
-                     "box_tests_per_ray": V, "tri_tests_per_ray": T, "kernel_ms": mean_ms,
-                     "kernel_share_of_step": mean_ms / (total_ms / args.steps) if world == 1 else None,
-                     "stage_ms": stages,
-                     "stage_ms_note": "second timed pass, one sub-frame, CUDA events between consecutive launches; the headline "
-                                      "pass overlaps two sub-frames on two streams" if stages else None,
-                     "gather_gbs_measured": gather_bw,
-                     "fetched_bytes_per_ray": fetched_per_ray,
-                     "fetched_gbs": fetched_per_ray * seg_per_frame_rank / (mean_ms * 1e-3) / 1e9,
-                     "frac_of_l1_gather": fetched_per_ray * seg_per_frame_rank / (mean_ms * 1e-3) / 1e9 / gather_bw["l1_64KiB"],
-                     "note": "achieved = algorithmic reference-layout bytes per ray segment of this kernel (closest hit: "
-                             "48 V + 56 T + 20 S; megakernels add 128 H + 52 L H + output stores) x segments / its launch "
-                             "time; V/T counted by an instrumented launch of the same kernels; the scene fits the 126 MB "
-                             "L2, so achieved can exceed the HBM copy peak and DRAM traffic is far below the algorithmic "
-                             "bytes: the kernel is bound on chip.  fetched_gbs / frac_of_l1_gather compare the node and "
-                             "triangle sectors it really loads with the measured rate of divergent 32-B gathers from L1; "
-                             "with one-sector nodes ncu shows the issue slots (65-75 % active, 20 of 32 lanes per "
-                             "instruction) ahead of the L1 data stage (47-62 %), see DESIGN.md section 5"},
+        "config": cfg,
+        "run": {"ray_segments_per_frame": int(seg_per_frame), "traversal": trav_name(ctx.last_traversal),
+                "engine": ("streaming wavefront (extend / shade per depth, resolve)" if wave else
+                           ("megakernel" if path else "fused trace+shade kernel")),
+                "literal_fallback_rays": cnt["literal_fallbacks"], "upload_relayout_build_ms": ctx.last_build_ms,
+                "tiles_per_rank": my_tiles, "src_hash": source_hash(),
+                "parallelism": ("64x64 tile split x%d (tile i -> rank i %% N), scene replicated, %s inside the timed step"
+                                % (world, "composite pixels stored into rank 0's frame by the render kernels (P2P over NVLink, "
+                                          "CUDA IPC) + 4-byte NCCL all-reduce as barrier" if peer is not None else
+                                   "NCCL gather of the composite tiles to rank 0")) if world > 1 else "single GPU"},
+        "roofline": roof,
         "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": h2d_bytes,
                 "d2h_bytes_per_step": int(host_img.nbytes), "ms_per_step": e2e_total / args.steps},
         "gpu_launches": int(launches), "clocks": clk, "rank_frame_ms": rank_kernel_ms,
         "assembled_frame_bit_identical_to_single_gpu": assembled_ok,
     }
-    if world == 1 and not args.no_cpu_baseline:
-        line["cpu_baseline"] = {k: v for k, v in cpu_baseline_sample(scene, wl, args.cpu_seconds).items()
-                                if k in ("value", "unit", "cores", "kind", "sample")}
+    if primary:
+        line["primary"] = primary
+    if cpu_rec:
+        line["cpu_baseline"] = {k: v for k, v in cpu_rec.items() if k in ("value", "unit", "cores", "threads_used", "kind", "sample")}
+        line.update(parity)
     print(json.dumps(line), flush=True)
+    ctx.close()
+    if parity and not parity["bit_exact"]:
+        print("PARITY FAILURE: GPU frame differs from the oracle on rows %s" % parity["rows"], file=sys.stderr)
+        sys.exit(3)
+
+
+def trav_name(t):
+    from gpu_raytracer_b200 import abi
+    return {abi.TRAVERSAL_LITERAL: "literal", abi.TRAVERSAL_ORDERED: "ordered (uploaded tree)",
+            abi.TRAVERSAL_REBUILT: "rebuilt (internal LBVH, winners certified against the uploaded tree)"}.get(t, str(t))
 
 
 def main():

@@ -249,3 +249,39 @@ def test_path_depth_increases_radiance_and_segments_bounded():
     assert d8["accum"][..., :3].sum() > d0["accum"][..., :3].sum()
     assert d0["counters"]["rays"] == 32 * 32 * 4
     assert 32 * 32 * 4 < d8["counters"]["rays"] <= 32 * 32 * 4 * 9
+
+
+def test_material_id_below_bound_capacity_is_a_zero_material():
+    # materials.len() is the bound buffer's length (capacity 64, zero-filled past the 4 uploaded materials;
+    # src/buffers.rs:100-106, src/renderer.rs:698, lib.rs:307): id 10 shades as a zero material -> black hit
+    s = g.default_scene()
+    s.spheres["material_id"][0] = 10
+    r = ob.render(s, 3, 3, threads=1)
+    assert r["hits"][1, 1]["kind"] == 1 and r["hits"][1, 1]["material_id"] == 10
+    assert not r["radiance"][1, 1].any()
+    s.spheres["material_id"][0] = 64
+    assert np.array_equal(ob.render(s, 3, 3, threads=1)["radiance"][1, 1], np.array([1, 0, 1], f32))
+    assert ob.materials_capacity(64) == 64 and ob.materials_capacity(65) == 130
+
+
+def test_bound_triangle_buffers_alias_and_tail():
+    # one triangle, buffers of 4 entries: index 0 valid; index 1..3 = zero-filled tail (degenerate, no hit);
+    # index 4 and 8 (buffers 1, 2: not created, bound to buffer 0 again, src/renderer.rs:680-693) alias triangle 0;
+    # index 12 (buffer 3) is invalid
+    for idx, want in ((0, True), (2, False), (4, True), (8, True), (12, False)):
+        s = one_triangle_scene([0, 0, 0], [1, 0, 0], [0, 1, 0], [0.25, 0.25, 3], [0, 0, -1])
+        s.triangle_indices = np.array([idx], np.uint32)
+        b = ob.BoundScene(s, triangles_per_buffer=4)
+        rec = ob.render(b, 1, 1, threads=1)["hits"][0, 0]
+        assert (rec["kind"] == 2) == want, idx
+        if want:
+            assert rec["prim"] == idx and t_of(rec) == 3.0
+
+
+def test_oracle_threads_share_short_bands():
+    # 2 rows must still give every thread work (64-pixel spans): same pixels whatever the thread count
+    s = g.default_scene()
+    a = ob.render_path(s, 320, 180, spp=2, max_depth=3, rows=(90, 92), threads=1)
+    b = ob.render_path(s, 320, 180, spp=2, max_depth=3, rows=(90, 92), threads=7)
+    assert np.array_equal(a["accum"].view(np.uint32), b["accum"].view(np.uint32))
+    assert a["counters"] == b["counters"]
