@@ -56,7 +56,7 @@ WORKLOADS = {
 # figures are the same measurement): a centred band of rows of the workload's own frame, full spp and depth.
 # Sized for ~2-6 s on 16 host threads; the oracle hands 64-pixel spans to its pool, so even 2 rows keep every
 # thread busy.  Primary workloads: whole 128-row tile bands, three channel passes (the reference's own loop).
-CPU_SAMPLE_ROWS = {"c3": 8, "c3-smallleaf": 64, "c4": 48, "c5": 1, "c3-primary": 128, "c3-primary-smallleaf": 1080,
+CPU_SAMPLE_ROWS = {"c3": 4, "c3-smallleaf": 64, "c4": 48, "c5": 1, "c3-primary": 128, "c3-primary-smallleaf": 1080,
                    "c2": 1080}
 
 
