@@ -1005,6 +1005,61 @@ int launch_wave(RtContext* c, KParams k, uint32_t traversal) {
     return RT_OK;
 }
 
+// Primary frames (RT_MODE_LEGACY / RT_MODE_WAVEFRONT0) of a fused rt_render_frame through the wave engine's
+// traversal: one wv_extend<GEN> launch + one wv_shade_primary launch (rt_wave.cuh).  Returns -100 when no
+// re-laid-out policy is available (the caller then launches rt_trace_shade with the literal policy).
+int launch_primary_wave(RtContext* c, KParams k, uint32_t traversal, uint32_t my_tiles) {
+    if (my_tiles == 0) return RT_OK;
+    int policy = pick_policy(c, k, traversal);
+    if (policy < 1) return -100;
+    if (getenv("RTB200_PRIMARY_FUSED")) return -100; // tuning/tests: the one-kernel form (rt_trace_shade)
+    k.n_work = my_tiles * 4096u;
+    k.spp = 1; k.first_sample = 0; k.base_seed = 0; k.path_max_depth = 0;
+    k.legacy_camera = k.mode == RT_MODE_WAVEFRONT0 ? 0u : 1u;
+    const size_t P = k.n_work;
+    if (c->wv_hit[0].reserve(P) < 0 || c->wv_ctrl.reserve(4) < 0)
+        return fail(c, RT_ERR_CUDA, "wave engine cudaMalloc failed for %zu primary rays", P);
+    const bool count = k.counters != nullptr;
+    const uint32_t tree_levels = policy == 2 ? c->lbvh_depth : c->wide.max_depth;
+    bool deep = tree_levels + 2u > WV_STK;
+    if (const char* e = getenv("RTB200_WAVE_DEEP")) deep = deep || atoi(e) != 0;
+    int per_sm = 0, sms = 0;
+    const void* fn = (const void*)wv_extend_kernel(policy, false, true, deep);
+    CK(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, 256, 0));
+    CK(c, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, c->device));
+    WvBuffers w;
+    memset(&w, 0, sizeof w);
+    w.hit[0] = c->wv_hit[0].ptr; w.hit[1] = c->wv_hit[0].ptr; // depth 0 only: nothing is appended
+    w.ctrl = c->wv_ctrl.ptr;
+    w.s0 = 0; w.spp_wave = 1; w.first_wave = 1; w.last_wave = 1;
+    for (uint32_t t = 0; t < my_tiles; t++) {
+        const uint32_t tile = k.tile_phase + t * k.tile_stride, tx = tile % k.tiles_x, ty = tile / k.tiles_x;
+        const uint32_t x0 = tx * RT_SPLIT_TILE, y0 = ty * RT_SPLIT_TILE;
+        const uint32_t tw = x0 >= k.width ? 0u : (k.width - x0 < RT_SPLIT_TILE ? k.width - x0 : RT_SPLIT_TILE);
+        const uint32_t th = y0 >= k.height ? 0u : (k.height - y0 < RT_SPLIT_TILE ? k.height - y0 : RT_SPLIT_TILE);
+        w.valid_pixels += tw * th;
+    }
+    uint32_t full_blocks = (uint32_t)((P + 255) / 256);
+    uint32_t ext_blocks = (uint32_t)(per_sm > 0 ? per_sm : 1) * (uint32_t)sms;
+    if (ext_blocks > full_blocks) ext_blocks = full_blocks;
+    uint32_t shade_blocks = (uint32_t)sms * 8u;
+    if (shade_blocks > full_blocks) shade_blocks = full_blocks;
+    CK(c, cudaEventRecord(c->ev0, c->stream));
+    CK(c, cudaMemsetAsync(c->wv_ctrl.ptr, 0, sizeof(WvCtrl), c->stream));
+    wv_extend_kernel(policy, count, true, deep)<<<ext_blocks, 256, 0, c->stream>>>(k, w, 0);
+    if (policy == 2) { if (count) wv_shade_primary<2, true><<<shade_blocks, 256, 0, c->stream>>>(k, w); else wv_shade_primary<2, false><<<shade_blocks, 256, 0, c->stream>>>(k, w); }
+    else { if (count) wv_shade_primary<1, true><<<shade_blocks, 256, 0, c->stream>>>(k, w); else wv_shade_primary<1, false><<<shade_blocks, 256, 0, c->stream>>>(k, w); }
+    CK(c, cudaGetLastError());
+    c->launches += 2;
+    if (count) { wv_publish<<<1, 1, 0, c->stream>>>(c->wv_ctrl.ptr, 1, c->dcounters.ptr, 1); c->launches++; }
+    CK(c, cudaEventRecord(c->ev1, c->stream));
+    c->timed = true;
+    c->last_traversal = policy == 2 ? RT_TRAVERSAL_REBUILT : RT_TRAVERSAL_ORDERED;
+    c->count_next = false;
+    c->last_was_wavefront = false;
+    return RT_OK;
+}
+
 // Microbenchmark behind the traversal roofline: every lane loads one random, independent
 // 32-byte sector per iteration (ld.global.nc.v8.f32, the node-fetch instruction) from a
 // buffer of `sectors` sectors.  A small footprint measures the SM's L1 rate for divergent
@@ -1120,6 +1175,10 @@ int rt_render_frame(RtContext* c, const RtCamera* cam, const RtFrameParams* fp) 
             if (wr != -100) return wr;
         }
         return launch_path(c, k, fp->traversal);
+    }
+    {   // reference-semantics primary frame: the wave engine's traversal where a re-laid-out policy exists
+        int wr = launch_primary_wave(c, k, fp->traversal, my_tiles);
+        if (wr != -100) return wr;
     }
     return launch(c, k, my_tiles * 16u, fp->traversal);
 }

@@ -81,6 +81,7 @@ struct KParams {
     unsigned long long* counters;
     // RT_MODE_PATH (EXTENSION, SPEC.md)
     uint32_t spp, first_sample, path_max_depth, base_seed;
+    uint32_t legacy_camera;          // wave engine primary frames: 1 = Ray::from_screen_coordinates (legacy), 0 = wavefront camera ray
     uint32_t n_work;                 // pixels in this launch's work list (4096 per assigned split tile)
     unsigned int* work_counter;      // persistent-thread work fetch
     unsigned long long* seg_counter; // ray segments traced (the Mrays/s numerator)
@@ -627,31 +628,11 @@ __device__ __forceinline__ bool pixel_of_thread(const KParams& p, uint32_t* px, 
     return lx < w && ly < h && *px < p.width && *py < p.height;
 }
 
-template <int POLICY, bool COUNT>
-__global__ void __launch_bounds__(256) rt_trace_shade(const __grid_constant__ KParams p) {
-    uint32_t px, py;
-    if (!pixel_of_thread(p, &px, &py)) return;
-    uint32_t n_seg = 0;
-    const bool wavefront = p.mode == RT_MODE_WAVEFRONT0;
-    const bool fused = p.use_tiles != 0u;
-    const uint32_t channel = fused ? 0xFFu : p.channel;
-    V3 color = mk(0.0f, 0.0f, 0.0f);
-    Hit h;
-    h.t = FLT_MAX; h.kind = 0u; h.prim = 0xFFFFFFFFu; h.material_id = 0xFFFFFFFFu; h.n_box = 0; h.n_tri = 0; h.n_fallback = 0;
-    if (!wavefront) {
-        Ray ray = camera_ray(p, px, py, 0.5f, 0.5f, false);
-        n_seg = 1;
-        h = find_closest<POLICY>(p, ray);
-        if (h.kind != 0u) color = shade_hit(p, h, channel); // miss: (0,0,0), lib.rs:77
-    } else if (p.cur_depth <= p.max_depth) {
-        // run_wavefront_raytracing, lib.rs:92-149: throughput (1,1,1); sky on miss
-        Ray ray = camera_ray(p, px, py, 0.5f, 0.5f, true);
-        n_seg = 1;
-        h = find_closest<POLICY>(p, ray);
-        V3 tp = mk(1.0f, 1.0f, 1.0f);
-        V3 c = (h.kind != 0u) ? shade_hit(p, h, channel) * tp : mk(0.1f, 0.2f, 0.3f) * tp;
-        color = color + c;
-    }
+// Output stage of one pixel: filter_color_by_channel + Rgba8Unorm store of one reference dispatch
+// (lib.rs:82-88, 342-349), or the fused frame's three channel images + main_fs composite (lib.rs:368-391) +
+// accumulation; hit record.  Shared by rt_trace_shade and the wave engine's primary-frame shading kernel.
+__device__ __forceinline__ void store_pixel(const KParams& p, uint32_t px, uint32_t py, V3 color, const Hit& h, bool fused,
+                                            uint32_t channel) {
     const size_t pix = (size_t)py * p.width + px;
     if (!fused) {
         // filter_color_by_channel (lib.rs:342-349) + Rgba8Unorm store
@@ -694,6 +675,34 @@ __global__ void __launch_bounds__(256) rt_trace_shade(const __grid_constant__ KP
         uint4 rec = make_uint4(h.kind, h.prim, __float_as_uint(h.t), h.material_id);
         reinterpret_cast<uint4*>(p.hits)[pix] = rec;
     }
+}
+
+template <int POLICY, bool COUNT>
+__global__ void __launch_bounds__(256) rt_trace_shade(const __grid_constant__ KParams p) {
+    uint32_t px, py;
+    if (!pixel_of_thread(p, &px, &py)) return;
+    uint32_t n_seg = 0;
+    const bool wavefront = p.mode == RT_MODE_WAVEFRONT0;
+    const bool fused = p.use_tiles != 0u;
+    const uint32_t channel = fused ? 0xFFu : p.channel;
+    V3 color = mk(0.0f, 0.0f, 0.0f);
+    Hit h;
+    h.t = FLT_MAX; h.kind = 0u; h.prim = 0xFFFFFFFFu; h.material_id = 0xFFFFFFFFu; h.n_box = 0; h.n_tri = 0; h.n_fallback = 0;
+    if (!wavefront) {
+        Ray ray = camera_ray(p, px, py, 0.5f, 0.5f, false);
+        n_seg = 1;
+        h = find_closest<POLICY>(p, ray);
+        if (h.kind != 0u) color = shade_hit(p, h, channel); // miss: (0,0,0), lib.rs:77
+    } else if (p.cur_depth <= p.max_depth) {
+        // run_wavefront_raytracing, lib.rs:92-149: throughput (1,1,1); sky on miss
+        Ray ray = camera_ray(p, px, py, 0.5f, 0.5f, true);
+        n_seg = 1;
+        h = find_closest<POLICY>(p, ray);
+        V3 tp = mk(1.0f, 1.0f, 1.0f);
+        V3 c = (h.kind != 0u) ? shade_hit(p, h, channel) * tp : mk(0.1f, 0.2f, 0.3f) * tp;
+        color = color + c;
+    }
+    store_pixel(p, px, py, color, h, fused, channel);
     if (p.outputs & RT_OUT_PEER) __threadfence_system(); // the composite store went to another GPU's frame
     if (COUNT) {
         atomicAdd(p.counters + 0, (unsigned long long)h.n_box);

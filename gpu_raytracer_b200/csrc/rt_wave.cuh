@@ -126,7 +126,7 @@ __device__ __forceinline__ bool wv_primary(const KParams& p, const WvBuffers& w,
     SimpleRng rng; rng.seed = p.base_seed + s + px + py * p.width;
     float jx = 0.5f, jy = 0.5f;
     if (s != 0u) { jx = rng.next_f32(); jy = rng.next_f32(); }
-    *ray = camera_ray(p, px, py, jx, jy, true);
+    *ray = camera_ray(p, px, py, jx, jy, p.legacy_camera == 0u);
     *rng_seed = rng.seed;
     return true;
 }
@@ -632,4 +632,82 @@ __global__ void __launch_bounds__(256) wv_resolve(const __grid_constant__ KParam
                                            (unsigned char)unorm8(a.z / a.w), 255);
     }
     if (p.outputs & RT_OUT_PEER) __threadfence_system(); // composite stores went to another GPU's frame
+}
+
+// ---- primary frames with the reference's semantics (RT_MODE_LEGACY / RT_MODE_WAVEFRONT0) through the wave
+// engine's traversal: wv_extend<GEN> finds the closest triangle of every primary ray (shared-memory stack
+// column, one-sector nodes, speculative leaf postponement), then this kernel, convergent with one thread per
+// primary ray in queue order, certifies the winner (REBUILT), shades it exactly like main_cs (lib.rs:59-89 /
+// 92-149 at depth 0) and runs the output stage.  Results are bit-identical to rt_trace_shade's.
+template <int POLICY, bool COUNT>
+__global__ void __launch_bounds__(256) wv_shade_primary(const __grid_constant__ KParams p, WvBuffers w) {
+    const uint32_t n = p.n_work;
+    const float4* __restrict__ tris = POLICY == 2 ? p.btris : p.wtris;
+    if (blockIdx.x == 0 && threadIdx.x == 0) { w.ctrl->head = 0; w.ctrl->segments += (unsigned long long)w.valid_pixels; }
+    const bool wavefront = p.mode == RT_MODE_WAVEFRONT0;
+    unsigned long long c_shaded = 0, c_fb = 0, c_box = 0, c_tri = 0;
+    for (uint32_t q = blockIdx.x * blockDim.x + threadIdx.x; q < n; q += gridDim.x * blockDim.x) {
+        uint32_t idx, sl, seed, px, py;
+        Ray ray;
+        if (!wv_primary(p, w, q, &idx, &sl, &ray, &seed)) continue;
+        work_to_pixel(p, idx, &px, &py);
+        const uint2 hr = __ldcs(w.hit[0] + q);
+        Hit h;
+        h.t = FLT_MAX; h.kind = 0u; h.prim = 0xFFFFFFFFu; h.material_id = 0xFFFFFFFFu;
+        h.point = mk(0, 0, 0); h.normal = mk(0, 0, 0); h.n_box = 0; h.n_tri = 0; h.n_fallback = 0;
+        V3 color = mk(0.0f, 0.0f, 0.0f);
+        if (!wavefront || p.cur_depth <= p.max_depth) {
+            const uint32_t kind = hr.y >> 30;
+            bool lit = hr.y != WV_ID_MISS && kind == WV_KIND_LITERAL;
+            TriBest b;
+            b.hit = false; b.n_box = 0; b.n_tri = 0; b.n_fallback = 0;
+            if (hr.y != WV_ID_MISS && kind == WV_KIND_TRI) {
+                const float4* tpn = tris + (uint64_t)hr.y * 3;
+                float4 a = __ldg(tpn), c = __ldg(tpn + 1), d = __ldg(tpn + 2);
+                b.hit = true; b.t = __uint_as_float(hr.x);
+                b.v0 = mk(a.x, a.y, a.z); b.e1 = mk(a.w, c.x, c.y); b.e2 = mk(c.z, c.w, d.x);
+                b.mat = __float_as_uint(d.y); b.prim = __float_as_uint(d.z);
+                if (POLICY == 2) { // certification against the uploaded tree (see closest_triangle_rebuilt)
+                    uint32_t leaf = __ldg(p.leaf_of_pos + __float_as_uint(d.w));
+                    const float4 blo = __ldg(p.cert_box + (uint64_t)leaf * 2), bhi = __ldg(p.cert_box + (uint64_t)leaf * 2 + 1);
+                    V3 inv = mk(1.0f / ray.d.x, 1.0f / ray.d.y, 1.0f / ray.d.z);
+                    float entry;
+                    lit = !slab(ray.o, inv, mk(blo.x, blo.y, blo.z), mk(bhi.x, bhi.y, bhi.z), &entry);
+                }
+            }
+            float sphere_seed = FLT_MAX - 2.0f;
+            uint32_t sphere_idx = WV_NO_SPHERE;
+            if (hr.y != WV_ID_MISS && kind == WV_KIND_SPHERE) { sphere_seed = __uint_as_float(hr.x); sphere_idx = hr.y & WV_NO_SPHERE; }
+            if (lit) { // rare: the reference's own traversal for this ray
+                wv_sphere_seed(p, ray, &sphere_seed, &sphere_idx);
+                closest_triangle_literal(p, ray, sphere_seed, b);
+                if (COUNT) { c_fb++; c_box += b.n_box; c_tri += b.n_tri; }
+            }
+            if (b.hit) {
+                h.t = b.t; h.kind = 2u; h.prim = b.prim; h.material_id = b.mat;
+                h.point = ray.o + ray.d * b.t;
+                h.normal = normalize3(cross3(b.e1, b.e2));
+            } else if (sphere_idx != WV_NO_SPHERE) {
+                uint64_t o = (uint64_t)p.off.spheres_offset + (uint64_t)sphere_idx * 5;
+                V3 c = mk(meta_f(p, o), meta_f(p, o + 1), meta_f(p, o + 2));
+                h.t = sphere_seed; h.kind = 1u; h.prim = sphere_idx; h.material_id = meta_at(p, o + 4);
+                h.point = ray.o + ray.d * sphere_seed;
+                h.normal = normalize3(h.point - c);
+            }
+            if (COUNT && h.kind != 0u) c_shaded++;
+            if (!wavefront) {
+                if (h.kind != 0u) color = shade_hit(p, h, 0xFFu); // miss: (0,0,0), lib.rs:77
+            } else { // run_wavefront_raytracing, lib.rs:92-149: throughput (1,1,1); sky on miss
+                V3 tp = mk(1.0f, 1.0f, 1.0f);
+                V3 c = (h.kind != 0u) ? shade_hit(p, h, 0xFFu) * tp : mk(0.1f, 0.2f, 0.3f) * tp;
+                color = color + c;
+            }
+        }
+        store_pixel(p, px, py, color, h, true, 0xFFu);
+    }
+    if (p.outputs & RT_OUT_PEER) __threadfence_system(); // the composite store went to another GPU's frame
+    if (COUNT) {
+        if (c_shaded) atomicAdd(&w.ctrl->c[2], c_shaded);
+        if (c_fb) { atomicAdd(&w.ctrl->c[3], c_fb); atomicAdd(&w.ctrl->c[0], c_box); atomicAdd(&w.ctrl->c[1], c_tri); }
+    }
 }
