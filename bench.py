@@ -96,6 +96,11 @@ def parse_args():
     ap.add_argument("--cpu-seconds", type=float, default=10.0,
                     help="GPU arm: repeat the fixed cpu_baseline sample (CPU_SAMPLE_ROWS) until this much CPU time has passed")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--dump-rows", default=None, help="reference arm: also write the rendered rows of the last step to this .npz "
+                                                      "(the GPU arm's cpu_baseline leg runs the reference arm as a child process "
+                                                      "and compares its pixels with the GPU frame)")
+    ap.add_argument("--ref-seconds", type=float, default=0.0,
+                    help="reference arm: keep adding timed steps past --steps until this much time has been measured")
     ap.add_argument("--variant", type=int, default=0, help="path mode engine: 0 auto = streaming wavefront (default), 1 megakernel, "
                                                            "4 streaming wavefront")
     ap.add_argument("--traversal", default="auto", choices=["auto", "literal", "ordered", "rebuilt"])
@@ -257,20 +262,23 @@ def run_reference(args, wl, world, rank):
     scene = build_scene(wl)
     bound = ob.BoundScene(scene)
     rows = cpu_sample_rows(args, wl)
-    vals, last = [], None
-    for i in range(args.warmup + args.steps):
-        last, _ = cpu_baseline_sample(scene, wl, rows, bound)
+    vals, last, px, i = [], None, None, 0
+    while i < args.warmup + args.steps or sum(x["seconds"] for x in vals) < args.ref_seconds:
+        last, px = cpu_baseline_sample(scene, wl, rows, bound)
         if i >= args.warmup:
             vals.append(last)
+        i += 1
+    if args.dump_rows:
+        np.savez(args.dump_rows, rows=np.array(rows), **px)
     secs = float(np.sum([x["seconds"] for x in vals]))
     v = float(np.sum([x["value"] * x["seconds"] for x in vals]) / secs)  # total rays / total time
     line = {"impl": "reference", "metric": "Mrays/s", "value": v, "unit": "Mrays/s", "n_gpus": args.gpus,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": secs / len(vals) * 1e3, "higher_is_better": True,
+            "steps": len(vals), "warmup": args.warmup, "ms_per_step": secs / len(vals) * 1e3, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": workload_config(wl, scene),
             "traversal": "literal (the reference's own unordered, un-pruned DFS over the uploaded tree)",
             "cpu_baseline": {"value": v, "unit": "Mrays/s", "cores": last["cores"], "threads_used": last["threads_used"],
-                             "kind": "port", "sample": last["sample"]},
+                             "kind": "port", "sample": last["sample"] + " (%d timed passes)" % len(vals)},
             "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
@@ -487,9 +495,19 @@ def run_b200(args, wl, world, rank, local):
     # literal oracle; its pixels must equal the GPU frame's bit for bit
     cpu_rec, parity = None, None
     if world == 1 and not args.no_cpu_baseline:
-        rows = cpu_sample_rows(args, wl)
-        cpu_rec, px = cpu_baseline_sample(scene, wl, rows, min_seconds=args.cpu_seconds)
-        y0, y1 = rows
+        # the leg IS the reference arm, run as a child process (same code, same sample, a process of its own like
+        # the driver's reference run), so the two figures are one measurement
+        import tempfile
+        tmp = os.path.join(tempfile.mkdtemp(), "rows.npz")
+        env = {k: v for k, v in os.environ.items() if k not in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "MASTER_ADDR", "MASTER_PORT")}
+        child = subprocess.run([sys.executable, os.path.abspath(__file__), "--impl", "reference", "--workload", args.workload,
+                                "--steps", "1", "--warmup", "1", "--ref-seconds", str(args.cpu_seconds), "--dump-rows", tmp],
+                               capture_output=True, text=True, env=env)
+        if child.returncode != 0:
+            raise RuntimeError("cpu_baseline child failed: " + child.stderr[-2000:])
+        cpu_rec = json.loads(child.stdout.strip().splitlines()[-1])["cpu_baseline"]
+        px = np.load(tmp)
+        y0, y1 = (int(x) for x in px["rows"])
         if path:
             acc = ctx.read_accum()[y0:y1]
             ok = bool(np.array_equal(acc.view(np.uint32), px["accum"].view(np.uint32)) and
@@ -608,7 +626,7 @@ def run_b200(args, wl, world, rank, local):
     if primary:
         line["primary"] = primary
     if cpu_rec:
-        line["cpu_baseline"] = {k: v for k, v in cpu_rec.items() if k in ("value", "unit", "cores", "threads_used", "kind", "sample")}
+        line["cpu_baseline"] = cpu_rec
         line.update(parity)
     print(json.dumps(line), flush=True)
     ctx.close()
