@@ -47,7 +47,8 @@ struct DevBuf {
 struct WideBvh { // host-side result of validation + node re-layout
     bool ordered_ok = false;
     std::string why_not;
-    std::vector<float4> nodes;      // 4 per internal node
+    std::vector<uint32_t> index;    // uploaded node -> compact internal-node index (0xFFFFFFFF: leaf / unreachable)
+    uint32_t n_internal = 0;
     std::vector<uint2> leaves;      // (start, effective count) of every reachable non-empty leaf
     std::vector<uint32_t> leaf_nodes; // uploaded node index of each entry of `leaves`
     bool nested_ok = false;         // every child box inside its parent's box, no NaN (REBUILT policy needs it)
@@ -69,7 +70,8 @@ struct RtContext {
     int last_traversal = 0;
 
     // BufferManager state (src/buffers.rs:13-45)
-    DevBuf<uint32_t> meta;
+    DevBuf<uint32_t> meta, meta_back; // live scene / staging buffer of the next upload (swapped on success)
+    DevBuf<uint32_t> wide_index;      // uploaded node -> compact internal index (relayout_wide_nodes)
     size_t meta_len = 0; // u32
     size_t scene_metadata_capacity_bytes = 0;
     RtSceneMetadataOffsets offsets{};
@@ -112,6 +114,8 @@ struct RtContext {
     bool rebuilt_ok = false;
     uint32_t broot_ref = RT_CHILD_ABSENT;
     float broot_min[3] = {0, 0, 0}, broot_max[3] = {0, 0, 0};
+    float4 rb_box[2] = {};     // read-back of the internal tree's root box / depth (build_rebuilt -> finish_rebuilt)
+    unsigned int rb_depth = 0;
     float rebuilt_far = 0.0f; // rays whose origin has a coordinate beyond this take the literal policy (rt_lbvh.cuh)
     float last_build_ms = -1.0f;
     bool last_was_wavefront = false;
@@ -172,7 +176,8 @@ void build_wide(const RtBvhNode* nodes, uint32_t n_nodes, uint32_t n_indices, Wi
     };
     auto is_leaf = [&](const RtBvhNode& nd) { return nd.left_child == RT_INVALID_INDEX; }; // bvh.rs:60
     auto valid_child = [&](uint32_t c) { return c != RT_INVALID_INDEX && c < n_nodes; };   // bvh.rs:45
-    std::vector<uint32_t> wide_index(n_nodes, 0xFFFFFFFFu);
+    std::vector<uint32_t>& wide_index = w.index;
+    wide_index.assign(n_nodes, 0xFFFFFFFFu);
     std::vector<uint8_t> seen(n_nodes, 0);
     struct Item { uint32_t node, depth; };
     std::vector<Item> stack;
@@ -214,29 +219,7 @@ void build_wide(const RtBvhNode* nodes, uint32_t n_nodes, uint32_t n_indices, Wi
             if (valid_child(nd.left_child)) { stack.push_back({nd.left_child, it.depth + 1}); nested = nested && inside(nodes[nd.left_child].bounds, nd.bounds); }
         }
     }
-    auto ref_of = [&](uint32_t c) -> uint32_t {
-        if (!valid_child(c)) return RT_CHILD_ABSENT;
-        const RtBvhNode& nd = nodes[c];
-        if (is_leaf(nd)) return eff_count(nd) ? (RT_LEAF_FLAG | nd.triangle_start) : RT_CHILD_ABSENT;
-        return wide_index[c];
-    };
-    auto as_f = [](uint32_t u) { float f; memcpy(&f, &u, 4); return f; };
-    w.nodes.assign((size_t)n_internal * 4, make_float4(0, 0, 0, 0));
-    const float inf = INFINITY;
-    for (uint32_t i = 0; i < n_nodes; i++) {
-        if (wide_index[i] == 0xFFFFFFFFu) continue;
-        const RtBvhNode& nd = nodes[i];
-        float lmin[3] = {inf, inf, inf}, lmax[3] = {-inf, -inf, -inf}, rmin[3] = {inf, inf, inf},
-              rmax[3] = {-inf, -inf, -inf};
-        uint32_t lref = ref_of(nd.left_child), rref = ref_of(nd.right_child);
-        if (valid_child(nd.left_child)) { memcpy(lmin, nodes[nd.left_child].bounds.min, 12); memcpy(lmax, nodes[nd.left_child].bounds.max, 12); }
-        if (valid_child(nd.right_child)) { memcpy(rmin, nodes[nd.right_child].bounds.min, 12); memcpy(rmax, nodes[nd.right_child].bounds.max, 12); }
-        float4* q = &w.nodes[(size_t)wide_index[i] * 4];
-        q[0] = make_float4(lmin[0], lmin[1], lmin[2], lmax[0]);
-        q[1] = make_float4(lmax[1], lmax[2], rmin[0], rmin[1]);
-        q[2] = make_float4(rmin[2], rmax[0], rmax[1], rmax[2]);
-        q[3] = make_float4(as_f(lref), as_f(rref), 0.0f, 0.0f);
-    }
+    w.n_internal = n_internal;
     const RtBvhNode& root = nodes[0];
     memcpy(w.root_min, root.bounds.min, 12);
     memcpy(w.root_max, root.bounds.max, 12);
@@ -247,6 +230,42 @@ void build_wide(const RtBvhNode* nodes, uint32_t n_nodes, uint32_t n_indices, Wi
 }
 
 // ---- device re-layout kernels -------------------------------------------------
+// One thread per uploaded node: internal nodes (compact index from the host's validation walk) become one
+// 64-byte two-child node each: (L box, R box, child refs), boxes copied bit for bit from the uploaded children.
+__global__ void relayout_wide_nodes(const uint32_t* __restrict__ meta, RtSceneMetadataOffsets off,
+                                    const uint32_t* __restrict__ wide_index, float4* __restrict__ wnodes) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t n_nodes = off.bvh_nodes_count, n_indices = off.triangle_indices_count;
+    if (i >= n_nodes) return;
+    const uint32_t wi = wide_index[i];
+    if (wi == 0xFFFFFFFFu) return;
+    const uint32_t* nb = meta + off.bvh_nodes_offset;
+    const float inf = __int_as_float(0x7f800000);
+    float4 q[4];
+    float bx[2][6];
+    uint32_t ref[2];
+    for (int k = 0; k < 2; k++) {
+        const uint32_t c = nb[(uint64_t)i * 12 + 8 + k];
+        for (int a = 0; a < 3; a++) { bx[k][a] = inf; bx[k][3 + a] = -inf; }
+        ref[k] = RT_CHILD_ABSENT;
+        if (c != RT_INVALID_INDEX && c < n_nodes) { // bvh.rs:45
+            const uint32_t* cn = nb + (uint64_t)c * 12;
+            for (int a = 0; a < 3; a++) { bx[k][a] = __uint_as_float(cn[a]); bx[k][3 + a] = __uint_as_float(cn[4 + a]); }
+            if (cn[8] == RT_INVALID_INDEX) { // leaf (bvh.rs:60): effective count per bvh.rs:109-111
+                const uint32_t start = cn[10], count = cn[11];
+                const uint32_t eff = start >= n_indices ? 0u : (count < n_indices - start ? count : n_indices - start);
+                ref[k] = eff ? (RT_LEAF_FLAG | start) : RT_CHILD_ABSENT;
+            } else ref[k] = wide_index[c];
+        }
+    }
+    q[0] = make_float4(bx[0][0], bx[0][1], bx[0][2], bx[0][3]);
+    q[1] = make_float4(bx[0][4], bx[0][5], bx[1][0], bx[1][1]);
+    q[2] = make_float4(bx[1][2], bx[1][3], bx[1][4], bx[1][5]);
+    q[3] = make_float4(__uint_as_float(ref[0]), __uint_as_float(ref[1]), 0.0f, 0.0f);
+    for (int k = 0; k < 4; k++) wnodes[(uint64_t)wi * 4 + k] = q[k];
+}
+
+
 // One thread per triangle_indices position: gather the indexed triangle into
 // (v0, e1, e2, material, index).  e1 = v1 - v0 and e2 = v2 - v0 are the same two
 // IEEE subtractions intersection.rs:102-103 performs per test, hoisted to upload.
@@ -439,14 +458,6 @@ int rt_update_scene_metadata(RtContext* c, const RtSphere* spheres, uint32_t ns,
     bool any_changed = ns != c->last_spheres || nl != c->last_lights || nn != c->last_nodes || ni != c->last_indices ||
                        nv != c->last_vertices;
     const bool upload = c->meta_dirty || needs_resize || any_changed; // src/buffers.rs:212
-    // Everything that can refuse the upload runs BEFORE any device buffer or bookkeeping is touched, so a
-    // refused upload leaves the previously uploaded scene fully in place (buffers, offsets, re-layout).
-    WideBvh wide;
-    if (upload) {
-        if (rt_bvh_has_cycle(nodes, nn))
-            return fail(c, RT_ERR_INVALID_ARGUMENT, "BVH child links form a cycle: the reference traversal would not terminate");
-        build_wide(nodes, nn, ni, wide); // validation + node re-layout while the host arrays are borrowed
-    }
     size_t new_capacity = c->scene_metadata_capacity_bytes;
     if (needs_resize) { // src/buffers.rs:186-204: double, with the default floors
         size_t sc = (size_t)ns * 2 > 64 ? (size_t)ns * 2 : 64, lc = (size_t)nl * 2 > 32 ? (size_t)nl * 2 : 32,
@@ -455,45 +466,56 @@ int rt_update_scene_metadata(RtContext* c, const RtSphere* spheres, uint32_t ns,
         new_capacity = sc * sizeof(RtSphere) + lc * sizeof(RtLight) + bc * sizeof(RtBvhNode) + ic * 4 + vc * sizeof(RtVertex);
     }
     if (upload) {
-        // the context's stream may still be reading the buffers a growth is about to replace
-        if (needs_resize || (wide.ordered_ok && (wide.nodes.size() > c->wnodes.capacity || wide.leaves.size() > c->wleaves.capacity ||
-                                                 wide.leaf_nodes.size() > c->wleaf_nodes.capacity)))
-            CK(c, cudaStreamSynchronize(c->stream));
-        // DevBuf::reserve keeps the old buffer when the new allocation fails: nothing is lost on these paths
-        if (wide.ordered_ok && (c->wnodes.reserve(wide.nodes.size()) < 0 || c->wleaves.reserve(wide.leaves.size()) < 0 ||
-                                c->wleaf_nodes.reserve(wide.leaf_nodes.size()) < 0)) {
-            c->relayout_dirty = true; // the auxiliary buffers may be half-grown: rebuild them before the next ordered launch
-            return fail(c, RT_ERR_CUDA, "wide BVH cudaMalloc failed");
-        }
-        if (needs_resize && c->meta.reserve(new_capacity / 4) < 0)
+        // The new scene is staged into the BACK buffer while the host validates it; the live buffer, its offsets
+        // and its re-layout are only replaced (pointer swap) once nothing can refuse the upload any more, so a
+        // refused upload leaves the previously uploaded scene fully in place.  The DMA from the caller's (pinned)
+        // arrays runs concurrently with the validation walk below.
+        if (c->meta_back.reserve(new_capacity / 4) < 0)
             return fail(c, RT_ERR_CUDA, "scene metadata cudaMalloc(%zu) failed", new_capacity);
-        c->scene_metadata_capacity_bytes = new_capacity;
-        // from here on the previous scene is being overwritten: any failure below leaves no scene
-        c->have_meta = false;
-        c->relayout_dirty = true; c->relayout_ok = false; c->rebuilt_ok = false;
-        c->wide = std::move(wide);
-        char* d = reinterpret_cast<char*>(c->meta.ptr);
+        char* d = reinterpret_cast<char*>(c->meta_back.ptr);
         size_t o = 0;
-        if (ss) CK(c, cudaMemcpyAsync(d + o, spheres, ss, cudaMemcpyHostToDevice, c->stream)); o += ss;
-        if (ls) CK(c, cudaMemcpyAsync(d + o, lights, ls, cudaMemcpyHostToDevice, c->stream)); o += ls;
-        if (bs) CK(c, cudaMemcpyAsync(d + o, nodes, bs, cudaMemcpyHostToDevice, c->stream)); o += bs;
-        if (is) CK(c, cudaMemcpyAsync(d + o, tri_idx, is, cudaMemcpyHostToDevice, c->stream)); o += is;
-        if (vs) CK(c, cudaMemcpyAsync(d + o, verts, vs, cudaMemcpyHostToDevice, c->stream));
-        if (c->wide.ordered_ok) {
-            if (!c->wide.nodes.empty())
-                CK(c, cudaMemcpyAsync(c->wnodes.ptr, c->wide.nodes.data(), c->wide.nodes.size() * sizeof(float4),
-                                      cudaMemcpyHostToDevice, c->stream));
-            if (!c->wide.leaves.empty()) {
-                CK(c, cudaMemcpyAsync(c->wleaves.ptr, c->wide.leaves.data(), c->wide.leaves.size() * sizeof(uint2),
-                                      cudaMemcpyHostToDevice, c->stream));
-                CK(c, cudaMemcpyAsync(c->wleaf_nodes.ptr, c->wide.leaf_nodes.data(), c->wide.leaf_nodes.size() * 4,
-                                      cudaMemcpyHostToDevice, c->stream));
+        cudaError_t ce = cudaSuccess;
+        auto put = [&](const void* src, size_t bytes) {
+            if (bytes && ce == cudaSuccess) ce = cudaMemcpyAsync(d + o, src, bytes, cudaMemcpyHostToDevice, c->stream);
+            o += bytes;
+        };
+        put(spheres, ss); put(lights, ls); put(nodes, bs); put(tri_idx, is); put(verts, vs);
+        // validation + compact numbering of the internal nodes (host walk, reference DFS order)
+        WideBvh wide;
+        build_wide(nodes, nn, ni, wide);
+        // a cycle among the child links is only possible when that walk did not certify a tree
+        const bool cyclic = !wide.ordered_ok && rt_bvh_has_cycle(nodes, nn);
+        if (!cyclic && ce == cudaSuccess && wide.ordered_ok) {
+            if ((wide.n_internal * 4 > c->wnodes.capacity || wide.leaves.size() > c->wleaves.capacity ||
+                 wide.leaf_nodes.size() > c->wleaf_nodes.capacity) && cudaStreamSynchronize(c->stream) != cudaSuccess)
+                ce = cudaErrorUnknown; // kernels may still read the auxiliary buffers a growth replaces
+            if (ce == cudaSuccess && (c->wide_index.reserve(nn) < 0 || c->wnodes.reserve((size_t)wide.n_internal * 4) < 0 ||
+                                      c->wleaves.reserve(wide.leaves.size()) < 0 || c->wleaf_nodes.reserve(wide.leaf_nodes.size()) < 0))
+                ce = cudaErrorMemoryAllocation;
+            if (ce == cudaSuccess && nn) ce = cudaMemcpyAsync(c->wide_index.ptr, wide.index.data(), (size_t)nn * 4, cudaMemcpyHostToDevice, c->stream);
+            if (ce == cudaSuccess && !wide.leaves.empty()) {
+                ce = cudaMemcpyAsync(c->wleaves.ptr, wide.leaves.data(), wide.leaves.size() * sizeof(uint2), cudaMemcpyHostToDevice, c->stream);
+                if (ce == cudaSuccess)
+                    ce = cudaMemcpyAsync(c->wleaf_nodes.ptr, wide.leaf_nodes.data(), wide.leaf_nodes.size() * 4, cudaMemcpyHostToDevice, c->stream);
             }
         }
-        // Borrowed host memory (src/buffers.rs:236 `queue.write_buffer` copy semantics): cudaMemcpyAsync from
-        // pageable memory returns once the source has been staged; from pinned memory it is a true async DMA,
-        // so the caller's arrays must stay valid until the stream reaches this point -> wait here.
-        CK(c, cudaStreamSynchronize(c->stream));
+        // Borrowed host memory (src/buffers.rs:236 `queue.write_buffer` copy semantics): the DMA reads the
+        // caller's arrays (and `wide`) until the stream reaches this point -> wait before returning.
+        cudaError_t se = cudaStreamSynchronize(c->stream);
+        if (cyclic)
+            return fail(c, RT_ERR_INVALID_ARGUMENT, "BVH child links form a cycle: the reference traversal would not terminate");
+        if (ce != cudaSuccess || se != cudaSuccess) {
+            // the live metadata buffer is untouched, but the auxiliary re-layout buffers may be half-written:
+            // the previous scene falls back to the literal policy until its next upload
+            c->wide.ordered_ok = false; c->wide.why_not = "a later upload failed half-way";
+            c->relayout_dirty = true;
+            return fail(c, RT_ERR_CUDA, "scene metadata upload failed: %s", cudaGetErrorString(ce != cudaSuccess ? ce : se));
+        }
+        std::swap(c->meta.ptr, c->meta_back.ptr);
+        std::swap(c->meta.capacity, c->meta_back.capacity);
+        c->scene_metadata_capacity_bytes = new_capacity;
+        c->wide = std::move(wide);
+        c->relayout_dirty = true; c->relayout_ok = false; c->rebuilt_ok = false;
         c->meta_len = total / 4;
         c->meta_dirty = false;
         c->last_spheres = ns; c->last_lights = nl; c->last_nodes = nn; c->last_indices = ni; c->last_vertices = nv;
@@ -639,9 +661,9 @@ int build_rebuilt(RtContext* c, uint32_t n) {
         c->lb_grid.reserve(8) < 0)
         return fail(c, RT_ERR_CUDA, "LBVH cudaMalloc failed for %u triangles", n);
     const uint32_t g = (n + 255) / 256;
-    const unsigned int init_bounds[8] = {0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0u, 0u, 0u, 0u, 0u}; // [6] = tree depth
-    CK(c, cudaMemcpyAsync(c->lb_bounds.ptr, init_bounds, sizeof init_bounds, cudaMemcpyHostToDevice, c->stream));
-    CK(c, cudaStreamSynchronize(c->stream)); // init_bounds is a stack array
+    // bounds[0..2] = 0xFFFFFFFF (ordered min), [3..7] = 0 (ordered max; [6] = tree depth)
+    CK(c, cudaMemsetAsync(c->lb_bounds.ptr, 0xFF, 12, c->stream));
+    CK(c, cudaMemsetAsync(c->lb_bounds.ptr + 3, 0, 20, c->stream));
     lbvh::centroid_bounds<<<g, 256, 0, c->stream>>>(c->pbox.ptr, n, c->lb_bounds.ptr);
     lbvh::morton_keys<<<g, 256, 0, c->stream>>>(c->pbox.ptr, n, c->lb_bounds.ptr, c->lb_keys.ptr, c->lb_vals.ptr);
     c->launches += 2;
@@ -668,28 +690,30 @@ int build_rebuilt(RtContext* c, uint32_t n) {
     }
     lbvh::gather_sorted<<<g, 256, 0, c->stream>>>(c->wtris.ptr, c->lb_vals_sorted.ptr, n, c->leaf_of_pos.ptr, c->btris.ptr);
     c->launches++;
-    // root: the whole tree collapses into one leaf when n <= RT_LBVH_LEAF
-    float4 rb[2];
-    unsigned int tree_depth = 0;
-    CK(c, cudaMemcpyAsync(&tree_depth, c->lb_bounds.ptr + 6, 4, cudaMemcpyDeviceToHost, c->stream));
-    if (n >= 2) CK(c, cudaMemcpyAsync(rb, c->lb_nbox.ptr, sizeof rb, cudaMemcpyDeviceToHost, c->stream));
-    else CK(c, cudaMemcpyAsync(rb, c->pbox.ptr, sizeof rb, cudaMemcpyDeviceToHost, c->stream));
+    // root box, grid and depth are read back by finish_rebuilt once the caller has waited for the stream
+    CK(c, cudaMemcpyAsync(&c->rb_depth, c->lb_bounds.ptr + 6, 4, cudaMemcpyDeviceToHost, c->stream));
+    CK(c, cudaMemcpyAsync(c->rb_box, n >= 2 ? c->lb_nbox.ptr : c->pbox.ptr, sizeof c->rb_box, cudaMemcpyDeviceToHost, c->stream));
     if (n >= 2) CK(c, cudaMemcpyAsync(c->bq_grid, c->lb_grid.ptr, sizeof c->bq_grid, cudaMemcpyDeviceToHost, c->stream));
-    CK(c, cudaStreamSynchronize(c->stream));
-    CK(c, cudaGetLastError());
+    return RT_OK;
+}
+
+void finish_rebuilt(RtContext* c, uint32_t n) {
+    if (n == 0 || n >= RT_LBVH_MAX_PRIMS) return;
+    const float4* rb = c->rb_box;
+    const unsigned int tree_depth = c->rb_depth;
     const float v[6] = {rb[0].x, rb[0].y, rb[0].z, rb[1].x, rb[1].y, rb[1].z};
     const float pad = lbvh::scene_pad(rb[0], rb[1]); // the same scene-wide inflation every box of the tree got
     for (int k = 0; k < 3; k++) { c->broot_min[k] = v[k] - pad; c->broot_max[k] = v[3 + k] + pad; }
     bool finite = true;
     for (float x : v) finite = finite && isfinite(x);
     c->rebuilt_far = RT_REBUILT_FAR * (pad * 65536.0f); // RT_REBUILT_FAR scene magnitudes
+    // root: the whole tree collapses into one leaf when n <= RT_LBVH_LEAF
     c->broot_ref = n <= RT_LBVH_LEAF ? (RT_LEAF_FLAG | ((n - 1u) << 28)) : 0u;
     if (getenv("RTB200_DEBUG")) fprintf(stderr, "[rtb200] internal LBVH: %u triangles, depth %u\n", n, tree_depth);
     c->lbvh_depth = tree_depth;
     // the traversal stacks hold 64 entries (many coincident centroids can deepen the tree); a scene with
     // non-finite coordinates has no usable grid or pad: such uploads keep the ORDERED / LITERAL policies
     c->rebuilt_ok = tree_depth < 60 && finite;
-    return RT_OK;
 }
 
 // Bring the ORDERED / REBUILT policy buffers up to date (all on the GPU).
@@ -715,6 +739,11 @@ int prepare_relayout(RtContext* c) {
             return fail(c, RT_ERR_CUDA, "relayout cudaMalloc failed");
         CK(c, cudaMemsetAsync(c->dflag.ptr, 0, 4, c->stream));
         CK(c, cudaMemsetAsync(c->leaf_of_pos.ptr, 0xFF, ((size_t)ni + 1) * 4, c->stream));
+        if (c->wide.n_internal) {
+            relayout_wide_nodes<<<(c->offsets.bvh_nodes_count + 255) / 256, 256, 0, c->stream>>>(c->meta.ptr, c->offsets, c->wide_index.ptr,
+                                                                                                 c->wnodes.ptr);
+            c->launches++;
+        }
         if (ni) {
             relayout_triangles<<<(ni + 255) / 256, 256, 0, c->stream>>>(c->meta.ptr, c->offsets, c->tris.ptr, c->n_tris,
                                                                         c->tpb, (uint32_t)c->tri_buffers, c->wtris.ptr,
@@ -729,19 +758,20 @@ int prepare_relayout(RtContext* c) {
                 c->launches++;
             }
         }
-        uint32_t flag = 0;
-        CK(c, cudaMemcpyAsync(&flag, c->dflag.ptr, 4, cudaMemcpyDeviceToHost, c->stream));
-        CK(c, cudaStreamSynchronize(c->stream));
-        CK(c, cudaGetLastError());
-        if (flag & 1u) return fail(c, RT_ERR_INVALID_SCENE, "a triangle references a vertex index >= vertices_count");
-        c->relayout_ok = true;
+        // the internal tree is enqueued before the validation flag is read back: one host wait for both
         if (want_rebuilt) {
             int r = build_rebuilt(c, ni);
             if (r != RT_OK) return r;
         }
+        uint32_t flag = 0;
+        CK(c, cudaMemcpyAsync(&flag, c->dflag.ptr, 4, cudaMemcpyDeviceToHost, c->stream));
         CK(c, cudaEventRecord(e1, c->stream));
         CK(c, cudaEventSynchronize(e1));
+        CK(c, cudaGetLastError());
         cudaEventElapsedTime(&c->last_build_ms, e0, e1);
+        if (flag & 1u) { c->rebuilt_ok = false; return fail(c, RT_ERR_INVALID_SCENE, "a triangle references a vertex index >= vertices_count"); }
+        c->relayout_ok = true;
+        if (want_rebuilt) finish_rebuilt(c, ni);
     }
     c->relayout_dirty = false;
     return RT_OK;
