@@ -991,10 +991,13 @@ int launch_wave(RtContext* c, KParams k, uint32_t traversal) {
         w.hit[0] = c->wv_hit[0].ptr + path_base; w.hit[1] = c->wv_hit[1].ptr + path_base;
         w.lbuf = c->wv_lbuf.ptr + path_base; w.ctrl = c->wv_ctrl.ptr + sub;
         path_base += Ps;
-        uint32_t ext_blocks = (uint32_t)(per_sm > 0 ? per_sm : 1) * (uint32_t)sms;
+        uint32_t ext_per_sm = (uint32_t)(per_sm > 0 ? per_sm : 1);
+        if (const char* e = getenv("RTB200_EXT_BLOCKS_PER_SM")) { int v = atoi(e); if (v >= 1 && (uint32_t)v < ext_per_sm) ext_per_sm = (uint32_t)v; } // tuning
+        uint32_t ext_blocks = ext_per_sm * (uint32_t)sms;
         uint32_t full_blocks = (uint32_t)((Ps + 255) / 256);
         if (ext_blocks > full_blocks) ext_blocks = full_blocks;
         uint32_t stream_blocks = (uint32_t)sms * 8u;
+        if (const char* e = getenv("RTB200_SHADE_BLOCKS_PER_SM")) { int v = atoi(e); if (v >= 1 && v <= 16) stream_blocks = (uint32_t)sms * (uint32_t)v; } // tuning
         if (stream_blocks > full_blocks) stream_blocks = full_blocks;
         for (uint32_t s0 = k.first_sample; s0 < s_end; s0 += spp_wave) {
             w.s0 = s0; w.spp_wave = s_end - s0 < spp_wave ? s_end - s0 : spp_wave;

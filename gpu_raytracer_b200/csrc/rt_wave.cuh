@@ -85,6 +85,9 @@ struct WvBuffers {
 #ifndef WV_FUSE_GEN
 #define WV_FUSE_GEN 1      // 1: no wv_generate launch; the depth-0 extend / shade compute the primary ray from the queue position
 #endif
+#ifndef WV_SHADE_BLOCKS
+#define WV_SHADE_BLOCKS 3  // resident blocks per SM the shade kernel is compiled for (4: 64 registers, some spills; measured +-0 alone)
+#endif
 #ifndef WV_BLOCKS
 #define WV_BLOCKS 4        // resident 256-thread blocks per SM the extend kernel is compiled for
 #endif
@@ -433,7 +436,7 @@ __global__ void __launch_bounds__(256, WV_BLOCKS) wv_extend(const __grid_constan
 // quarter of the rays left the scene.  Results are identical either way; on a closed scene the queueing only
 // costs (Cornell box: 5 % of the frame), on the open terrain it saves a sixth of the shading time.
 template <int POLICY, bool COUNT, bool GEN, bool SPLIT>
-__global__ void __launch_bounds__(256, 3) wv_shade(const __grid_constant__ KParams p, WvBuffers w, int qi) {
+__global__ void __launch_bounds__(256, WV_SHADE_BLOCKS) wv_shade(const __grid_constant__ KParams p, WvBuffers w, int qi) {
     const unsigned full = 0xFFFFFFFFu;
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t n = GEN ? p.n_work * w.spp_wave : w.ctrl->n[qi];
