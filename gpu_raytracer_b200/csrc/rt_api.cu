@@ -119,6 +119,7 @@ struct RtContext {
     float rebuilt_far = 0.0f; // rays whose origin has a coordinate beyond this take the literal policy (rt_lbvh.cuh)
     float last_build_ms = -1.0f;
     bool last_was_wavefront = false;
+    uint32_t last_wave_max_depth = 0, last_wave_seed = 0;
     // streaming wavefront engine (rt_wave.cuh)
     DevBuf<float4> wv_state[2], wv_lbuf;
     DevBuf<uint2> wv_hit[2];
@@ -380,7 +381,7 @@ int rt_create(int device, RtContext** out) {
                                        1024 * sizeof(uint32_t) + 1024 * sizeof(RtVertex);
     if (c->meta.reserve(c->scene_metadata_capacity_bytes / 4) < 0 || c->mats.reserve(c->mats_capacity) < 0 ||
         c->textures.reserve(c->textures_capacity) < 0 || c->texdata.reserve(c->texdata_capacity) < 0 ||
-        c->tris.reserve(64) < 0 || c->dflag.reserve(1) < 0 || c->dcounters.reserve(16) < 0) {
+        c->tris.reserve(64) < 0 || c->dflag.reserve(1) < 0 || c->dcounters.reserve(32) < 0) {
         fail(nullptr, RT_ERR_CUDA, "rt_create: cudaMalloc failed");
         delete c;
         return RT_ERR_CUDA;
@@ -887,6 +888,7 @@ __global__ void wv_publish(const WvCtrl* ctrl, int n_sub, unsigned long long* dc
     unsigned long long seg = 0, cc[4] = {0, 0, 0, 0};
     for (int i = 0; i < n_sub; i++) { seg += ctrl[i].segments; for (int j = 0; j < 4; j++) cc[j] += ctrl[i].c[j]; }
     dcounters[6] = seg; // rt_last_segments
+    for (int d = 0; d < 8; d++) { unsigned long long r = 0; for (int i = 0; i < n_sub; i++) r += ctrl[i].rays_at_depth[d]; dcounters[16 + d] = r; }
     if (count) { dcounters[0] = cc[0]; dcounters[1] = cc[1]; dcounters[2] = seg; dcounters[3] = cc[2]; dcounters[4] = cc[3]; }
 }
 
@@ -1012,6 +1014,7 @@ int launch_wave(RtContext* c, KParams k, uint32_t traversal) {
             for (uint32_t d = 0; d <= k.path_max_depth; d++) {
                 const int qi = (int)(d & 1u);
                 const bool gen = WV_FUSE_GEN && d == 0u; // depth 0 computes its primary rays from the queue position
+                w.depth = d;
                 wv_extend_kernel(policy, count, gen, deep)<<<ext_blocks, 256, 0, st>>>(ks, w, qi);
                 mark(1);
                 // both forms are launched; the one that does not match the depth's miss ratio returns at once
@@ -1035,6 +1038,7 @@ int launch_wave(RtContext* c, KParams k, uint32_t traversal) {
     c->last_traversal = policy == 2 ? RT_TRAVERSAL_REBUILT : RT_TRAVERSAL_ORDERED;
     c->count_next = false;
     c->last_was_wavefront = true;
+    c->last_wave_max_depth = k.path_max_depth; c->last_wave_seed = k.base_seed;
     return RT_OK;
 }
 
@@ -1385,6 +1389,28 @@ int rt_last_segments(RtContext* c, uint64_t* out) {
     return RT_OK;
 }
 float rt_last_build_ms(const RtContext* c) { return c ? c->last_build_ms : -1.0f; }
+
+// WavefrontCounters of the last streaming-wavefront frame (shared/src/lib.rs:187-194, 1006-1043): what the
+// reference's host loop (src/compute.rs:413-479) only simulates with a 0.7^depth decay is counted here.
+int rt_last_wavefront_counters(RtContext* c, RtWavefrontCounters* out) {
+    if (!c || !out) return RT_ERR_INVALID_ARGUMENT;
+    if (!c->last_was_wavefront) return fail(c, RT_ERR_NOT_READY, "the last launch was not a wave-engine frame");
+    CK(c, cudaSetDevice(c->device));
+    unsigned long long h[8];
+    CK(c, cudaMemcpyAsync(h, c->dcounters.ptr + 16, sizeof h, cudaMemcpyDeviceToHost, c->stream));
+    CK(c, cudaStreamSynchronize(c->stream));
+    memset(out, 0, sizeof *out);
+    unsigned long long total = 0;
+    for (int d = 0; d < 8; d++) {
+        out->rays_per_bounce[d] = h[d] > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t)h[d]; // u32 like the reference; saturating
+        if (h[d]) out->active_bounce_depths |= 1u << d;                                  // WavefrontCounters::add_rays
+        total += h[d];
+    }
+    out->total_rays_generated = total > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t)total;
+    out->max_bounce_depth = c->last_wave_max_depth;
+    out->frame_seed = c->last_wave_seed;
+    return RT_OK;
+}
 
 // GPU time per stage of the last streaming-wavefront frame (rt_wave.cuh), summed over its
 // launches: out[0] generate, [1] extend, [2] shade, [3] resolve (ms); out[4..7] launch counts.

@@ -30,6 +30,8 @@ struct WvCtrl {
     unsigned long long c[4];    // instrumentation: box tests, triangle tests, shaded hits, literal fallbacks
     unsigned int misses[2];     // rays of the current / next depth that hit nothing (picks wv_shade's form)
     unsigned int _pad2[2];
+    unsigned int rays_at_depth[8]; // ray segments traced per bounce depth (depths >= 7 share the last entry): the
+                                   // reference's WavefrontCounters.rays_per_bounce (shared/src/lib.rs:187-194)
 };
 
 struct WvBuffers {
@@ -41,6 +43,7 @@ struct WvBuffers {
     uint32_t last_wave;    // resolve writes the composite
     uint32_t first_wave;   // resolve honours reset_accum
     uint32_t valid_pixels; // work items of this sub-frame that lie inside the image (fused generation: segment count of depth 0)
+    uint32_t depth;        // bounce depth of this launch (bookkeeping only: rays_at_depth)
 };
 
 // hit id encoding
@@ -443,7 +446,9 @@ __global__ void __launch_bounds__(256, WV_SHADE_BLOCKS) wv_shade(const __grid_co
     const float4* __restrict__ tris = POLICY == 2 ? p.btris : p.wtris;
     if (!SPLIT && blockIdx.x == 0 && threadIdx.x == 0) { // wv_extend of this depth has finished (first of the two launches)
         w.ctrl->head = 0;
-        w.ctrl->segments += GEN ? (unsigned long long)w.valid_pixels * w.spp_wave : (unsigned long long)n;
+        const unsigned long long traced = GEN ? (unsigned long long)w.valid_pixels * w.spp_wave : (unsigned long long)n;
+        w.ctrl->segments += traced;
+        w.ctrl->rays_at_depth[w.depth < 7u ? w.depth : 7u] += (unsigned int)traced;
     }
     if (((unsigned long long)w.ctrl->misses[qi] * 4ull > (unsigned long long)n) != SPLIT) return;
     // Paths whose ray left the scene (on open scenes most of depth >= 1) only add the sky term; if they shared

@@ -150,6 +150,12 @@ class Context:
         self._ck(self.lib.rt_last_segments(self.handle, C.byref(out)))
         return int(out.value)
 
+    def last_wavefront_counters(self):
+        """WavefrontCounters of the last wave-engine path frame (shared/src/lib.rs:187-194)."""
+        out = np.zeros((), abi.WavefrontCounters)
+        self._ck(self.lib.rt_last_wavefront_counters(self.handle, out.ctypes.data_as(C.c_void_p)))
+        return out
+
     @property
     def last_build_ms(self):
         return float(self.lib.rt_last_build_ms(self.handle))

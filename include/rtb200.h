@@ -196,6 +196,11 @@ int rt_close_peer_frame(RtContext* ctx);
 void* rt_stream(RtContext* ctx);
 /* EXTENSION: ray segments traced by the last RT_MODE_PATH launch (SPEC.md) */
 int rt_last_segments(RtContext* ctx, uint64_t* out);
+/* EXTENSION: the reference's WavefrontCounters (shared/src/lib.rs:187-194; host loop src/compute.rs:413-479, which
+ * only simulates the per-depth ray counts) for the last RT_MODE_PATH frame of the streaming wavefront engine:
+ * rays_per_bounce[d] = ray segments traced at bounce depth d (depths >= 7 share entry 7), total, active-depth
+ * bitmask, max depth and base seed.  Counts saturate at 2^32 - 1.  RT_ERR_NOT_READY after another engine. */
+int rt_last_wavefront_counters(RtContext* ctx, RtWavefrontCounters* out);
 /* GPU time of the last upload-time re-layout + LBVH build, ms (<0 if none) */
 float rt_last_build_ms(const RtContext* ctx);
 /* EXTENSION, streaming wavefront engine: GPU time per stage of the last RT_MODE_PATH frame,

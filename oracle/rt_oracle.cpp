@@ -44,7 +44,9 @@ struct Bind {
 
 struct Counters {
     uint64_t aabb_tests = 0, tri_tests = 0, sphere_tests = 0, rays = 0;
+    uint64_t depth_rays[8] = {0, 0, 0, 0, 0, 0, 0, 0}; /* path mode: segments per bounce depth (>= 7 share the last) */
 };
+static uint64_t g_last_depth_rays[8]; /* of the last orc_render_path call (orc_last_depth_rays) */
 
 struct Ray {
     V3 origin, direction;
@@ -540,6 +542,7 @@ static V3 path_sample(const Bind& b, uint32_t px, uint32_t py, uint32_t s, const
     uint32_t depth = 0;
     for (;;) {
         c.rays++;
+        c.depth_rays[depth < 7 ? depth : 7]++;
         Hit h = find_closest(ray, b, c);
         if (depth == 0 && primary) *primary = h;
         if (!h.hit) { L = L + v3(0.1f, 0.2f, 0.3f) * tp; break; }
@@ -743,8 +746,13 @@ int orc_render_path(const OrcBindings* ob, const RtPushConstants* pc, uint32_t s
             counters->aabb_tests += c.aabb_tests; counters->tri_tests += c.tri_tests;
             counters->sphere_tests += c.sphere_tests; counters->rays += c.rays;
         }
+    for (int d = 0; d < 8; d++) { g_last_depth_rays[d] = 0; for (auto& c : cs) g_last_depth_rays[d] += c.depth_rays[d]; }
     return 0;
 }
+
+/* Ray segments per bounce depth of the last orc_render_path call: what WavefrontCounters.rays_per_bounce
+ * (shared/src/lib.rs:187-194) would hold if the reference's wavefront loop were live. */
+void orc_last_depth_rays(uint64_t out[8]) { for (int d = 0; d < 8; d++) out[d] = g_last_depth_rays[d]; }
 
 /* resolve: rgb / w -> Rgba8Unorm (SPEC.md step 4) */
 void orc_resolve(const float* accum, uint8_t* out, uint64_t pixels) {

@@ -41,6 +41,7 @@ int orc_dispatch_policy(const OrcBindings* ob, const RtPushConstants* pc, uint8_
 int orc_render_path(const OrcBindings* ob, const RtPushConstants* pc, uint32_t spp, uint32_t first_sample,
                     uint32_t max_depth, uint32_t base_seed, int reset, uint32_t y0, uint32_t y1, float* accum,
                     OrcHit* hits, int threads, OrcCounters* counters, int policy);
+void orc_last_depth_rays(uint64_t out[8]);
 void orc_resolve(const float* accum, uint8_t* out, uint64_t pixels);
 void orc_composite(const uint8_t* r, const uint8_t* g, const uint8_t* b, uint8_t* out, uint64_t pixels);
 uint16_t orc_f32_to_f16(float f);

@@ -38,6 +38,8 @@ def lib():
         _lib.orc_render_path.argtypes = [C.POINTER(OrcBindings), C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32,
                                          C.c_int, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p, C.c_int,
                                          C.POINTER(OrcCounters), C.c_int]
+        _lib.orc_last_depth_rays.restype = None
+        _lib.orc_last_depth_rays.argtypes = [C.c_void_p]
         _lib.orc_resolve.restype = None
         _lib.orc_resolve.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64]
         _lib.orc_composite.restype = None
@@ -195,6 +197,8 @@ def render_path(scene, width, height, spp=1, max_depth=0, base_seed=1, first_sam
     resolved = np.zeros((height, width, 4), np.uint8)
     with np.errstate(all="ignore"):
         lib().orc_resolve(accum.ctypes.data, resolved.ctypes.data, width * height)
-    return dict(accum=accum, resolved=resolved, hits=hits,
+    depth_rays = np.zeros(8, np.uint64)
+    lib().orc_last_depth_rays(depth_rays.ctypes.data)
+    return dict(accum=accum, resolved=resolved, hits=hits, depth_rays=depth_rays,
                 counters=dict(aabb_tests=counters.aabb_tests, tri_tests=counters.tri_tests,
                               sphere_tests=counters.sphere_tests, rays=counters.rays))

@@ -757,3 +757,22 @@ def test_c5_10m_triangles_4k():
         assert np.array_equal(pacc[y].view(np.uint32), refp["accum"][y].view(np.uint32)), y
         assert np.array_equal(pcomp[y], refp["resolved"][y])
     ctx.close()
+
+
+def test_wavefront_counters_per_bounce_depth(default_ref):
+    """WavefrontCounters (shared/src/lib.rs:187-194) of a wave-engine frame against the oracle's per-depth counts."""
+    s, _ = default_ref
+    w, h = 320, 180
+    ref = ob.render_path(s, w, h, spp=3, max_depth=9, base_seed=21)
+    ctx = g.Context(0, w, h)
+    g.BufferManager(ctx).upload_scene(s)
+    g.ComputeRenderer(ctx).render_frame(s.camera, mode=abi.MODE_PATH, spp=3, max_depth=9, base_seed=21, variant=4)
+    wc = ctx.last_wavefront_counters()
+    assert list(wc["rays_per_bounce"]) == [int(x) for x in ref["depth_rays"]]
+    assert wc["rays_per_bounce"][0] == w * h * 3 and wc["total_rays_generated"] == ref["counters"]["rays"] == ctx.last_segments
+    assert wc["max_bounce_depth"] == 9 and wc["frame_seed"] == 21
+    assert wc["active_bounce_depths"] == sum(1 << d for d in range(8) if ref["depth_rays"][d])
+    g.ComputeRenderer(ctx).render_frame(s.camera, mode=abi.MODE_PATH, spp=1, max_depth=2, variant=1)  # megakernel
+    with pytest.raises(g.RtError):
+        ctx.last_wavefront_counters()
+    ctx.close()
