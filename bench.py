@@ -104,6 +104,9 @@ def parse_args():
     ap.add_argument("--variant", type=int, default=0, help="path mode engine: 0 auto = streaming wavefront (default), 1 megakernel, "
                                                            "4 streaming wavefront")
     ap.add_argument("--traversal", default="auto", choices=["auto", "literal", "ordered", "rebuilt"])
+    ap.add_argument("--balance", type=int, default=4,
+                    help="N > 1: load-balancing steps during warm-up (explicit per-rank tile lists adjusted on the previous "
+                         "frames' per-rank GPU times, tiles.rebalance); 0 keeps tile i -> rank i %% N")
     ap.add_argument("--gather", default="peer", choices=["peer", "nccl"],
                     help="N > 1: how finished tiles reach rank 0: peer = P2P stores from the render kernels into rank 0's "
                          "frame (CUDA IPC) + a 4-byte NCCL all-reduce as barrier; nccl = pack + dist.gather + unpack")
@@ -336,8 +339,16 @@ def run_b200(args, wl, world, rank, local):
         except g.RtError as e:  # no P2P between these GPUs: NCCL path
             print("peer frame unavailable (%s): falling back to the NCCL gather" % e, file=sys.stderr)
             peer = None
+    lists = None
+    if world > 1 and args.balance > 0:  # explicit tile lists, balanced below during warm-up
+        lists = tiles.initial_lists(w, h, world)
+        ctx.set_tile_list(lists[rank])
+        stride, phase = 0, 0
+
+    def make_gather():
+        return tiles.TileGather(dist, torch, w, h, tiles.WHAT_COMPOSITE, "cuda", lists=lists)
     if world > 1 and peer is None:
-        gather = tiles.TileGather(dist, torch, w, h, tiles.WHAT_COMPOSITE, "cuda")
+        gather = make_gather()
     flush = torch.empty(512 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
 
     def render():
@@ -354,11 +365,32 @@ def run_b200(args, wl, world, rank, local):
             peer.finish()  # the tiles are already in rank 0's frame (P2P stores in the kernels); stream-ordered barrier
         elif gather is not None:
             with torch.cuda.stream(stream):  # NCCL is ordered after the kernel on the context's stream
-                gather.run(lambda dst: ctx.pack_tiles(tiles.WHAT_COMPOSITE, world, rank, dst.data_ptr()),
-                           lambda src, r: ctx.unpack_tiles(tiles.WHAT_COMPOSITE, world, r, src.data_ptr()))
+                if lists is not None:
+                    gather.run(lambda dst: ctx.pack_tile_list(tiles.WHAT_COMPOSITE, lists[rank], dst.data_ptr()),
+                               lambda src, r: ctx.unpack_tile_list(tiles.WHAT_COMPOSITE, lists[r], src.data_ptr()))
+                else:
+                    gather.run(lambda dst: ctx.pack_tiles(tiles.WHAT_COMPOSITE, world, rank, dst.data_ptr()),
+                               lambda src, r: ctx.unpack_tiles(tiles.WHAT_COMPOSITE, world, r, src.data_ptr()))
 
     clocks = ClockSampler(local)
     clocks.start()  # sampled under the same load from the warm-up on (nvidia-smi takes a few 100 ms to start)
+    balance_log = []
+    if lists is not None:  # load balancing on the previous frames' per-rank GPU times (untimed warm-up frames)
+        for _ in range(args.balance):
+            for _ in range(2):
+                frame()
+            ctx.synchronize()
+            t = torch.tensor([ctx.last_kernel_ms], dtype=torch.float64, device="cuda")
+            allt = [torch.zeros_like(t) for _ in range(world)]
+            dist.all_gather(allt, t)
+            times = [float(x.item()) for x in allt]
+            balance_log.append({"rank_frame_ms": [round(x, 4) for x in times], "tiles": [len(l) for l in lists]})
+            lists = tiles.rebalance(lists, times)
+            ctx.set_tile_list(lists[rank])
+            if gather is not None:
+                gather = make_gather()
+        my_tiles = len(lists[rank])
+        my_pixels = tiles.pixels_of_tiles(w, h, lists[rank])
     for _ in range(max(args.warmup, 3)):
         frame()
     ctx.synchronize()
@@ -443,11 +475,14 @@ def run_b200(args, wl, world, rank, local):
     assembled_ok = None
     if world > 1 and rank == 0:
         got = host_img.copy()
+        ctx.set_tile_list(None)  # the whole frame on this one context
         if path:
             cr.render_frame(ps.camera, mode=abi.MODE_PATH, spp=wl["spp"], max_depth=wl["depth"], base_seed=1,
                             outputs=abi.OUT_ACCUM | abi.OUT_COMPOSITE, traversal=trav, variant=args.variant)
         else:
             cr.render_frame(ps.camera, outputs=abi.OUT_ACCUM | abi.OUT_COMPOSITE, traversal=trav)
+        if lists is not None:
+            ctx.set_tile_list(lists[0])
         assembled_ok = bool(np.array_equal(got, ctx.read_composite()))
     if peer is not None:
         peer.close()  # ranks != 0 unmap rank 0's frame before anybody frees anything
@@ -613,8 +648,10 @@ def run_b200(args, wl, world, rank, local):
                            ("megakernel" if path else "fused trace+shade kernel")),
                 "literal_fallback_rays": cnt["literal_fallbacks"], "upload_relayout_build_ms": ctx.last_build_ms,
                 "tiles_per_rank": my_tiles, "src_hash": source_hash(),
-                "parallelism": ("64x64 tile split x%d (tile i -> rank i %% N), scene replicated, %s inside the timed step"
-                                % (world, "composite pixels stored into rank 0's frame by the render kernels (P2P over NVLink, "
+                "tile_balance": ({"steps": balance_log, "tiles_per_rank": [len(l) for l in lists]} if lists is not None else None),
+                "parallelism": ("64x64 tile split x%d (%s), scene replicated, %s inside the timed step"
+                                % (world, "per-rank tile lists balanced on the warm-up frames' per-rank GPU times" if lists is not None
+                                   else "tile i -> rank i % N", "composite pixels stored into rank 0's frame by the render kernels (P2P over NVLink, "
                                           "CUDA IPC) + 4-byte NCCL all-reduce as barrier" if peer is not None else
                                    "NCCL gather of the composite tiles to rank 0")) if world > 1 else "single GPU"},
         "roofline": roof,

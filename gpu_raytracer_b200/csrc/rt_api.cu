@@ -140,6 +140,9 @@ struct RtContext {
     uchar4* peer_composite = nullptr; // rank 0's composite through peer memory (fused multi-GPU epilogue)
     bool peer_is_ipc = false;
     uint32_t stiles_x = 0, stiles_y = 0; // RT_SPLIT_TILE^2 split tiles of the fused frame / multi-GPU split
+    DevBuf<uint32_t> tile_list, copy_list; // rt_set_tile_list assignment; scratch list of rt_(un)pack_tile_list
+    std::vector<uint32_t> tile_list_host;
+    uint32_t tile_list_n = 0;
     bool needs_recompute = true, is_progressive = false;
 };
 
@@ -338,10 +341,11 @@ __global__ void relayout_leaf_counts(const uint2* __restrict__ leaves, const uin
 // [local tile][128][128]; unpack: the inverse, into the full frame.  T = uchar4 / float4.
 template <class T, bool PACK>
 __global__ void tile_copy(T* __restrict__ frame, T* __restrict__ compact, uint32_t width, uint32_t height, uint32_t tiles_x,
-                          uint32_t n_tiles_total, uint32_t stride, uint32_t phase) {
+                          uint32_t n_tiles_total, uint32_t stride, uint32_t phase, const uint32_t* __restrict__ tile_list) {
     uint32_t tile_local = blockIdx.y;
     uint32_t tile = phase + tile_local * stride;
     if (tile >= n_tiles_total) return;
+    if (tile_list) tile = tile_list[tile];
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; // 0..4095
     uint32_t x = (tile % tiles_x) * RT_SPLIT_TILE + (i & 63u), y = (tile / tiles_x) * RT_SPLIT_TILE + (i >> 6);
     size_t ci = (size_t)tile_local * 4096u + i;
@@ -431,6 +435,7 @@ int rt_resize(RtContext* c, uint32_t w, uint32_t h) {
     // ProgressiveState::resize, src/renderer.rs:838-848
     rt_tile_count(w, h, RT_TILE_SIZE, &c->tiles_x, &c->tiles_y);
     rt_tile_count(w, h, RT_SPLIT_TILE, &c->stiles_x, &c->stiles_y);
+    c->tile_list_n = 0; c->tile_list_host.clear(); // tile numbers belong to the old frame size
     c->tiles_per_frame = rt_tiles_per_frame(c->tiles_x * c->tiles_y);
     c->needs_recompute = true; c->current_tile = 0; c->is_progressive = false;
     return RT_OK;
@@ -983,7 +988,9 @@ int launch_wave(RtContext* c, KParams k, uint32_t traversal) {
         WvBuffers w;
         w.valid_pixels = 0; // pixels of this sub-frame's tiles that lie inside the image
         for (uint32_t t = 0; t < tiles_s; t++) {
-            const uint32_t tile = ks.tile_phase + t * ks.tile_stride, tx = tile % ks.tiles_x, ty = tile / ks.tiles_x;
+            uint32_t tile = ks.tile_phase + t * ks.tile_stride;
+            if (ks.tile_list) tile = c->tile_list_host[tile];
+            const uint32_t tx = tile % ks.tiles_x, ty = tile / ks.tiles_x;
             const uint32_t x0 = tx * RT_SPLIT_TILE, y0 = ty * RT_SPLIT_TILE;
             const uint32_t tw = x0 >= ks.width ? 0u : (ks.width - x0 < RT_SPLIT_TILE ? ks.width - x0 : RT_SPLIT_TILE);
             const uint32_t th = y0 >= ks.height ? 0u : (ks.height - y0 < RT_SPLIT_TILE ? ks.height - y0 : RT_SPLIT_TILE);
@@ -1070,7 +1077,9 @@ int launch_primary_wave(RtContext* c, KParams k, uint32_t traversal, uint32_t my
     w.ctrl = c->wv_ctrl.ptr;
     w.s0 = 0; w.spp_wave = 1; w.first_wave = 1; w.last_wave = 1;
     for (uint32_t t = 0; t < my_tiles; t++) {
-        const uint32_t tile = k.tile_phase + t * k.tile_stride, tx = tile % k.tiles_x, ty = tile / k.tiles_x;
+        uint32_t tile = k.tile_phase + t * k.tile_stride;
+        if (k.tile_list) tile = c->tile_list_host[tile];
+        const uint32_t tx = tile % k.tiles_x, ty = tile / k.tiles_x;
         const uint32_t x0 = tx * RT_SPLIT_TILE, y0 = ty * RT_SPLIT_TILE;
         const uint32_t tw = x0 >= k.width ? 0u : (k.width - x0 < RT_SPLIT_TILE ? k.width - x0 : RT_SPLIT_TILE);
         const uint32_t th = y0 >= k.height ? 0u : (k.height - y0 < RT_SPLIT_TILE ? k.height - y0 : RT_SPLIT_TILE);
@@ -1182,6 +1191,7 @@ int rt_render_frame(RtContext* c, const RtCamera* cam, const RtFrameParams* fp) 
     fill_camera(k, *cam);
     k.use_tiles = 1;
     k.tiles_x = c->stiles_x; k.n_tiles_total = c->stiles_x * c->stiles_y;
+    if (c->tile_list_n) { k.tile_list = c->tile_list.ptr; k.n_tiles_total = c->tile_list_n; } // stride / phase walk the list
     k.tile_stride = fp->tile_stride ? fp->tile_stride : 1u;
     k.tile_phase = fp->tile_stride ? fp->tile_phase : 0u;
     if (k.tile_phase >= k.tile_stride) return fail(c, RT_ERR_INVALID_ARGUMENT, "tile_phase >= tile_stride");
@@ -1317,31 +1327,73 @@ int rt_last_traversal(const RtContext* c) { return c ? c->last_traversal : 0; }
 void* rt_stream(RtContext* c) { return c ? (void*)c->stream : nullptr; }
 
 // what: 0 = composite rgba8 (4 B/px), 1 = accumulation float4 (16 B/px)
-static int tile_copy_launch(RtContext* c, uint32_t what, uint32_t stride, uint32_t phase, void* compact, bool pack) {
+// list != NULL: a host array of n tiles (staged into the context's scratch list buffer); else stride / phase over
+// the context's own assignment (its tile list if one is set, otherwise tile i -> i % stride)
+static int tile_copy_launch(RtContext* c, uint32_t what, uint32_t stride, uint32_t phase, const uint32_t* list, uint32_t n,
+                            void* compact, bool pack) {
     if (!c || !compact) return RT_ERR_INVALID_ARGUMENT;
     if (c->width == 0) return fail(c, RT_ERR_NOT_READY, "rt_resize has not been called");
     if (stride == 0 || phase >= stride || what > 1) return fail(c, RT_ERR_INVALID_ARGUMENT, "tile copy: bad stride/phase/what");
     CK(c, cudaSetDevice(c->device));
-    uint32_t total = c->stiles_x * c->stiles_y;
+    const uint32_t frame_tiles = c->stiles_x * c->stiles_y;
+    const uint32_t* dlist = nullptr;
+    uint32_t total = frame_tiles;
+    if (list) {
+        for (uint32_t i = 0; i < n; i++) if (list[i] >= frame_tiles) return fail(c, RT_ERR_INVALID_ARGUMENT, "tile %u of %u", list[i], frame_tiles);
+        if (n > c->copy_list.capacity) CK(c, cudaStreamSynchronize(c->stream));
+        if (c->copy_list.reserve(n ? n : 1) < 0) return fail(c, RT_ERR_CUDA, "tile list cudaMalloc failed");
+        if (n) CK(c, cudaMemcpyAsync(c->copy_list.ptr, list, (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
+        CK(c, cudaStreamSynchronize(c->stream)); // `list` is borrowed for the call
+        dlist = c->copy_list.ptr; total = n;
+    } else if (c->tile_list_n) { dlist = c->tile_list.ptr; total = c->tile_list_n; }
     uint32_t mine = total > phase ? (total - phase + stride - 1) / stride : 0;
     if (!mine) return RT_OK;
     dim3 grid(4096 / 256, mine);
     if (what == 0) {
-        if (pack) tile_copy<uchar4, true><<<grid, 256, 0, c->stream>>>(c->composite.ptr, (uchar4*)compact, c->width, c->height, c->stiles_x, total, stride, phase);
-        else tile_copy<uchar4, false><<<grid, 256, 0, c->stream>>>(c->composite.ptr, (uchar4*)compact, c->width, c->height, c->stiles_x, total, stride, phase);
+        if (pack) tile_copy<uchar4, true><<<grid, 256, 0, c->stream>>>(c->composite.ptr, (uchar4*)compact, c->width, c->height, c->stiles_x, total, stride, phase, dlist);
+        else tile_copy<uchar4, false><<<grid, 256, 0, c->stream>>>(c->composite.ptr, (uchar4*)compact, c->width, c->height, c->stiles_x, total, stride, phase, dlist);
     } else {
-        if (pack) tile_copy<float4, true><<<grid, 256, 0, c->stream>>>(c->accum.ptr, (float4*)compact, c->width, c->height, c->stiles_x, total, stride, phase);
-        else tile_copy<float4, false><<<grid, 256, 0, c->stream>>>(c->accum.ptr, (float4*)compact, c->width, c->height, c->stiles_x, total, stride, phase);
+        if (pack) tile_copy<float4, true><<<grid, 256, 0, c->stream>>>(c->accum.ptr, (float4*)compact, c->width, c->height, c->stiles_x, total, stride, phase, dlist);
+        else tile_copy<float4, false><<<grid, 256, 0, c->stream>>>(c->accum.ptr, (float4*)compact, c->width, c->height, c->stiles_x, total, stride, phase, dlist);
     }
     CK(c, cudaGetLastError());
     c->launches++;
     return RT_OK;
 }
 int rt_pack_tiles(RtContext* c, uint32_t what, uint32_t stride, uint32_t phase, void* dst_device) {
-    return tile_copy_launch(c, what, stride, phase, dst_device, true);
+    return tile_copy_launch(c, what, stride, phase, nullptr, 0, dst_device, true);
 }
 int rt_unpack_tiles(RtContext* c, uint32_t what, uint32_t stride, uint32_t phase, const void* src_device) {
-    return tile_copy_launch(c, what, stride, phase, const_cast<void*>(src_device), false);
+    return tile_copy_launch(c, what, stride, phase, nullptr, 0, const_cast<void*>(src_device), false);
+}
+int rt_pack_tile_list(RtContext* c, uint32_t what, const uint32_t* tiles, uint32_t n, void* dst_device) {
+    if (n && !tiles) return RT_ERR_INVALID_ARGUMENT;
+    static const uint32_t none = 0;
+    return tile_copy_launch(c, what, 1, 0, tiles ? tiles : &none, n, dst_device, true);
+}
+int rt_unpack_tile_list(RtContext* c, uint32_t what, const uint32_t* tiles, uint32_t n, const void* src_device) {
+    if (n && !tiles) return RT_ERR_INVALID_ARGUMENT;
+    static const uint32_t none = 0;
+    return tile_copy_launch(c, what, 1, 0, tiles ? tiles : &none, n, const_cast<void*>(src_device), false);
+}
+// Explicit tile assignment of this context for fused frames (multi-GPU load balancing): `tiles` = the split tiles
+// (numbered row-major, RT_SPLIT_TILE^2 pixels) it renders, in the order it walks them.  n = 0 returns to the
+// arithmetic assignment tile i -> i % tile_stride.
+int rt_set_tile_list(RtContext* c, const uint32_t* tiles, uint32_t n) {
+    if (!c || (n && !tiles)) return RT_ERR_INVALID_ARGUMENT;
+    if (c->width == 0) return fail(c, RT_ERR_NOT_READY, "rt_resize has not been called");
+    CK(c, cudaSetDevice(c->device));
+    const uint32_t frame_tiles = c->stiles_x * c->stiles_y;
+    for (uint32_t i = 0; i < n; i++) if (tiles[i] >= frame_tiles) return fail(c, RT_ERR_INVALID_ARGUMENT, "tile %u of %u", tiles[i], frame_tiles);
+    CK(c, cudaStreamSynchronize(c->stream)); // frames in flight still read the old list
+    if (n) {
+        if (c->tile_list.reserve(n) < 0) return fail(c, RT_ERR_CUDA, "tile list cudaMalloc failed");
+        CK(c, cudaMemcpyAsync(c->tile_list.ptr, tiles, (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
+        CK(c, cudaStreamSynchronize(c->stream));
+    }
+    c->tile_list_host.assign(tiles, tiles + n);
+    c->tile_list_n = n;
+    return RT_OK;
 }
 
 int rt_export_frame_handle(RtContext* c, void* out_handle64) {

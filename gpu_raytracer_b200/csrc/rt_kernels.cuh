@@ -38,6 +38,8 @@ struct KParams {
     // work: pixel rectangle of one dispatch, or tiles of a fused frame
     uint32_t rect_x0, rect_y0, rect_w, rect_h;
     uint32_t tiles_x, n_tiles_total, tile_stride, tile_phase; // fused frame: RT_SPLIT_TILE^2 tile split
+    const uint32_t* tile_list; // explicit assignment (rt_set_tile_list): entry j = a tile of the frame; n_tiles_total = its
+                               // length and stride / phase walk the list.  NULL: entry j is tile j (tile i -> i % stride)
     uint32_t use_tiles;       // 1: fused frame over tiles; 0: single rect
     uint32_t mode;            // RT_MODE_*
     uint32_t outputs;         // RT_OUT_*
@@ -615,6 +617,7 @@ __device__ __forceinline__ bool pixel_of_thread(const KParams& p, uint32_t* px, 
         uint32_t tile_local = blk >> 4, sub = blk & 15u; // 16 blocks of 16x16 pixels per 64x64 split tile
         uint32_t tile = p.tile_phase + tile_local * p.tile_stride;
         if (tile >= p.n_tiles_total) return false;
+        if (p.tile_list) tile = __ldg(p.tile_list + tile);
         uint32_t tx = tile % p.tiles_x, ty = tile / p.tiles_x;
         x0 = tx * RT_SPLIT_TILE; y0 = ty * RT_SPLIT_TILE; w = RT_SPLIT_TILE; h = RT_SPLIT_TILE;
         lx += (sub & 3u) * 16u; ly += (sub >> 2) * 16u;
@@ -786,6 +789,7 @@ __device__ __forceinline__ bool path_bounce(const KParams& p, const Hit& h, Ray&
 __device__ __forceinline__ bool work_to_pixel(const KParams& p, uint32_t idx, uint32_t* px, uint32_t* py) {
     uint32_t tile_local = idx >> 12, within = idx & 4095u; // 4096 work items per 64x64 split tile
     uint32_t tile = p.tile_phase + tile_local * p.tile_stride;
+    if (p.tile_list) tile = __ldg(p.tile_list + tile);
     uint32_t tx = tile % p.tiles_x, ty = tile / p.tiles_x;
     uint32_t sub = within >> 5, l = within & 31u; // 8x4 pixel groups, 8 across x 16 down per tile
     *px = tx * RT_SPLIT_TILE + (sub & 7u) * 8u + (l & 7u);

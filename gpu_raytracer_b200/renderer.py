@@ -93,6 +93,19 @@ class Context:
     def unpack_tiles(self, what, stride, phase, src_device_ptr):
         self._ck(self.lib.rt_unpack_tiles(self.handle, what, stride, phase, C.c_void_p(src_device_ptr)))
 
+    def set_tile_list(self, tiles):
+        """Explicit tile assignment of this context (multi-GPU load balancing); empty / None clears it."""
+        t = np.ascontiguousarray(tiles if tiles is not None else [], np.uint32)
+        self._ck(self.lib.rt_set_tile_list(self.handle, _p(t), len(t)))
+
+    def pack_tile_list(self, what, tiles, dst_device_ptr):
+        t = np.ascontiguousarray(tiles, np.uint32)
+        self._ck(self.lib.rt_pack_tile_list(self.handle, what, _p(t), len(t), C.c_void_p(dst_device_ptr)))
+
+    def unpack_tile_list(self, what, tiles, src_device_ptr):
+        t = np.ascontiguousarray(tiles, np.uint32)
+        self._ck(self.lib.rt_unpack_tile_list(self.handle, what, _p(t), len(t), C.c_void_p(src_device_ptr)))
+
     def count_next_launch(self):
         self._ck(self.lib.rt_count_next_launch(self.handle))
 

@@ -42,8 +42,58 @@ def tile_rect(width, height, tile):
 
 
 def pixels_of_rank(width, height, world, rank):
-    return sum(tile_rect(width, height, t)[2] * tile_rect(width, height, t)[3]
-               for t in tiles_of_rank(width, height, world, rank))
+    return pixels_of_tiles(width, height, tiles_of_rank(width, height, world, rank))
+
+
+def pixels_of_tiles(width, height, tile_list):
+    return sum(tile_rect(width, height, t)[2] * tile_rect(width, height, t)[3] for t in tile_list)
+
+
+def initial_lists(width, height, world):
+    """Round-robin assignment tile i -> rank i % N as explicit lists (the starting point of `rebalance`)."""
+    return [tiles_of_rank(width, height, world, r) for r in range(world)]
+
+
+def rebalance(lists, times_ms):
+    """One load-balancing step on the previous frame's per-rank times (every rank runs it on the same
+    all-gathered numbers, so all ranks hold the same lists): tiles move one at a time from the rank with the
+    largest projected time to the one with the smallest, a tile of rank r being charged the rank's mean time per
+    tile t_r / n_r.  A rank's time has a part that does not depend on its tile count, so the mean overstates what
+    moving one tile buys: each step under-corrects and consecutive warm-up frames converge without overshoot.
+    The donor gives tiles spread over its list (not its last ones), so what it gives costs about its mean.
+    Pixels never depend on the assignment: the assembled frame stays bit-identical."""
+    lists = [list(l) for l in lists]
+    n = len(lists)
+    proj = [float(t) for t in times_ms]
+    cost = [float(t) / max(1, len(l)) for t, l in zip(times_ms, lists)]
+    given = [0] * n
+    for _ in range(sum(len(l) for l in lists)):
+        s = max(range(n), key=lambda r: (proj[r], -r))
+        d = min(range(n), key=lambda r: (proj[r], r))
+        if s == d or len(lists[s]) <= 1 or proj[d] + cost[s] >= proj[s]:
+            break
+        given[s] += 1
+        lists[d].append(lists[s].pop((given[s] * 7919) % len(lists[s])))
+        proj[s] -= cost[s]
+        proj[d] += cost[s]
+    return [sorted(l) for l in lists]
+
+
+def pack_tile_list_host(frame, tile_list, n_pad=None):
+    """numpy statement of rt_pack_tile_list."""
+    h, w = frame.shape[:2]
+    out = np.zeros((n_pad if n_pad is not None else len(tile_list), TILE, TILE) + frame.shape[2:], frame.dtype)
+    for k, t in enumerate(tile_list):
+        ox, oy, tw, th = tile_rect(w, h, t)
+        out[k, :th, :tw] = frame[oy:oy + th, ox:ox + tw]
+    return out
+
+
+def unpack_tile_list_host(frame, compact, tile_list):
+    h, w = frame.shape[:2]
+    for k, t in enumerate(tile_list):
+        ox, oy, tw, th = tile_rect(w, h, t)
+        frame[oy:oy + th, ox:ox + tw] = compact[k, :th, :tw]
 
 
 def pack_tiles_host(frame, world, rank):
@@ -67,11 +117,14 @@ class TileGather:
     """Gathers every rank's tiles to rank 0.  `pack(dst_tensor)` and
     `unpack(src_tensor, src_rank)` are the device (or, in CPU tests, numpy) copies."""
 
-    def __init__(self, dist, torch, width, height, what, device):
+    def __init__(self, dist, torch, width, height, what, device, lists=None):
+        """`lists`: explicit per-rank tile lists (rebalance); the equal-sized buffers hold the longest one."""
         self.dist, self.torch = dist, torch
         self.world, self.rank = dist.get_world_size(), dist.get_rank()
         self.width, self.height, self.what = width, height, what
-        n = tiles_per_rank_padded(width, height, self.world) * TILE * TILE * BYTES_PER_PIXEL[what]
+        self.lists = lists
+        n_pad = max(len(l) for l in lists) if lists is not None else tiles_per_rank_padded(width, height, self.world)
+        n = n_pad * TILE * TILE * BYTES_PER_PIXEL[what]
         self.bytes_per_rank = n
         self.send = torch.zeros(n, dtype=torch.uint8, device=device)
         self.recv = [torch.zeros(n, dtype=torch.uint8, device=device) for _ in range(self.world)] if self.rank == 0 else None

@@ -181,6 +181,14 @@ int rt_last_traversal(const RtContext* ctx);
  * what: 0 = composite rgba8, 1 = accumulation float4.  Asynchronous on rt_stream(). */
 int rt_pack_tiles(RtContext* ctx, uint32_t what, uint32_t stride, uint32_t phase, void* dst_device);
 int rt_unpack_tiles(RtContext* ctx, uint32_t what, uint32_t stride, uint32_t phase, const void* src_device);
+/* Explicit tile assignment (multi-GPU load balancing on the previous frame's per-rank times): the split tiles this
+ * context renders in fused frames, in the order it walks them; RtFrameParams.tile_stride / tile_phase then index
+ * positions of this list (0, 0 = all of it) and rt_pack_tiles / rt_unpack_tiles follow it.  n = 0 clears it.
+ * rt_pack_tile_list / rt_unpack_tile_list copy the tiles of ANY list (another rank's, on rank 0) between the frame
+ * and a tile-major compact device buffer [k][RT_SPLIT_TILE][RT_SPLIT_TILE].  rt_resize clears the list. */
+int rt_set_tile_list(RtContext* ctx, const uint32_t* tiles, uint32_t n);
+int rt_pack_tile_list(RtContext* ctx, uint32_t what, const uint32_t* tiles, uint32_t n, void* dst_device);
+int rt_unpack_tile_list(RtContext* ctx, uint32_t what, const uint32_t* tiles, uint32_t n, const void* src_device);
 /* Fused multi-GPU epilogue (no reference analogue): instead of pack -> NCCL gather -> unpack, the kernels of
  * ranks != 0 store their finished composite pixels straight into rank 0's frame through peer memory (P2P
  * stores over NVLink; the frame is W*H*4 bytes in total).  Rank 0 exports its composite buffer as a 64-byte

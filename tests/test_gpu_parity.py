@@ -776,3 +776,50 @@ def test_wavefront_counters_per_bounce_depth(default_ref):
     with pytest.raises(g.RtError):
         ctx.last_wavefront_counters()
     ctx.close()
+
+
+def test_explicit_tile_lists_assemble_the_frame():
+    """Multi-GPU load balancing: contexts render explicit, unequal tile lists (rt_set_tile_list); rank 0 assembles
+    them with rt_pack_tile_list / rt_unpack_tile_list and, separately, through the peer-store epilogue.  Both frames
+    must equal the single-context frame bit for bit."""
+    import torch
+    from gpu_raytracer_b200 import tiles
+    s = g.default_scene()
+    w, h, world = 1000, 600, 3
+    kw = dict(mode=abi.MODE_PATH, spp=2, max_depth=3, base_seed=4)
+    one = g.Context(0, w, h)
+    g.BufferManager(one).upload_scene(s)
+    g.ComputeRenderer(one).render_frame(s.camera, outputs=abi.OUT_ACCUM | abi.OUT_COMPOSITE, **kw)
+    want_c, want_a = one.read_composite(), one.read_accum()
+    lists = tiles.rebalance(tiles.initial_lists(w, h, world), [3.0, 1.0, 2.0])
+    assert len(set(len(l) for l in lists)) > 1 and sorted(t for l in lists for t in l) == list(range(16 * 10))
+    root, peer_root = g.Context(0, w, h), g.Context(0, w, h)
+    for r in range(world):
+        ctx = g.Context(0, w, h)
+        g.BufferManager(ctx).upload_scene(s)
+        ctx.set_tile_list(lists[r])
+        g.ComputeRenderer(ctx).render_frame(s.camera, outputs=abi.OUT_ACCUM | abi.OUT_COMPOSITE, **kw)
+        for what, bpp in ((tiles.WHAT_COMPOSITE, 4), (tiles.WHAT_ACCUM, 16)):
+            buf = torch.zeros(len(lists[r]) * tiles.TILE * tiles.TILE * bpp, dtype=torch.uint8, device="cuda")
+            ctx.pack_tiles(what, 1, 0, buf.data_ptr())  # the context's own list
+            ctx.synchronize()
+            root.unpack_tile_list(what, lists[r], buf.data_ptr())
+            root.synchronize()
+        ctx.set_peer_frame(peer_root.device_composite)
+        g.ComputeRenderer(ctx).render_frame(s.camera, outputs=abi.OUT_ACCUM | abi.OUT_COMPOSITE | abi.OUT_PEER, **kw)
+        ctx.synchronize()
+        # primary frames follow the list too
+        g.ComputeRenderer(ctx).render_frame(s.camera, outputs=abi.OUT_HITS)
+        hits = ctx.read_hits()
+        ctx.close()
+    assert np.array_equal(root.read_composite(), want_c)
+    assert np.array_equal(root.read_accum().view(np.uint32), want_a.view(np.uint32))
+    assert np.array_equal(peer_root.read_composite(), want_c)
+    with pytest.raises(g.RtError):
+        one.set_tile_list([16 * 10])  # not a tile of this frame
+    one.set_tile_list([3, 5])
+    one.resize(320, 200)  # tile numbers belong to the old size: cleared
+    g.ComputeRenderer(one).render_frame(s.camera, outputs=abi.OUT_HITS)
+    assert (one.read_hits()["kind"] != 0).any()
+    for c in (one, root, peer_root):
+        c.close()
