@@ -122,6 +122,7 @@ struct RtContext {
     uint32_t last_wave_max_depth = 0, last_wave_seed = 0;
     // streaming wavefront engine (rt_wave.cuh)
     DevBuf<float4> wv_state[2], wv_lbuf;
+    DevBuf<uint32_t> wv_fb;  // per path: queue positions handed to wv_fallback
     DevBuf<uint2> wv_hit[2];
     DevBuf<WvCtrl> wv_ctrl;
     std::vector<cudaStream_t> wv_streams; // extra streams of the sub-frames (launch_wave)
@@ -796,6 +797,7 @@ void fill_scene(RtContext* c, KParams& k) {
     k.broot_ref = c->broot_ref;
     memcpy(k.broot_min, c->broot_min, 12); memcpy(k.broot_max, c->broot_max, 12);
     k.cert_box = c->cert_box.ptr; k.rebuilt_far = c->rebuilt_far;
+    k.fallback_ordered = (c->relayout_ok && !getenv("RTB200_FALLBACK_LITERAL")) ? 1u : 0u;
     k.bqnodes = c->bqnodes.ptr; memcpy(k.bq_origin, c->bq_grid, 12); memcpy(k.bq_scale, c->bq_grid + 3, 12);
     k.accum = c->accum.ptr; k.hits = c->hits.ptr;
     for (int i = 0; i < 3; i++) k.chan[i] = c->chan[i].ptr;
@@ -937,7 +939,7 @@ int launch_wave(RtContext* c, KParams k, uint32_t traversal) {
     if (n_sub > my_tiles) n_sub = my_tiles;
     const size_t P = (size_t)k.n_work * spp_wave;
     if (c->wv_state[0].reserve(P * 4) < 0 || c->wv_state[1].reserve(P * 4) < 0 || c->wv_hit[0].reserve(P) < 0 ||
-        c->wv_hit[1].reserve(P) < 0 || c->wv_lbuf.reserve(P) < 0 || c->wv_ctrl.reserve(4) < 0)
+        c->wv_hit[1].reserve(P) < 0 || c->wv_lbuf.reserve(P) < 0 || c->wv_fb.reserve(P) < 0 || c->wv_ctrl.reserve(4) < 0)
         return fail(c, RT_ERR_CUDA, "wave engine cudaMalloc failed for %zu paths", P);
     while (c->wv_streams.size() + 1 < n_sub) {
         cudaStream_t st; cudaEvent_t ev;
@@ -959,6 +961,10 @@ int launch_wave(RtContext* c, KParams k, uint32_t traversal) {
     CK(c, cudaMemsetAsync(c->wv_ctrl.ptr, 0, 4 * sizeof(WvCtrl), c->stream));
     if (n_sub > 1) CK(c, cudaEventRecord(c->wv_fork, c->stream));
     const uint32_t s_end = k.first_sample + k.spp;
+    // which wv_shade form a depth takes (rt_wave.cuh): split when misses * 4 > rays * quarters
+    uint32_t split_gen = 1u, split_deep = 1u;
+    if (const char* e = getenv("RTB200_SPLIT_GEN")) { int v = atoi(e); if (v >= 0 && v <= 5) split_gen = (uint32_t)v; }
+    if (const char* e = getenv("RTB200_SPLIT_DEEP")) { int v = atoi(e); if (v >= 0 && v <= 5) split_deep = (uint32_t)v; }
     // per-stage timing (single sub-frame only): an event between consecutive launches (rt_last_stage_ms)
     size_t n_ev = 0;
     c->wv_event_stage.clear();
@@ -998,7 +1004,7 @@ int launch_wave(RtContext* c, KParams k, uint32_t traversal) {
         }
         w.state[0] = c->wv_state[0].ptr + path_base * 4; w.state[1] = c->wv_state[1].ptr + path_base * 4;
         w.hit[0] = c->wv_hit[0].ptr + path_base; w.hit[1] = c->wv_hit[1].ptr + path_base;
-        w.lbuf = c->wv_lbuf.ptr + path_base; w.ctrl = c->wv_ctrl.ptr + sub;
+        w.lbuf = c->wv_lbuf.ptr + path_base; w.ctrl = c->wv_ctrl.ptr + sub; w.fb_list = c->wv_fb.ptr + path_base;
         path_base += Ps;
         uint32_t ext_per_sm = (uint32_t)(per_sm > 0 ? per_sm : 1);
         if (const char* e = getenv("RTB200_EXT_BLOCKS_PER_SM")) { int v = atoi(e); if (v >= 1 && (uint32_t)v < ext_per_sm) ext_per_sm = (uint32_t)v; } // tuning
@@ -1008,6 +1014,7 @@ int launch_wave(RtContext* c, KParams k, uint32_t traversal) {
         uint32_t stream_blocks = (uint32_t)sms * 8u;
         if (const char* e = getenv("RTB200_SHADE_BLOCKS_PER_SM")) { int v = atoi(e); if (v >= 1 && v <= 16) stream_blocks = (uint32_t)sms * (uint32_t)v; } // tuning
         if (stream_blocks > full_blocks) stream_blocks = full_blocks;
+        const uint32_t fb_blocks = stream_blocks < (uint32_t)sms * 2u ? stream_blocks : (uint32_t)sms * 2u;
         for (uint32_t s0 = k.first_sample; s0 < s_end; s0 += spp_wave) {
             w.s0 = s0; w.spp_wave = s_end - s0 < spp_wave ? s_end - s0 : spp_wave;
             w.first_wave = s0 == k.first_sample; w.last_wave = s0 + w.spp_wave == s_end;
@@ -1022,13 +1029,19 @@ int launch_wave(RtContext* c, KParams k, uint32_t traversal) {
                 const int qi = (int)(d & 1u);
                 const bool gen = WV_FUSE_GEN && d == 0u; // depth 0 computes its primary rays from the queue position
                 w.depth = d;
+                w.split_quarters = gen ? split_gen : split_deep;
                 wv_extend_kernel(policy, count, gen, deep)<<<ext_blocks, 256, 0, st>>>(ks, w, qi);
                 mark(1);
                 // both forms are launched; the one that does not match the depth's miss ratio returns at once
                 wv_shade_kernel(policy, count, gen, false)<<<stream_blocks, 256, 0, st>>>(ks, w, qi);
-                wv_shade_kernel(policy, count, gen, true)<<<stream_blocks, 256, 0, st>>>(ks, w, qi);
                 mark(2);
-                c->launches += 3;
+                wv_shade_kernel(policy, count, gen, true)<<<stream_blocks, 256, 0, st>>>(ks, w, qi);
+                mark(4);
+                // the rays those left to the reference's own traversal (normally none: the kernel reads an empty list)
+                if (count) { if (gen) wv_fallback<true, true><<<fb_blocks, 256, 0, st>>>(ks, w, qi); else wv_fallback<true, false><<<fb_blocks, 256, 0, st>>>(ks, w, qi); }
+                else { if (gen) wv_fallback<false, true><<<fb_blocks, 256, 0, st>>>(ks, w, qi); else wv_fallback<false, false><<<fb_blocks, 256, 0, st>>>(ks, w, qi); }
+                mark(5);
+                c->launches += 4;
             }
             wv_resolve<<<stream_blocks, 256, 0, st>>>(ks, w);
             mark(3);
@@ -1056,7 +1069,11 @@ int launch_primary_wave(RtContext* c, KParams k, uint32_t traversal, uint32_t my
     if (my_tiles == 0) return RT_OK;
     int policy = pick_policy(c, k, traversal);
     if (policy < 1) return -100;
-    if (getenv("RTB200_PRIMARY_FUSED")) return -100; // tuning/tests: the one-kernel form (rt_trace_shade)
+    // Measured on B200 (profiles/r2b_probe_primary.log): for ONE sample per pixel the fused kernel rt_trace_shade
+    // is faster than this two-launch form (C3 scene 0.388 vs 0.420 ms, C2 0.285 vs 0.383 ms: 2 M rays leave each of
+    // the 151 552 persistent threads ~14 rays, and the hit records make a round trip through memory), so the
+    // fused kernel stays the default and this path is opt-in (tests run both).
+    if (!getenv("RTB200_PRIMARY_WAVE")) return -100;
     k.n_work = my_tiles * 4096u;
     k.spp = 1; k.first_sample = 0; k.base_seed = 0; k.path_max_depth = 0;
     k.legacy_camera = k.mode == RT_MODE_WAVEFRONT0 ? 0u : 1u;
@@ -1478,10 +1495,31 @@ int rt_last_stage_ms(RtContext* c, float out[8]) {
         if (st == 0 && i != 0) e++; // a new wave starts with its own opening event
         float ms = 0.0f;
         CK(c, cudaEventElapsedTime(&ms, c->wv_events[e], c->wv_events[e + 1]));
-        out[st] += ms; out[4 + st] += 1.0f;
+        const int bucket = st >= 4 ? 2 : st; // shade = its in-place form (2), its split form (4) and the fallback launch (5)
+        out[bucket] += ms; if (st < 4) out[4 + st] += 1.0f;
         e++;
     }
     return RT_OK;
+}
+
+// The same events one by one: GPU ms and stage (0 generate, 1 extend, 2 shade, 3 resolve) of every launch interval
+// of the last single-sub-frame wave-engine frame, in launch order.  Returns the number of intervals (<= cap written).
+int rt_last_launch_table(RtContext* c, float* ms, int32_t* stage, uint32_t cap) {
+    if (!c || !ms || !stage) return RT_ERR_INVALID_ARGUMENT;
+    if (!c->last_was_wavefront || c->wv_event_stage.empty()) return fail(c, RT_ERR_NOT_READY, "the last launch was not a single-sub-frame wave-engine frame");
+    CK(c, cudaSetDevice(c->device));
+    CK(c, cudaStreamSynchronize(c->stream));
+    size_t e = 0;
+    uint32_t n = 0;
+    for (size_t i = 0; i < c->wv_event_stage.size(); i++) {
+        int st = c->wv_event_stage[i];
+        if (st == 0 && i != 0) e++;
+        float t = 0.0f;
+        CK(c, cudaEventElapsedTime(&t, c->wv_events[e], c->wv_events[e + 1]));
+        if (n < cap) { ms[n] = t; stage[n] = st; }
+        n++; e++;
+    }
+    return (int)n;
 }
 
 // Measured gather bandwidth (GB/s) for random independent 32-byte sector loads over a

@@ -83,6 +83,7 @@ struct KParams {
     unsigned long long* counters;
     // RT_MODE_PATH (EXTENSION, SPEC.md)
     uint32_t spp, first_sample, path_max_depth, base_seed;
+    uint32_t fallback_ordered;       // wv_fallback: 1 = pruned ORDERED search over wnodes / wtris, 0 = the literal walk
     uint32_t legacy_camera;          // wave engine primary frames: 1 = Ray::from_screen_coordinates (legacy), 0 = wavefront camera ray
     uint32_t n_work;                 // pixels in this launch's work list (4096 per assigned split tile)
     unsigned int* work_counter;      // persistent-thread work fetch
@@ -314,6 +315,82 @@ __device__ void closest_triangle_literal(const KParams& p, const Ray& ray, float
     }
 }
 
+// The same search by a whole warp for ONE ray (every lane passes the same ray): the walk over the nodes is
+// uniform, the triangles of a leaf (or of the brute-force loop) are dealt to the lanes, and the result is the
+// minimum of (t, position in the reference's visit order) over all accepted triangles, which is exactly what the
+// sequential strict `t < closest` scan returns (the first triangle in visit order that attains the minimum).
+// Used by wv_fallback for the rare rays of the wave engine whose REBUILT winner fails certification (or that the
+// internal tree cannot serve): alone on one lane such a ray takes ~0.25 ms on 100-triangle leaves.
+// Must be called by all 32 lanes of a converged warp; every lane returns the same result.
+__device__ __noinline__ void closest_triangle_literal_warp(const KParams& p, const Ray& ray, float max_t, TriBest& b) {
+    const unsigned full = 0xFFFFFFFFu;
+    const uint32_t lane = threadIdx.x & 31u;
+    TriBest m;
+    m.t = max_t; m.hit = false; m.prim = 0xFFFFFFFFu; m.mat = 0xFFFFFFFFu; m.n_box = 0; m.n_tri = 0; m.n_fallback = 0;
+    m.v0 = mk(0, 0, 0); m.e1 = mk(0, 0, 0); m.e2 = mk(0, 0, 0);
+    uint32_t my_seq = 0xFFFFFFFFu, seq = 0u;
+    auto test = [&](uint32_t tri_index, uint32_t s) {
+        V3 v0, v1, v2;
+        uint32_t mat;
+        if (!fetch_triangle_ref(p, tri_index, &v0, &v1, &v2, &mat)) return;
+        m.n_tri++;
+        V3 e1 = v1 - v0, e2 = v2 - v0;
+        float t = triangle_t(ray, v0, e1, e2);
+        if (t > 0.0f && t < m.t) { // a lane sees its triangles in visit order: strict less keeps the first
+            m.t = t; m.prim = tri_index; m.mat = mat; m.v0 = v0; m.e1 = e1; m.e2 = e2; m.hit = true; my_seq = s;
+        }
+    };
+    const uint32_t node_count = p.off.bvh_nodes_count;
+    if (node_count == 0u) {
+        for (uint32_t i = lane; i < p.triangle_count; i += 32u) test(i, i);
+    } else {
+        V3 inv = mk(1.0f / ray.d.x, 1.0f / ray.d.y, 1.0f / ray.d.z);
+        uint32_t stack[64];
+        int sp = 0;
+        stack[sp++] = 0u;
+        while (sp > 0) {
+            uint32_t n = stack[--sp];
+            if (n == 0xFFFFFFFFu || n >= node_count) continue;
+            uint64_t no = (uint64_t)p.off.bvh_nodes_offset + (uint64_t)n * 12;
+            V3 bmin = mk(meta_f(p, no), meta_f(p, no + 1), meta_f(p, no + 2));
+            V3 bmax = mk(meta_f(p, no + 4), meta_f(p, no + 5), meta_f(p, no + 6));
+            float entry;
+            m.n_box++;
+            if (!slab(ray.o, inv, bmin, bmax, &entry)) continue;
+            uint32_t left = meta_at(p, no + 8), right = meta_at(p, no + 9);
+            if (left == 0xFFFFFFFFu) {
+                uint32_t start = meta_at(p, no + 10), count = meta_at(p, no + 11);
+                for (uint32_t i = lane; i < count; i += 32u) {
+                    if (start + i >= p.off.triangle_indices_count) break;
+                    test(meta_at(p, (uint64_t)p.off.triangle_indices_offset + start + i), seq + i);
+                }
+                seq += count;
+            } else {
+                if (right != 0xFFFFFFFFu && sp < 63) stack[sp++] = right;
+                if (left != 0xFFFFFFFFu && sp < 63) stack[sp++] = left;
+            }
+        }
+    }
+    float bt = m.t;
+    uint32_t bs = my_seq, nt = m.n_tri;
+    for (int o = 16; o; o >>= 1) {
+        float ot = __shfl_xor_sync(full, bt, o);
+        uint32_t os = __shfl_xor_sync(full, bs, o);
+        nt += __shfl_xor_sync(full, nt, o);
+        if (ot < bt || (ot == bt && os < bs)) { bt = ot; bs = os; }
+    }
+    const unsigned wm = __ballot_sync(full, m.hit && my_seq == bs);
+    b.t = max_t; b.hit = false; b.prim = 0xFFFFFFFFu; b.mat = 0xFFFFFFFFu; b.n_box = m.n_box; b.n_tri = nt;
+    if (wm) {
+        const int src = __ffs(wm) - 1;
+        b.hit = true;
+        b.t = __shfl_sync(full, m.t, src); b.prim = __shfl_sync(full, m.prim, src); b.mat = __shfl_sync(full, m.mat, src);
+        b.v0 = mk(__shfl_sync(full, m.v0.x, src), __shfl_sync(full, m.v0.y, src), __shfl_sync(full, m.v0.z, src));
+        b.e1 = mk(__shfl_sync(full, m.e1.x, src), __shfl_sync(full, m.e1.y, src), __shfl_sync(full, m.e1.z, src));
+        b.e2 = mk(__shfl_sync(full, m.e2.x, src), __shfl_sync(full, m.e2.y, src), __shfl_sync(full, m.e2.z, src));
+    }
+}
+
 // ------------------------------------------------- ORDERED closest-hit policy
 // Wide node i = 4 x float4:
 //   q0 = (L.min.x, L.min.y, L.min.z, L.max.x)   q1 = (L.max.y, L.max.z, R.min.x, R.min.y)
@@ -388,6 +465,81 @@ __device__ void closest_triangle_ordered(const KParams& p, const Ray& ray, float
     }
 }
 
+// The ORDERED search by a whole warp for ONE ray (every lane passes the same ray; all 32 lanes of a converged warp
+// must call it; every lane returns the same result): the near-first, t-pruned walk is uniform, the triangles of a
+// leaf are dealt to the lanes and folded with a warp-wide minimum of (t, position).  The ORDERED policy returns the
+// reference's (= the LITERAL policy's) hit for every ray on a validated upload, so wv_fallback uses this for the
+// rays the internal tree cannot serve: pruned, it visits a few dozen nodes where the un-pruned literal walk of a
+// grazing ray visits a thousand (measured: 0.25-0.4 ms for ONE such ray, on one lane or on a warp alike).
+__device__ __forceinline__ void closest_triangle_ordered_warp(const KParams& p, const Ray& ray, float max_t, TriBest& b) {
+    const unsigned full = 0xFFFFFFFFu;
+    const uint32_t lane = threadIdx.x & 31u;
+    b.t = max_t; b.hit = false; b.prim = 0xFFFFFFFFu; b.mat = 0xFFFFFFFFu; b.n_box = 1; b.n_tri = 0; b.n_fallback = 0;
+    b.v0 = mk(0, 0, 0); b.e1 = mk(0, 0, 0); b.e2 = mk(0, 0, 0);
+    uint32_t best_pos = 0u, n_tri = 0u;
+    uint32_t cur = p.root_ref;
+    if (cur == RT_CHILD_ABSENT) return;
+    V3 inv = mk(1.0f / ray.d.x, 1.0f / ray.d.y, 1.0f / ray.d.z);
+    {
+        float entry;
+        if (!slab(ray.o, inv, mka(p.root_min), mka(p.root_max), &entry)) return;
+    }
+    uint32_t stack[64];
+    int sp = 0;
+    const uint32_t DONE = 0xFFFFFFFFu;
+    for (;;) {
+        while (!(cur & RT_LEAF_FLAG)) { // uniform: the same node step as closest_triangle_ordered
+            const float4* np = p.wnodes + (uint64_t)cur * 4;
+            float4 q0, q1, q2, q3;
+            ldg_node(np, q0, q1, q2, q3);
+            uint32_t lref = __float_as_uint(q3.x), rref = __float_as_uint(q3.y);
+            float el, er;
+            b.n_box += 2;
+            bool hl = slab(ray.o, inv, mk(q0.x, q0.y, q0.z), mk(q0.w, q1.x, q1.y), &el);
+            bool hr = slab(ray.o, inv, mk(q1.z, q1.w, q2.x), mk(q2.y, q2.z, q2.w), &er);
+            float limit = b.t * RT_PRUNE_SCALE + RT_PRUNE_ABS;
+            hl = hl && (lref != RT_CHILD_ABSENT) && (el <= limit);
+            hr = hr && (rref != RT_CHILD_ABSENT) && (er <= limit);
+            if (hl && hr) {
+                bool right_first = er < el;
+                stack[sp++] = right_first ? lref : rref;
+                cur = right_first ? rref : lref;
+            } else if (hl) cur = lref;
+            else if (hr) cur = rref;
+            else cur = sp ? stack[--sp] : DONE;
+        }
+        if (cur == DONE) break;
+        const uint32_t start = cur & ~RT_LEAF_FLAG;
+        const uint32_t cnt = __float_as_uint(__ldg(p.wtris + (uint64_t)start * 3 + 2).w); // `remaining` of the first record
+        float mt = 0.0f;
+        uint32_t mpos = 0xFFFFFFFFu; // this lane's best of the leaf: valid iff mpos != ~0
+        for (uint32_t i = lane; i < cnt; i += 32u) {
+            const uint32_t pos = start + i;
+            const float4* tp = p.wtris + (uint64_t)pos * 3;
+            float4 a = __ldg(tp), c = __ldg(tp + 1), d = __ldg(tp + 2);
+            float t = triangle_t(ray, mk(a.x, a.y, a.z), mk(a.w, c.x, c.y), mk(c.z, c.w, d.x));
+            n_tri++;
+            if (t > 0.0f && (mpos == 0xFFFFFFFFu || t < mt)) { mt = t; mpos = pos; } // increasing pos per lane: strict less keeps the smaller
+        }
+        for (int o = 16; o; o >>= 1) {
+            float ot = __shfl_xor_sync(full, mt, o);
+            uint32_t op = __shfl_xor_sync(full, mpos, o);
+            if (op != 0xFFFFFFFFu && (mpos == 0xFFFFFFFFu || ot < mt || (ot == mt && op < mpos))) { mt = ot; mpos = op; }
+        }
+        // the same acceptance rule as ordered_leaf: strictly closer, or equally close at a smaller position
+        if (mpos != 0xFFFFFFFFu && (mt < b.t || (mt == b.t && b.hit && mpos < best_pos))) { b.t = mt; b.hit = true; best_pos = mpos; }
+        cur = sp ? stack[--sp] : DONE;
+    }
+    for (int o = 16; o; o >>= 1) n_tri += __shfl_xor_sync(full, n_tri, o);
+    b.n_tri = n_tri;
+    if (b.hit) {
+        const float4* tp = p.wtris + (uint64_t)best_pos * 3;
+        float4 a = __ldg(tp), c = __ldg(tp + 1), d = __ldg(tp + 2);
+        b.v0 = mk(a.x, a.y, a.z); b.e1 = mk(a.w, c.x, c.y); b.e2 = mk(c.z, c.w, d.x);
+        b.mat = __float_as_uint(d.y); b.prim = __float_as_uint(d.z);
+    }
+}
+
 // ------------------------------------------------- REBUILT closest-hit policy
 // Traverses the internal LBVH (conservatively inflated boxes, leaves of <= 4
 // triangles), then certifies the winner W against the reference traversal:
@@ -400,14 +552,26 @@ __device__ void closest_triangle_ordered(const KParams& p, const Ray& ray, float
 //   * upload validated that every ancestor box contains the leaf box component-wise;
 //     (b - o) * inv is monotone in b under IEEE rounding, so for rays without zero
 //     direction components "leaf box passes" implies "every ancestor passes".
-// Hence one exact slab test on W's uploaded leaf box certifies W.  Rays that fail it
-// (or have a zero direction component) re-run the literal policy.
-__device__ void closest_triangle_rebuilt(const KParams& p, const Ray& ray, float max_t, TriBest& b) {
+// Hence one exact slab test on W's uploaded leaf box certifies W.  Rays with a zero direction
+// component (or a far origin) take the literal policy.  A ray whose winner fails the test is
+// searched again with FILTER = true: a triangle is then only accepted if its own uploaded leaf
+// box passes the exact slab test, i.e. (same monotonicity argument) if the reference traversal
+// tests it; the minimum over exactly those triangles IS the reference result, found at the
+// internal tree's speed instead of the un-pruned literal walk's (0.25-0.4 ms for one grazing ray
+// on the terrain's 100-triangle leaves).
+__device__ __forceinline__ bool rebuilt_leaf_certified(const KParams& p, const Ray& ray, V3 inv, uint32_t pos) {
+    const uint32_t leaf = __ldg(p.leaf_of_pos + pos);
+    const float4 blo = __ldg(p.cert_box + (uint64_t)leaf * 2), bhi = __ldg(p.cert_box + (uint64_t)leaf * 2 + 1);
+    float entry;
+    return slab(ray.o, inv, mk(blo.x, blo.y, blo.z), mk(bhi.x, bhi.y, bhi.z), &entry);
+}
+template <bool FILTER>
+__device__ __forceinline__ void closest_triangle_rebuilt_t(const KParams& p, const Ray& ray, float max_t, TriBest& b) {
     // zero (or so tiny that o/d overflows) direction components: certification argument and the
     // FMA slab do not apply -> literal policy
     // origins far outside the scene: the rounding of the exact tests outgrows the boxes' pad (rt_lbvh.cuh)
-    if (!(fabsf(ray.d.x) >= 1e-30f && fabsf(ray.d.y) >= 1e-30f && fabsf(ray.d.z) >= 1e-30f) ||
-        !(fmaxf(fmaxf(fabsf(ray.o.x), fabsf(ray.o.y)), fabsf(ray.o.z)) <= p.rebuilt_far)) { closest_triangle_literal(p, ray, max_t, b); b.n_fallback = 1; return; }
+    if (!FILTER && (!(fabsf(ray.d.x) >= 1e-30f && fabsf(ray.d.y) >= 1e-30f && fabsf(ray.d.z) >= 1e-30f) ||
+        !(fmaxf(fmaxf(fabsf(ray.o.x), fabsf(ray.o.y)), fabsf(ray.o.z)) <= p.rebuilt_far))) { closest_triangle_literal(p, ray, max_t, b); b.n_fallback = 1; return; }
     b.t = max_t; b.hit = false; b.prim = 0xFFFFFFFFu; b.mat = 0xFFFFFFFFu; b.n_box = 1; b.n_tri = 0;
     uint32_t best_pos = 0u;
     uint32_t cur = p.broot_ref;
@@ -435,7 +599,8 @@ __device__ void closest_triangle_rebuilt(const KParams& p, const Ray& ray, float
                 float t = triangle_t(ray, v0, e1, e2);
                 b.n_tri++;
                 uint32_t pos = __float_as_uint(d.w);
-                if (t > 0.0f && (t < b.t || (t == b.t && b.hit && pos < best_pos))) {
+                if (t > 0.0f && (t < b.t || (t == b.t && b.hit && pos < best_pos)) &&
+                    (!FILTER || rebuilt_leaf_certified(p, ray, inv, pos))) {
                     b.t = t; b.hit = true; best_pos = pos;
                     b.mat = __float_as_uint(d.y); b.prim = __float_as_uint(d.z);
                     b.v0 = v0; b.e1 = e1; b.e2 = e2;
@@ -464,18 +629,20 @@ __device__ void closest_triangle_rebuilt(const KParams& p, const Ray& ray, float
         if (sp == 0) break;
         cur = stack[--sp];
     }
-    if (b.hit) {
-        uint32_t leaf = __ldg(p.leaf_of_pos + best_pos);
-        uint64_t no = (uint64_t)p.off.bvh_nodes_offset + (uint64_t)leaf * 12;
-        float entry;
+    if (!FILTER && b.hit) {
         b.n_box++;
-        bool ok = slab(ray.o, inv, mk(meta_f(p, no), meta_f(p, no + 1), meta_f(p, no + 2)),
-                       mk(meta_f(p, no + 4), meta_f(p, no + 5), meta_f(p, no + 6)), &entry);
-        if (!ok) {
-            uint32_t nb = b.n_box, nt = b.n_tri;
-            closest_triangle_literal(p, ray, max_t, b);
-            b.n_box += nb; b.n_tri += nt; b.n_fallback = 1;
-        }
+        if (!rebuilt_leaf_certified(p, ray, inv, best_pos)) b.n_fallback = 2; // the caller searches again with the filter
+    }
+}
+// (ptxas 12.9 crashes when the filtered search or closest_triangle_ordered_warp are emitted as out-of-line functions:
+// both are inlined into wv_fallback, their only caller; the per-lane megakernels keep the literal walk for the
+// rare failures so that their code does not grow.)
+__device__ void closest_triangle_rebuilt(const KParams& p, const Ray& ray, float max_t, TriBest& b) {
+    closest_triangle_rebuilt_t<false>(p, ray, max_t, b);
+    if (b.n_fallback == 2u) {
+        uint32_t nb = b.n_box, nt = b.n_tri;
+        closest_triangle_literal(p, ray, max_t, b);
+        b.n_box += nb; b.n_tri += nt; b.n_fallback = 1;
     }
 }
 

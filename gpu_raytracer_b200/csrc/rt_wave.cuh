@@ -30,6 +30,8 @@ struct WvCtrl {
     unsigned long long c[4];    // instrumentation: box tests, triangle tests, shaded hits, literal fallbacks
     unsigned int misses[2];     // rays of the current / next depth that hit nothing (picks wv_shade's form)
     unsigned int _pad2[2];
+    unsigned int n_fb;          // paths of the current depth handed to wv_fallback (the reference's own traversal)
+    unsigned int _pad3[3];
     unsigned int rays_at_depth[8]; // ray segments traced per bounce depth (depths >= 7 share the last entry): the
                                    // reference's WavefrontCounters.rays_per_bounce (shared/src/lib.rs:187-194)
 };
@@ -38,12 +40,14 @@ struct WvBuffers {
     float4* state[2];  // 4 x float4 per path: (o, rng) (d, depth) (throughput, work idx) (L, local sample)
     uint2* hit[2];     // per path: (t bits, id); in: sphere seed, out: closest hit
     float4* lbuf;      // [local sample][work idx]: finished sample radiance
+    uint32_t* fb_list; // queue positions of the current depth that wv_shade left to wv_fallback
     WvCtrl* ctrl;
     uint32_t s0, spp_wave; // samples [s0, s0 + spp_wave) are in this wave
     uint32_t last_wave;    // resolve writes the composite
     uint32_t first_wave;   // resolve honours reset_accum
     uint32_t valid_pixels; // work items of this sub-frame that lie inside the image (fused generation: segment count of depth 0)
     uint32_t depth;        // bounce depth of this launch (bookkeeping only: rays_at_depth)
+    uint32_t split_quarters; // wv_shade takes its split form when misses * 4 > rays * split_quarters (>= 5: never)
 };
 
 // hit id encoding
@@ -192,7 +196,7 @@ __global__ void __launch_bounds__(256, WV_BLOCKS) wv_extend(const __grid_constan
     const uint32_t n = GEN ? p.n_work * w.spp_wave : w.ctrl->n[qi];
     const float4* __restrict__ state = w.state[qi];
     uint2* __restrict__ hit = w.hit[qi];
-    if (blockIdx.x == 0 && tid == 0) { w.ctrl->n[qi ^ 1] = 0; w.ctrl->misses[qi ^ 1] = 0; } // wv_shade of this depth appends there
+    if (blockIdx.x == 0 && tid == 0) { w.ctrl->n[qi ^ 1] = 0; w.ctrl->misses[qi ^ 1] = 0; w.ctrl->n_fb = 0; } // wv_shade of this depth appends there
     uint32_t n_miss = 0;
 #if WV_L2_KEEP
     const unsigned long long keep = l2_keep_policy();
@@ -433,6 +437,106 @@ __global__ void __launch_bounds__(256, WV_BLOCKS) wv_extend(const __grid_constan
     }
 }
 
+
+// Second half of shading one path of the current depth, given its closest hit: primary-hit record, SPEC.md steps
+// 3.2-3.8 (path_bounce) and 4; survivors become the compact path list of the next depth (warp-aggregated append,
+// order within the warp kept).  Called by all 32 lanes of a converged warp; `have` marks the lanes holding a path.
+template <bool COUNT>
+__device__ __forceinline__ void wv_finish_path(const KParams& p, const WvBuffers& w, int qi, bool have, const Hit& h, Ray& ray,
+                                               V3& tp, V3& L, SimpleRng& rng, uint32_t& depth, uint32_t idx, uint32_t sl) {
+    const unsigned full = 0xFFFFFFFFu;
+    const uint32_t lane = threadIdx.x & 31u;
+    bool cont = false;
+    if (have) {
+        if (COUNT && h.kind != 0u) atomicAdd(&w.ctrl->c[2], 1ull);
+        if (depth == 0u && w.s0 + sl == 0u && (p.outputs & RT_OUT_HITS)) {
+            uint32_t px, py;
+            work_to_pixel(p, idx, &px, &py);
+            reinterpret_cast<uint4*>(p.hits)[(size_t)py * p.width + px] = make_uint4(h.kind, h.prim, __float_as_uint(h.t), h.material_id);
+        }
+        const bool end = path_bounce(p, h, ray, tp, L, rng, depth); // SPEC.md steps 3.2-3.8 (rt_kernels.cuh)
+        cont = !end;
+        if (end) WV_ST(w.lbuf + (size_t)sl * p.n_work + idx, make_float4(L.x, L.y, L.z, 1.0f)); // SPEC.md step 4, summed by wv_resolve
+    }
+    unsigned m = __ballot_sync(full, cont);
+    if (m) {
+        uint32_t base = 0;
+        int leader = __ffs(m) - 1;
+        if ((int)lane == leader) base = atomicAdd(&w.ctrl->n[qi ^ 1], (unsigned int)__popc(m));
+        base = __shfl_sync(full, base, leader);
+        if (cont) {
+            uint32_t ns = base + __popc(m & ((1u << lane) - 1u));
+            float4* st = w.state[qi ^ 1] + (size_t)ns * 4;
+            WV_ST(st, make_float4(ray.o.x, ray.o.y, ray.o.z, __uint_as_float(rng.seed)));
+            WV_ST(st + 1, make_float4(ray.d.x, ray.d.y, ray.d.z, __uint_as_float(depth)));
+            WV_ST(st + 2, make_float4(tp.x, tp.y, tp.z, __uint_as_float(idx)));
+            WV_ST(st + 3, make_float4(L.x, L.y, L.z, __uint_as_float(sl)));
+            WV_ST(w.hit[qi ^ 1] + ns, wv_seed_record(p, ray));
+        }
+    }
+}
+
+// ---- fallback: the paths of the current depth that wv_shade could not serve from the re-laid-out scene (REBUILT
+// winner failed its certification; zero / tiny direction component; origin far outside the scene) get the
+// reference's result here, one warp per ray (closest_triangle_ordered_warp / _literal_warp), then the same second half of
+// the shading.  Launched after the shade launches of every depth; normally the list is empty (C3: 5 of 70 M
+// segments).  Kept out of wv_shade because (a) one such ray on one lane takes ~0.25 ms on 100-triangle leaves and
+// holds a small launch (a 1/8 frame share) up for that long, and (b) the literal traversal's registers and
+// 256-byte stack slowed every shade launch by ~13 % when it was inlined there.
+template <bool COUNT, bool GEN>
+__global__ void __launch_bounds__(256) wv_fallback(const __grid_constant__ KParams p, WvBuffers w, int qi) {
+    const unsigned full = 0xFFFFFFFFu;
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t n_fb = w.ctrl->n_fb;
+    const uint32_t warps = gridDim.x * 8u;
+    for (uint32_t j = blockIdx.x * 8u + (threadIdx.x >> 5); j < n_fb; j += warps) {
+        const uint32_t entry = w.fb_list[j], i = entry & 0x7FFFFFFFu;
+        const bool filtered = (entry & 0x80000000u) != 0u; // uniform over the warp
+        // every lane holds the same path (uniform loads)
+        Ray ray; ray.o = mk(0, 0, 0); ray.d = mk(0, 0, 1);
+        V3 tp = mk(1.0f, 1.0f, 1.0f), L = mk(0, 0, 0);
+        SimpleRng rng; rng.seed = 0;
+        uint32_t depth = 0, idx = 0, sl = 0;
+        if (GEN) wv_primary(p, w, i, &idx, &sl, &ray, &rng.seed);
+        else {
+            const float4* st = w.state[qi] + (size_t)i * 4;
+            float4 s0 = __ldcs(st), s1 = __ldcs(st + 1), s2 = __ldcs(st + 2), s3 = __ldcs(st + 3);
+            ray.o = mk(s0.x, s0.y, s0.z); ray.d = mk(s1.x, s1.y, s1.z);
+            rng.seed = __float_as_uint(s0.w);
+            depth = __float_as_uint(s1.w); idx = __float_as_uint(s2.w); sl = __float_as_uint(s3.w);
+            tp = mk(s2.x, s2.y, s2.z); L = mk(s3.x, s3.y, s3.z);
+        }
+        float sphere_seed; uint32_t sphere_idx;
+        wv_sphere_seed(p, ray, &sphere_seed, &sphere_idx); // lib.rs:183-190: spheres first, then triangles seeded with it
+        TriBest b;
+        // the ORDERED policy over the uploaded tree returns the reference's hit for every ray (pinned to the
+        // oracle and to LITERAL by the parity suite) and prunes; without a usable re-layout, the literal walk
+        // a winner that failed certification: search the internal tree again, accepting only triangles whose own
+        // uploaded leaf box passes the exact slab test (closest_triangle_rebuilt_t<true>: that minimum is the reference
+        // result); all lanes run it on the same ray
+        if (filtered) closest_triangle_rebuilt_t<true>(p, ray, sphere_seed, b);
+        else if (p.fallback_ordered) closest_triangle_ordered_warp(p, ray, sphere_seed, b);
+        else closest_triangle_literal_warp(p, ray, sphere_seed, b);
+        Hit h;
+        h.t = FLT_MAX; h.kind = 0u; h.prim = 0xFFFFFFFFu; h.material_id = 0xFFFFFFFFu;
+        h.point = mk(0, 0, 0); h.normal = mk(0, 0, 0);
+        if (b.hit) {
+            h.t = b.t; h.kind = 2u; h.prim = b.prim; h.material_id = b.mat;
+            h.point = ray.o + ray.d * b.t;
+            h.normal = normalize3(cross3(b.e1, b.e2));
+        } else if (sphere_idx != WV_NO_SPHERE) {
+            uint64_t o = (uint64_t)p.off.spheres_offset + (uint64_t)sphere_idx * 5;
+            V3 c = mk(meta_f(p, o), meta_f(p, o + 1), meta_f(p, o + 2));
+            h.t = sphere_seed; h.kind = 1u; h.prim = sphere_idx; h.material_id = meta_at(p, o + 4);
+            h.point = ray.o + ray.d * sphere_seed;
+            h.normal = normalize3(h.point - c);
+        }
+        if (COUNT && lane == 0u) { atomicAdd(&w.ctrl->c[3], 1ull); atomicAdd(&w.ctrl->c[0], (unsigned long long)b.n_box); atomicAdd(&w.ctrl->c[1], (unsigned long long)b.n_tri); }
+        wv_finish_path<COUNT>(p, w, qi, lane == 0u, h, ray, tp, L, rng, depth, idx, sl);
+    }
+    (void)full;
+}
+
 // ---- shade: SPEC.md steps 3.2-3.8 and 4 for every path of the current depth ----------------
 // Both forms (SPLIT = false / true) are launched for every depth; each looks at the miss count wv_extend left in
 // ctrl->misses[qi] and only the matching one runs (the other returns at once): the split form when more than a
@@ -450,7 +554,7 @@ __global__ void __launch_bounds__(256, WV_SHADE_BLOCKS) wv_shade(const __grid_co
         w.ctrl->segments += traced;
         w.ctrl->rays_at_depth[w.depth < 7u ? w.depth : 7u] += (unsigned int)traced;
     }
-    if (((unsigned long long)w.ctrl->misses[qi] * 4ull > (unsigned long long)n) != SPLIT) return;
+    if (((unsigned long long)w.ctrl->misses[qi] * 4ull > (unsigned long long)n * w.split_quarters) != SPLIT) return;
     // Paths whose ray left the scene (on open scenes most of depth >= 1) only add the sky term; if they shared
     // warps with the hits, the shading code would run with a handful of lanes (ncu: 7 of 32 at depth 1 of C3).
     // Every warp owns a small queue in shared memory: phase A of each 32-path chunk finishes the misses and queues
@@ -573,11 +677,11 @@ __global__ void __launch_bounds__(256, WV_SHADE_BLOCKS) wv_shade(const __grid_co
             float sphere_seed = FLT_MAX - 2.0f;
             uint32_t sphere_idx = WV_NO_SPHERE;
             if (hr.y != WV_ID_MISS && kind == WV_KIND_SPHERE) { sphere_seed = __uint_as_float(hr.x); sphere_idx = hr.y & WV_NO_SPHERE; }
-            if (lit) { // rare: the reference's own traversal for this ray
-                wv_sphere_seed(p, ray, &sphere_seed, &sphere_idx);
-                closest_triangle_literal(p, ray, sphere_seed, b);
-                if (COUNT) { atomicAdd(&w.ctrl->c[3], 1ull); atomicAdd(&w.ctrl->c[0], (unsigned long long)b.n_box); atomicAdd(&w.ctrl->c[1], (unsigned long long)b.n_tri); }
-            }
+            if (lit) { // rare: the internal tree's answer does not stand for this ray -> wv_fallback (launched after this kernel)
+                // bit 31: the ray went through the internal tree and its winner failed certification (filtered re-search);
+                // clear: the tree could not be used at all (zero / tiny direction component, far origin)
+                w.fb_list[atomicAdd(&w.ctrl->n_fb, 1u)] = i | ((hr.y != WV_ID_MISS && kind == WV_KIND_TRI) ? 0x80000000u : 0u);
+            } else {
             if (b.hit) {
                 h.t = b.t; h.kind = 2u; h.prim = b.prim; h.material_id = b.mat;
                 h.point = ray.o + ray.d * b.t;
@@ -598,8 +702,10 @@ __global__ void __launch_bounds__(256, WV_SHADE_BLOCKS) wv_shade(const __grid_co
             const bool end = path_bounce(p, h, ray, tp, L, rng, depth); // SPEC.md steps 3.2-3.8 (rt_kernels.cuh)
             cont = !end;
             if (end) WV_ST(w.lbuf + (size_t)sl * p.n_work + idx, make_float4(L.x, L.y, L.z, 1.0f)); // SPEC.md step 4, summed by wv_resolve
+            } // !lit
         }
-        // ---- survivors become the compact path list of the next depth (order within the warp kept)
+        // ---- survivors become the compact path list of the next depth (order within the warp kept; the same
+        // append as wv_finish_path, which wv_fallback uses for the rays it serves)
         unsigned m = __ballot_sync(full, cont);
         if (m) {
             uint32_t base = 0;

@@ -16,7 +16,7 @@ API_SYMBOLS = [
     "rt_get_metadata_offsets", "rt_dispatch", "rt_run_compute", "rt_render_frame", "rt_read_channel_rgba8",
     "rt_read_composite_rgba8", "rt_read_accum_f32", "rt_write_accum_f32", "rt_read_hit_records", "rt_device_accum",
     "rt_device_composite", "rt_count_next_launch", "rt_read_counters", "rt_last_kernel_ms", "rt_launch_count",
-    "rt_last_traversal", "rt_last_build_ms", "rt_last_segments", "rt_last_wavefront_counters", "rt_last_stage_ms", "rt_probe_gather_bandwidth",
+    "rt_last_traversal", "rt_last_build_ms", "rt_last_segments", "rt_last_wavefront_counters", "rt_last_stage_ms", "rt_last_launch_table", "rt_probe_gather_bandwidth",
     "rt_export_frame_handle", "rt_open_peer_frame", "rt_set_peer_frame", "rt_close_peer_frame", "rt_pack_tiles",
     "rt_unpack_tiles", "rt_set_tile_list", "rt_pack_tile_list", "rt_unpack_tile_list",
     "rt_stream"]
@@ -62,7 +62,7 @@ def load():
         "rt_read_hit_records": (i32, [vp, vp]), "rt_device_accum": (vp, [vp]), "rt_device_composite": (vp, [vp]),
         "rt_last_kernel_ms": (f32, [vp]), "rt_count_next_launch": (i32, [vp]), "rt_read_counters": (i32, [vp, vp]),
         "rt_launch_count": (u64, [vp]), "rt_last_traversal": (i32, [vp]), "rt_last_build_ms": (f32, [vp]),
-        "rt_last_segments": (i32, [vp, vp]), "rt_last_wavefront_counters": (i32, [vp, vp]), "rt_last_stage_ms": (i32, [vp, vp]),
+        "rt_last_segments": (i32, [vp, vp]), "rt_last_wavefront_counters": (i32, [vp, vp]), "rt_last_stage_ms": (i32, [vp, vp]), "rt_last_launch_table": (i32, [vp, vp, vp, u32]),
         "rt_probe_gather_bandwidth": (i32, [vp, u64, vp]), "rt_export_frame_handle": (i32, [vp, vp]),
         "rt_open_peer_frame": (i32, [vp, vp]), "rt_set_peer_frame": (i32, [vp, vp]),
         "rt_close_peer_frame": (i32, [vp]), "rt_pack_tiles": (i32, [vp, u32, u32, u32, vp]),

@@ -149,6 +149,13 @@ class Context:
         return dict(generate=float(out[0]), extend=float(out[1]), shade=float(out[2]), resolve=float(out[3]),
                     launches=[int(x) for x in out[4:8]])
 
+    def last_launch_table(self):
+        """[(stage name, ms)] of every launch interval of the last single-sub-frame wave-engine frame."""
+        ms, st = np.zeros(256, np.float32), np.zeros(256, np.int32)
+        n = self._ck(self.lib.rt_last_launch_table(self.handle, _p(ms), _p(st), 256))
+        names = ("generate", "extend", "shade", "resolve", "shade-split", "fallback")
+        return [(names[int(st[i])], float(ms[i])) for i in range(min(n, 256))]
+
     @property
     def last_kernel_ms(self):
         return float(self.lib.rt_last_kernel_ms(self.handle))

@@ -88,6 +88,8 @@ typedef struct RtFrameParams {
  *   RTB200_WAVE_SPLIT=1..4  sub-frames of the streaming wavefront engine (default 2; 1 enables rt_last_stage_ms)
  *   RTB200_WAVE_PATHS=N     paths in flight per wave (default 40 M)
  *   RTB200_WAVE_DEEP=1      force the traversal-stack form used for trees deeper than 30 levels
+ *   RTB200_PRIMARY_WAVE=1   primary frames through wv_extend + wv_shade_primary instead of the fused rt_trace_shade
+ *   RTB200_EXT_BLOCKS_PER_SM, RTB200_SHADE_BLOCKS_PER_SM, RTB200_SPLIT_GEN, RTB200_SPLIT_DEEP   launch-shape tuning
  *   RTB200_DEBUG=1          print the internal tree's size and depth at upload */
 
 /* ---- context: stands in for RenderState.device/queue + the three output
@@ -217,6 +219,10 @@ float rt_last_build_ms(const RtContext* ctx);
  * out[4..7] the number of launches of each stage.  RT_ERR_NOT_READY if the last frame used
  * another engine. */
 int rt_last_stage_ms(RtContext* ctx, float out[8]);
+/* The same intervals one by one, in launch order: ms[i] and stage[i] (0 generate, 1 extend, 2 shade in place,
+ * 3 resolve, 4 shade split form, 5 fallback launch; of 2 and 4 one returns at once, 5 normally finds an empty list);
+ * returns their number (at most `cap` are written). */
+int rt_last_launch_table(RtContext* ctx, float* ms, int32_t* stage, uint32_t cap);
 /* Microbenchmark for the traversal roofline (no reference analogue): GB/s of random,
  * independent 32-byte sector loads (the node-fetch instruction) over a buffer of
  * footprint_bytes (rounded down to a power of two): small = L1 gather rate, between L1 and

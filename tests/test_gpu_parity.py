@@ -823,3 +823,53 @@ def test_explicit_tile_lists_assemble_the_frame():
     assert (one.read_hits()["kind"] != 0).any()
     for c in (one, root, peer_root):
         c.close()
+
+
+@pytest.mark.parametrize("scene_name", ["default", "terrain"])
+def test_primary_frames_through_the_wave_traversal(monkeypatch, scene_name):
+    """RTB200_PRIMARY_WAVE=1: legacy and wavefront-depth-0 frames through wv_extend<GEN> + wv_shade_primary must equal
+    the fused kernel's (and the oracle's) bit for bit, ragged tiles and a tile split included."""
+    s = g.default_scene() if scene_name == "default" else g.terrain_scene(120, 90, strategy=abi.BVH_CHUNKED)
+    w, h = 1000, 600
+    ref = ob.render(s, w, h)
+    refw = ob.render(s, w, h, wavefront=(0, 4, 9))
+    monkeypatch.setenv("RTB200_PRIMARY_WAVE", "1")
+    compare(render_gpu_fused(s, w, h), ref)
+    compare(render_gpu_fused(s, w, h, mode=abi.MODE_WAVEFRONT0), refw)
+    ctx = g.Context(0, w, h)
+    g.BufferManager(ctx).upload_scene(s)
+    for ph in range(3):
+        g.ComputeRenderer(ctx).render_frame(s.camera, tile_stride=3, tile_phase=ph, outputs=abi.OUT_HITS | abi.OUT_ACCUM | abi.OUT_COMPOSITE)
+    check_hits(ctx.read_hits(), ref["hits"])
+    assert np.array_equal(ctx.read_composite(), ref["composite"])
+    ctx.close()
+
+
+@pytest.mark.parametrize("literal_walk", [False, True])
+def test_literal_fallback_rays_take_the_fallback_kernel(monkeypatch, literal_walk):
+    """Rays the internal tree cannot serve (axis-aligned directions: zero components; a camera 40 scene sizes away)
+    are traced by wv_fallback, one warp per ray (pruned ORDERED search, or the literal walk with
+    RTB200_FALLBACK_LITERAL=1); whole frames of them must still equal the oracle."""
+    if literal_walk:
+        monkeypatch.setenv("RTB200_FALLBACK_LITERAL", "1")
+    s = g.terrain_scene(60, 45, strategy=abi.BVH_CHUNKED)
+    w, h = 97, 55  # odd: the centre column / row have cx == 0 / cy == 0 exactly
+    cam = s.camera.copy()
+    cam["position"], cam["direction"], cam["up"] = [0.3, 30.0, 0.2], [0, -1, 0], [0, 0, -1]  # centre row / column: d.x == 0 or d.z == 0
+    far = s.camera.copy()
+    far["position"] = -far["direction"] * np.float32(40.0 * float(np.abs(s.vertices["position"]).max()))
+    far["fov"] = np.float32(2.5)
+    for c in (cam, far):
+        ref = ob.render_path(s, w, h, spp=2, max_depth=3, base_seed=6, camera=c)
+        ctx = g.Context(0, w, h)
+        g.BufferManager(ctx).upload_scene(s)
+        cr = g.ComputeRenderer(ctx)
+        ctx.count_next_launch()
+        cr.render_frame(c, mode=abi.MODE_PATH, spp=2, max_depth=3, base_seed=6, traversal=abi.TRAVERSAL_REBUILT, variant=4,
+                        outputs=abi.OUT_ACCUM | abi.OUT_HITS | abi.OUT_COMPOSITE)
+        n_fb = ctx.read_counters()["literal_fallbacks"]
+        assert n_fb > (w * h if c is far else 10)
+        assert ctx.last_segments == ref["counters"]["rays"]
+        assert np.array_equal(ctx.read_accum().view(np.uint32), ref["accum"].view(np.uint32))
+        check_hits(ctx.read_hits(), ref["hits"])
+        ctx.close()
