@@ -909,14 +909,14 @@ static WvKernel wv_extend_kernel(int policy, bool count, bool gen, bool deep) {
     if (policy == 2) return deep ? wv_extend_pick<2, true>(count, gen) : wv_extend_pick<2, false>(count, gen);
     return deep ? wv_extend_pick<1, true>(count, gen) : wv_extend_pick<1, false>(count, gen);
 }
-template <int P, bool S>
+template <int P, int S>
 static WvKernel wv_shade_pick(bool count, bool gen) {
     if (count) return gen ? wv_shade<P, true, true, S> : wv_shade<P, true, false, S>;
     return gen ? wv_shade<P, false, true, S> : wv_shade<P, false, false, S>;
 }
-static WvKernel wv_shade_kernel(int policy, bool count, bool gen, bool split) {
-    if (policy == 2) return split ? wv_shade_pick<2, true>(count, gen) : wv_shade_pick<2, false>(count, gen);
-    return split ? wv_shade_pick<1, true>(count, gen) : wv_shade_pick<1, false>(count, gen);
+static WvKernel wv_shade_kernel(int policy, bool count, bool gen, int split) { // split: 0 / 1 one form, 2 both (rt_wave.cuh)
+    if (policy == 2) return split == 2 ? wv_shade_pick<2, 2>(count, gen) : split ? wv_shade_pick<2, 1>(count, gen) : wv_shade_pick<2, 0>(count, gen);
+    return split == 2 ? wv_shade_pick<1, 2>(count, gen) : split ? wv_shade_pick<1, 1>(count, gen) : wv_shade_pick<1, 0>(count, gen);
 }
 
 int launch_wave(RtContext* c, KParams k, uint32_t traversal) {
@@ -962,6 +962,8 @@ int launch_wave(RtContext* c, KParams k, uint32_t traversal) {
     if (n_sub > 1) CK(c, cudaEventRecord(c->wv_fork, c->stream));
     const uint32_t s_end = k.first_sample + k.spp;
     // which wv_shade form a depth takes (rt_wave.cuh): split when misses * 4 > rays * quarters
+    bool one_shade_launch = WV_SHADE_ONE_LAUNCH != 0;
+    if (const char* e = getenv("RTB200_SHADE_LAUNCHES")) one_shade_launch = atoi(e) == 1;
     uint32_t split_gen = 1u, split_deep = 1u;
     if (const char* e = getenv("RTB200_SPLIT_GEN")) { int v = atoi(e); if (v >= 0 && v <= 5) split_gen = (uint32_t)v; }
     if (const char* e = getenv("RTB200_SPLIT_DEEP")) { int v = atoi(e); if (v >= 0 && v <= 5) split_deep = (uint32_t)v; }
@@ -1033,15 +1035,21 @@ int launch_wave(RtContext* c, KParams k, uint32_t traversal) {
                 wv_extend_kernel(policy, count, gen, deep)<<<ext_blocks, 256, 0, st>>>(ks, w, qi);
                 mark(1);
                 // both forms are launched; the one that does not match the depth's miss ratio returns at once
-                wv_shade_kernel(policy, count, gen, false)<<<stream_blocks, 256, 0, st>>>(ks, w, qi);
-                mark(2);
-                wv_shade_kernel(policy, count, gen, true)<<<stream_blocks, 256, 0, st>>>(ks, w, qi);
-                mark(4);
+                if (one_shade_launch) {
+                    wv_shade_kernel(policy, count, gen, 2)<<<stream_blocks, 256, 0, st>>>(ks, w, qi);
+                    mark(2);
+                } else {
+                    wv_shade_kernel(policy, count, gen, 0)<<<stream_blocks, 256, 0, st>>>(ks, w, qi);
+                    mark(2);
+                    wv_shade_kernel(policy, count, gen, 1)<<<stream_blocks, 256, 0, st>>>(ks, w, qi);
+                    mark(4);
+                    c->launches++;
+                }
                 // the rays those left to the reference's own traversal (normally none: the kernel reads an empty list)
                 if (count) { if (gen) wv_fallback<true, true><<<fb_blocks, 256, 0, st>>>(ks, w, qi); else wv_fallback<true, false><<<fb_blocks, 256, 0, st>>>(ks, w, qi); }
                 else { if (gen) wv_fallback<false, true><<<fb_blocks, 256, 0, st>>>(ks, w, qi); else wv_fallback<false, false><<<fb_blocks, 256, 0, st>>>(ks, w, qi); }
                 mark(5);
-                c->launches += 4;
+                c->launches += 3;
             }
             wv_resolve<<<stream_blocks, 256, 0, st>>>(ks, w);
             mark(3);

@@ -543,18 +543,36 @@ __global__ void __launch_bounds__(256) wv_fallback(const __grid_constant__ KPara
 // quarter of the rays left the scene.  Results are identical either way; on a closed scene the queueing only
 // costs (Cornell box: 5 % of the frame), on the open terrain it saves a sixth of the shading time.
 template <int POLICY, bool COUNT, bool GEN, bool SPLIT>
+__device__ __forceinline__ void wv_shade_body(const KParams& p, const WvBuffers& w, int qi, uint32_t (*s_list)[3][64]);
+
+#ifndef WV_SHADE_ONE_LAUNCH
+#define WV_SHADE_ONE_LAUNCH 1 // 1: one shade launch per depth holding both forms (the device picks); 0: one launch per form
+#endif
+// SPLIT here: 0 in-place form only, 1 split form only (two launches per depth, each returns at once if the miss
+// ratio asks for the other), 2 both forms in one launch
+template <int POLICY, bool COUNT, bool GEN, int SPLIT>
 __global__ void __launch_bounds__(256, WV_SHADE_BLOCKS) wv_shade(const __grid_constant__ KParams p, WvBuffers w, int qi) {
-    const unsigned full = 0xFFFFFFFFu;
-    const uint32_t lane = threadIdx.x & 31u;
+    __shared__ uint32_t s_list[SPLIT == 0 ? 1 : 8][3][64];
     const uint32_t n = GEN ? p.n_work * w.spp_wave : w.ctrl->n[qi];
-    const float4* __restrict__ tris = POLICY == 2 ? p.btris : p.wtris;
-    if (!SPLIT && blockIdx.x == 0 && threadIdx.x == 0) { // wv_extend of this depth has finished (first of the two launches)
+    if (SPLIT != 1 && blockIdx.x == 0 && threadIdx.x == 0) { // wv_extend of this depth has finished (first launch of the depth)
         w.ctrl->head = 0;
         const unsigned long long traced = GEN ? (unsigned long long)w.valid_pixels * w.spp_wave : (unsigned long long)n;
         w.ctrl->segments += traced;
         w.ctrl->rays_at_depth[w.depth < 7u ? w.depth : 7u] += (unsigned int)traced;
     }
-    if (((unsigned long long)w.ctrl->misses[qi] * 4ull > (unsigned long long)n * w.split_quarters) != SPLIT) return;
+    const bool want_split = (unsigned long long)w.ctrl->misses[qi] * 4ull > (unsigned long long)n * w.split_quarters;
+    if (SPLIT == 2) {
+        if (want_split) wv_shade_body<POLICY, COUNT, GEN, true>(p, w, qi, s_list);
+        else wv_shade_body<POLICY, COUNT, GEN, false>(p, w, qi, s_list);
+    } else if (want_split == (SPLIT == 1)) wv_shade_body<POLICY, COUNT, GEN, SPLIT == 1>(p, w, qi, s_list);
+}
+
+template <int POLICY, bool COUNT, bool GEN, bool SPLIT>
+__device__ __forceinline__ void wv_shade_body(const KParams& p, const WvBuffers& w, int qi, uint32_t (*s_list)[3][64]) {
+    const unsigned full = 0xFFFFFFFFu;
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t n = GEN ? p.n_work * w.spp_wave : w.ctrl->n[qi];
+    const float4* __restrict__ tris = POLICY == 2 ? p.btris : p.wtris;
     // Paths whose ray left the scene (on open scenes most of depth >= 1) only add the sky term; if they shared
     // warps with the hits, the shading code would run with a handful of lanes (ncu: 7 of 32 at depth 1 of C3).
     // Every warp owns a small queue in shared memory: phase A of each 32-path chunk finishes the misses and queues
@@ -562,8 +580,7 @@ __global__ void __launch_bounds__(256, WV_SHADE_BLOCKS) wv_shade(const __grid_co
     // for each other (a dense chunk goes straight through: 32 queued, 32 shaded).
     // A queue entry is (path, hit record); the hit records of the next chunk are loaded before the current one is
     // shaded, so the only global-memory wait on the dense path stays the path-state load of phase B.
-    __shared__ uint32_t s_list[8][3][64];
-    uint32_t (*const my_list)[64] = s_list[threadIdx.x >> 5];
+    uint32_t (*const my_list)[64] = s_list[SPLIT ? (threadIdx.x >> 5) : 0];
     uint32_t queued_now = 0; // warp-uniform
     const uint32_t n_round = (n + 31u) & ~31u;
     const uint32_t warp_stride = gridDim.x * 256u;
