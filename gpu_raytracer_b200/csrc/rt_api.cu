@@ -671,7 +671,7 @@ int build_rebuilt(RtContext* c, uint32_t n) {
     // bounds[0..2] = 0xFFFFFFFF (ordered min), [3..7] = 0 (ordered max; [6] = tree depth)
     CK(c, cudaMemsetAsync(c->lb_bounds.ptr, 0xFF, 12, c->stream));
     CK(c, cudaMemsetAsync(c->lb_bounds.ptr + 3, 0, 20, c->stream));
-    lbvh::centroid_bounds<<<g, 256, 0, c->stream>>>(c->pbox.ptr, n, c->lb_bounds.ptr);
+    lbvh::centroid_bounds<<<g < 1184u ? g : 1184u, 256, 0, c->stream>>>(c->pbox.ptr, n, c->lb_bounds.ptr);
     lbvh::morton_keys<<<g, 256, 0, c->stream>>>(c->pbox.ptr, n, c->lb_bounds.ptr, c->lb_keys.ptr, c->lb_vals.ptr);
     c->launches += 2;
     if (cub::DeviceRadixSort::SortPairs(c->lb_temp.ptr, temp_bytes, c->lb_keys.ptr, c->lb_keys_sorted.ptr, c->lb_vals.ptr,
