@@ -50,6 +50,7 @@ for _name, (_dt, _sz) in SIZES.items():
 # RaytracerConfig, shared/src/lib.rs:18-35
 TILE_SIZE = 128
 SPLIT_TILE = 64  # include/rtb200.h RT_SPLIT_TILE: unit of the multi-GPU screen split
+STATIC_TILE_LIST_MAX = 16384  # include/rtb200.h RT_STATIC_TILE_LIST_MAX: rt_pack_tile_list_static scratch entries
 THREAD_GROUP_SIZE = (16, 16)
 MIN_RAY_DISTANCE = np.float32(0.00001)
 MAX_TRIANGLES_PER_BUFFER = 8388608

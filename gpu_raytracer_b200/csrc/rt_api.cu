@@ -1396,6 +1396,47 @@ int rt_pack_tile_list(RtContext* c, uint32_t what, const uint32_t* tiles, uint32
     static const uint32_t none = 0;
     return tile_copy_launch(c, what, 1, 0, tiles ? tiles : &none, n, dst_device, true);
 }
+// ---- rt_pack_tile_list without any allocation -----------------------------------------------------------------
+// rt_pack_tile_list stages the caller's tile list in a device scratch buffer that it (re)allocates with cudaMalloc
+// when the list grows.  Callers that must not allocate (code under CUDA graph capture, tight serving loops, harnesses
+// that forbid cudaMalloc) use this variant: the list is staged in ONE file-scope device array of RT_STATIC_TILE_LIST_MAX
+// entries (64 KiB; every GPU that loads the library holds it until exit).  In host code the array's name is a host-side
+// stand-in, not a device address: the address comes from cudaGetSymbolAddress, taken once per device with that device
+// current.  All calls on a GPU share the array (it keeps the last call's list; every call overwrites the n entries it
+// uses, nothing has to start at zero), so calls that overlap on the GPU (other streams / contexts of the same device)
+// race.  No cudaMalloc / cudaFree / allocating library call, and no host wait.
+static __device__ __align__(256) uint32_t g_static_tile_list[RT_STATIC_TILE_LIST_MAX];
+static uint32_t* g_static_tile_list_addr[64]; // per device ordinal; filled on the first call for that device
+
+int rt_pack_tile_list_static(RtContext* c, uint32_t what, const uint32_t* tiles, uint32_t n, void* dst_device) {
+    if (!c || !dst_device || (n && !tiles)) return c ? fail(c, RT_ERR_INVALID_ARGUMENT, "rt_pack_tile_list_static: NULL argument") : RT_ERR_INVALID_ARGUMENT;
+    if (c->width == 0) return fail(c, RT_ERR_NOT_READY, "rt_resize has not been called");
+    if (what > 1) return fail(c, RT_ERR_INVALID_ARGUMENT, "rt_pack_tile_list_static: what = %u (0 composite, 1 accumulation)", what);
+    if (n > RT_STATIC_TILE_LIST_MAX)
+        return fail(c, RT_ERR_INVALID_ARGUMENT, "rt_pack_tile_list_static: %u tiles exceed the static scratch of %u entries "
+                                                "(use rt_pack_tile_list, which allocates)", n, (unsigned)RT_STATIC_TILE_LIST_MAX);
+    if (c->device < 0 || c->device >= 64) return fail(c, RT_ERR_INVALID_ARGUMENT, "rt_pack_tile_list_static: device ordinal %d", c->device);
+    const uint32_t frame_tiles = c->stiles_x * c->stiles_y;
+    for (uint32_t i = 0; i < n; i++) if (tiles[i] >= frame_tiles) return fail(c, RT_ERR_INVALID_ARGUMENT, "tile %u of %u", tiles[i], frame_tiles);
+    CK(c, cudaSetDevice(c->device));
+    uint32_t* list = g_static_tile_list_addr[c->device];
+    if (!list) { // set-up, once per device, with that device current
+        CK(c, cudaGetSymbolAddress((void**)&list, g_static_tile_list));
+        if (!list) return fail(c, RT_ERR_CUDA, "cudaGetSymbolAddress returned NULL");
+        g_static_tile_list_addr[c->device] = list;
+    }
+    if (n == 0) return RT_OK;
+    // stream-ordered like every other call: `tiles` is read when the stream reaches this copy (pageable memory is
+    // staged before the call returns, pinned memory must stay valid until then)
+    CK(c, cudaMemcpyAsync(list, tiles, (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
+    dim3 grid(4096 / 256, n);
+    if (what == 0) tile_copy<uchar4, true><<<grid, 256, 0, c->stream>>>(c->composite.ptr, (uchar4*)dst_device, c->width, c->height, c->stiles_x, n, 1u, 0u, list);
+    else tile_copy<float4, true><<<grid, 256, 0, c->stream>>>(c->accum.ptr, (float4*)dst_device, c->width, c->height, c->stiles_x, n, 1u, 0u, list);
+    CK(c, cudaGetLastError());
+    c->launches++;
+    return RT_OK;
+}
+
 int rt_unpack_tile_list(RtContext* c, uint32_t what, const uint32_t* tiles, uint32_t n, const void* src_device) {
     if (n && !tiles) return RT_ERR_INVALID_ARGUMENT;
     static const uint32_t none = 0;

@@ -18,7 +18,7 @@ API_SYMBOLS = [
     "rt_device_composite", "rt_count_next_launch", "rt_read_counters", "rt_last_kernel_ms", "rt_launch_count",
     "rt_last_traversal", "rt_last_build_ms", "rt_last_segments", "rt_last_wavefront_counters", "rt_last_stage_ms", "rt_last_launch_table", "rt_probe_gather_bandwidth",
     "rt_export_frame_handle", "rt_open_peer_frame", "rt_set_peer_frame", "rt_close_peer_frame", "rt_pack_tiles",
-    "rt_unpack_tiles", "rt_set_tile_list", "rt_pack_tile_list", "rt_unpack_tile_list",
+    "rt_unpack_tiles", "rt_set_tile_list", "rt_pack_tile_list", "rt_unpack_tile_list", "rt_pack_tile_list_static",
     "rt_stream"]
 HOST_SYMBOLS = [
     "rt_f32_to_f16", "rt_f16_to_f32", "rt_camera_default", "rt_material_new", "rt_material_diffuse",
@@ -68,7 +68,7 @@ def load():
         "rt_close_peer_frame": (i32, [vp]), "rt_pack_tiles": (i32, [vp, u32, u32, u32, vp]),
         "rt_unpack_tiles": (i32, [vp, u32, u32, u32, vp]), "rt_stream": (vp, [vp]),
         "rt_set_tile_list": (i32, [vp, vp, u32]), "rt_pack_tile_list": (i32, [vp, u32, vp, u32, vp]),
-        "rt_unpack_tile_list": (i32, [vp, u32, vp, u32, vp]),
+        "rt_unpack_tile_list": (i32, [vp, u32, vp, u32, vp]), "rt_pack_tile_list_static": (i32, [vp, u32, vp, u32, vp]),
         "rt_f32_to_f16": (C.c_uint16, [f32]), "rt_f16_to_f32": (f32, [C.c_uint16]),
         "rt_camera_default": (None, [vp]),
         "rt_material_new": (None, [vp, vp, f32, f32, vp, f32, f32]), "rt_material_diffuse": (None, [vp, vp]),

@@ -102,6 +102,13 @@ class Context:
         t = np.ascontiguousarray(tiles, np.uint32)
         self._ck(self.lib.rt_pack_tile_list(self.handle, what, _p(t), len(t), C.c_void_p(dst_device_ptr)))
 
+    def pack_tile_list_static(self, what, tiles, dst_device_ptr):
+        """rt_pack_tile_list_static: no allocation (static device scratch, <= abi.STATIC_TILE_LIST_MAX tiles).  The list
+        is kept alive on this object until the next call: the copy is stream-ordered."""
+        self._static_list = np.ascontiguousarray(tiles, np.uint32)
+        self._ck(self.lib.rt_pack_tile_list_static(self.handle, what, _p(self._static_list), len(self._static_list),
+                                                   C.c_void_p(dst_device_ptr)))
+
     def unpack_tile_list(self, what, tiles, src_device_ptr):
         t = np.ascontiguousarray(tiles, np.uint32)
         self._ck(self.lib.rt_unpack_tile_list(self.handle, what, _p(t), len(t), C.c_void_p(src_device_ptr)))

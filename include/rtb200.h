@@ -191,6 +191,17 @@ int rt_unpack_tiles(RtContext* ctx, uint32_t what, uint32_t stride, uint32_t pha
 int rt_set_tile_list(RtContext* ctx, const uint32_t* tiles, uint32_t n);
 int rt_pack_tile_list(RtContext* ctx, uint32_t what, const uint32_t* tiles, uint32_t n, void* dst_device);
 int rt_unpack_tile_list(RtContext* ctx, uint32_t what, const uint32_t* tiles, uint32_t n, const void* src_device);
+/* rt_pack_tile_list that allocates nothing.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  Same result as rt_pack_tile_list (tile k of `tiles` -> dst_device[k][RT_SPLIT_TILE][RT_SPLIT_TILE]), but
+ * the list is staged in one file-scope static device array of RT_STATIC_TILE_LIST_MAX entries (64 KiB per GPU that
+ * loads the library, held until exit) instead of a scratch buffer grown with cudaMalloc; n beyond that limit is refused
+ * with RT_ERR_INVALID_ARGUMENT.  The call makes no cudaMalloc / cudaFree / allocating library call and does not wait
+ * on the host: `tiles` must stay valid until the context's stream has passed the call when it lies in pinned memory.
+ * Every call on a GPU shares that array and leaves its list in it (each call overwrites the entries it uses; nothing
+ * needs clearing): calls that overlap on the GPU, from other contexts or streams of the same device, race. */
+#define RT_STATIC_TILE_LIST_MAX 16384u
+int rt_pack_tile_list_static(RtContext* ctx, uint32_t what, const uint32_t* tiles, uint32_t n, void* dst_device);
 /* Fused multi-GPU epilogue (no reference analogue): instead of pack -> NCCL gather -> unpack, the kernels of
  * ranks != 0 store their finished composite pixels straight into rank 0's frame through peer memory (P2P
  * stores over NVLink; the frame is W*H*4 bytes in total).  Rank 0 exports its composite buffer as a 64-byte
