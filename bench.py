@@ -43,6 +43,13 @@ WORKLOADS = {
     "c3-smallleaf": dict(nx=1000, nz=500, w=1920, h=1080, bvh="small_leaf", mode="path", spp=16, depth=4,
                          desc="C3 with the scene uploaded as a small-leaf BVH (<=4 tris/leaf, binned SAH, reference node "
                               "format; SURVEY 8f #1): 1M-triangle terrain, 1920x1080, 4 bounces, 16 spp (EXTENSION semantics)"),
+    "field": dict(scene="field", w=1920, h=1080, bvh="auto", mode="path", spp=16, depth=4,
+                  desc="Field (not a height field; tree-quality check off the benchmark terrain): 1996 tori at mixed scales and "
+                       "orientations scattered through a volume over a ground grid = 1 000 000 triangles, 1920x1080, 4 bounces, "
+                       "16 spp (EXTENSION semantics), uploaded with the reference's chunked BVH (100 tris/leaf)"),
+    "field-smallleaf": dict(scene="field", w=1920, h=1080, bvh="small_leaf", mode="path", spp=16, depth=4,
+                            desc="Field scene uploaded as a small-leaf BVH (<= 4 tris/leaf, host binned SAH, reference node "
+                                 "format), 1920x1080, 4 bounces, 16 spp (EXTENSION semantics)"),
     "c4": dict(scene="cornell", w=1024, h=1024, bvh="auto", mode="path", spp=64, depth=8,
                desc="C4: Cornell box (36 triangles), 1024x1024, diffuse bounces to depth 8, 64 spp (EXTENSION "
                     "semantics, SPEC.md) - divergence stress"),
@@ -56,7 +63,7 @@ WORKLOADS = {
 # figures are the same measurement): a centred band of rows of the workload's own frame, full spp and depth.
 # Sized for ~2-6 s on 16 host threads; the oracle hands 64-pixel spans to its pool, so even 2 rows keep every
 # thread busy.  Primary workloads: whole 128-row tile bands, three channel passes (the reference's own loop).
-CPU_SAMPLE_ROWS = {"c3": 4, "c3-smallleaf": 64, "c4": 48, "c5": 1, "c3-primary": 128, "c3-primary-smallleaf": 1080,
+CPU_SAMPLE_ROWS = {"field": 4, "field-smallleaf": 64, "c3": 4, "c3-smallleaf": 64, "c4": 48, "c5": 1, "c3-primary": 128, "c3-primary-smallleaf": 1080,
                    "c2": 1080}
 
 
@@ -156,6 +163,8 @@ def build_scene(wl):
     strat = {"auto": abi.BVH_AUTO, "small_leaf": abi.BVH_SMALL_LEAF, "standard": abi.BVH_STANDARD}[wl["bvh"]]
     if wl.get("scene") == "cornell":
         return g.cornell_scene(strat)
+    if wl.get("scene") == "field":
+        return g.field_scene(strategy=strat)
     return g.terrain_scene(wl["nx"], wl["nz"], seed=1, strategy=strat)
 
 

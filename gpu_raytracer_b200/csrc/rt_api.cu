@@ -681,8 +681,11 @@ int build_rebuilt(RtContext* c, uint32_t n) {
         CK(c, cudaMemsetAsync(c->lb_visits.ptr, 0, (size_t)n * 4, c->stream));
         lbvh::build_radix_tree<<<g, 256, 0, c->stream>>>(c->lb_keys_sorted.ptr, n, c->lb_children.ptr, c->lb_range.ptr,
                                                          c->lb_parent_i.ptr, c->lb_parent_l.ptr);
-        lbvh::fit_boxes<<<g, 256, 0, c->stream>>>(c->pbox.ptr, c->lb_vals_sorted.ptr, n, c->lb_children.ptr,
-                                                  c->lb_parent_i.ptr, c->lb_parent_l.ptr, c->lb_nbox.ptr, c->lb_visits.ptr);
+        // tree rotations while fitting (rt_lbvh.cuh); RTB200_LBVH_ROTATE=0 switches them off (tuning / A-B measurements)
+        const char* rot_env = getenv("RTB200_LBVH_ROTATE");
+        lbvh::fit_boxes<<<g, 256, 0, c->stream>>>(c->pbox.ptr, c->lb_vals_sorted.ptr, n, c->lb_children.ptr, c->lb_range.ptr,
+                                                  c->lb_parent_i.ptr, c->lb_parent_l.ptr, c->lb_nbox.ptr, c->lb_visits.ptr,
+                                                  (rot_env && atoi(rot_env) == 0) ? 0 : 1);
         // compact index of every emitted node: flags in lb_visits (free after the fit), scan into lb_vals (free after the sort)
         lbvh::mark_emitted<<<g, 256, 0, c->stream>>>(c->lb_range.ptr, n, c->lb_visits.ptr);
         if (cub::DeviceScan::ExclusiveSum(c->lb_temp.ptr, temp_bytes, c->lb_visits.ptr, c->lb_vals.ptr, (int)n, c->stream) != cudaSuccess)
@@ -1007,6 +1010,7 @@ int launch_wave(RtContext* c, KParams k, uint32_t traversal) {
         w.state[0] = c->wv_state[0].ptr + path_base * 4; w.state[1] = c->wv_state[1].ptr + path_base * 4;
         w.hit[0] = c->wv_hit[0].ptr + path_base; w.hit[1] = c->wv_hit[1].ptr + path_base;
         w.lbuf = c->wv_lbuf.ptr + path_base; w.ctrl = c->wv_ctrl.ptr + sub; w.fb_list = c->wv_fb.ptr + path_base;
+        w.capacity = (uint32_t)Ps;
         path_base += Ps;
         uint32_t ext_per_sm = (uint32_t)(per_sm > 0 ? per_sm : 1);
         if (const char* e = getenv("RTB200_EXT_BLOCKS_PER_SM")) { int v = atoi(e); if (v >= 1 && (uint32_t)v < ext_per_sm) ext_per_sm = (uint32_t)v; } // tuning
@@ -1100,7 +1104,7 @@ int launch_primary_wave(RtContext* c, KParams k, uint32_t traversal, uint32_t my
     memset(&w, 0, sizeof w);
     w.hit[0] = c->wv_hit[0].ptr; w.hit[1] = c->wv_hit[0].ptr; // depth 0 only: nothing is appended
     w.ctrl = c->wv_ctrl.ptr;
-    w.s0 = 0; w.spp_wave = 1; w.first_wave = 1; w.last_wave = 1;
+    w.s0 = 0; w.spp_wave = 1; w.first_wave = 1; w.last_wave = 1; w.capacity = (uint32_t)P;
     for (uint32_t t = 0; t < my_tiles; t++) {
         uint32_t tile = k.tile_phase + t * k.tile_stride;
         if (k.tile_list) tile = c->tile_list_host[tile];

@@ -152,29 +152,81 @@ __global__ void build_radix_tree(const unsigned long long* __restrict__ keys, ui
     if (i == 0) parent_internal[0] = 0xFFFFFFFFu;
 }
 
-// bottom-up fit: the second thread to reach a node computes its box
+// bottom-up fit: the second thread to reach a node computes its box.
+// ROTATE: before it moves on, the same thread tries the four tree rotations at that node (Kensler 2008): swap one
+// child K with a grandchild G under the other child O when that shrinks O's box area (O = {K, sibling of G}).  The
+// whole subtree below the node is finished at that point and no thread above has started, so the rewrite is race-free.
+// Subtrees that will be collapsed into leaves (<= RT_LBVH_LEAF triangles: contiguous sorted slots) only move as a
+// whole, and a rotation that would leave O with <= RT_LBVH_LEAF triangles (a leaf of non-contiguous slots) is not
+// taken.  After a rotation range[O] only carries O's triangle COUNT (y - x + 1); its x is meaningless, and it is
+// only ever read for nodes of <= RT_LBVH_LEAF triangles, which are never rewritten.  Measured on a scene that is not a
+// height field (1 M triangles of tori, scripts/tree_study.py / bench --workload field): 5 % fewer box tests per ray;
+// nothing to gain on the terrains (x/z Morton code).
+__device__ __forceinline__ float box_area(float4 lo, float4 hi) {
+    float dx = fmaxf(hi.x - lo.x, 0.0f), dy = fmaxf(hi.y - lo.y, 0.0f), dz = fmaxf(hi.z - lo.z, 0.0f);
+    return dx * dy + dy * dz + dz * dx;
+}
 __global__ void fit_boxes(const float4* __restrict__ pbox, const uint32_t* __restrict__ sorted_pos, uint32_t n,
-                          const uint2* __restrict__ children, const uint32_t* __restrict__ parent_internal,
-                          const uint32_t* __restrict__ parent_leaf, float4* __restrict__ nbox,
-                          unsigned int* __restrict__ visits) {
+                          uint2* children, uint2* range, uint32_t* parent_internal, uint32_t* parent_leaf,
+                          float4* __restrict__ nbox, unsigned int* __restrict__ visits, int rotate) {
     uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= n || n < 2) return;
+    auto load_box = [&](uint32_t c, float4& lo, float4& hi) {
+        const float4* s = (c & 0x80000000u) ? pbox + (size_t)sorted_pos[c & 0x7FFFFFFFu] * 2 : nbox + (size_t)c * 2;
+        lo = __ldcg(s); hi = __ldcg(s + 1); // plain L2 loads: nbox entries were written by other threads in this launch
+    };
+    auto count_of = [&](uint32_t c) -> uint32_t {
+        if (c & 0x80000000u) return 1u;
+        uint2 r = __ldcg(range + c);
+        return r.y - r.x + 1u;
+    };
     uint32_t node = parent_leaf[k];
     while (node != 0xFFFFFFFFu) {
         __threadfence();
         if (atomicAdd(visits + node, 1u) == 0u) return; // first arrival waits for the sibling
-        uint2 ch = children[node];
-        float4 lo, hi;
-        {
-            const float4* a = (ch.x & 0x80000000u) ? pbox + (size_t)sorted_pos[ch.x & 0x7FFFFFFFu] * 2 : nbox + (size_t)ch.x * 2;
-            const float4* b = (ch.y & 0x80000000u) ? pbox + (size_t)sorted_pos[ch.y & 0x7FFFFFFFu] * 2 : nbox + (size_t)ch.y * 2;
-            // plain (non-__ldg) loads: nbox entries were written by other threads in this launch
-            float4 alo = __ldcg(a), ahi = __ldcg(a + 1), blo = __ldcg(b), bhi = __ldcg(b + 1);
-            lo = make_float4(fminf(alo.x, blo.x), fminf(alo.y, blo.y), fminf(alo.z, blo.z), 0.0f);
-            hi = make_float4(fmaxf(ahi.x, bhi.x), fmaxf(ahi.y, bhi.y), fmaxf(ahi.z, bhi.z), 0.0f);
+        uint2 ch = __ldcg(children + node);
+        float4 alo, ahi, blo, bhi;
+        load_box(ch.x, alo, ahi);
+        load_box(ch.y, blo, bhi);
+        __stcg(nbox + (size_t)node * 2, make_float4(fminf(alo.x, blo.x), fminf(alo.y, blo.y), fminf(alo.z, blo.z), 0.0f));
+        __stcg(nbox + (size_t)node * 2 + 1, make_float4(fmaxf(ahi.x, bhi.x), fmaxf(ahi.y, bhi.y), fmaxf(ahi.z, bhi.z), 0.0f));
+        if (rotate) {
+            float best = 0.0f;
+            int best_side = -1, best_gs = 0;
+            float4 best_lo = alo, best_hi = ahi;
+            for (int side = 0; side < 2; side++) {
+                const uint32_t keep = side == 0 ? ch.x : ch.y, other = side == 0 ? ch.y : ch.x;
+                if ((other & 0x80000000u) || count_of(other) <= RT_LBVH_LEAF) continue; // O is (or becomes) a leaf
+                const float4 klo = side == 0 ? alo : blo, khi = side == 0 ? ahi : bhi;
+                const float cur = box_area(side == 0 ? blo : alo, side == 0 ? bhi : ahi);
+                const uint2 och = __ldcg(children + other);
+                const uint32_t kc = count_of(keep);
+                for (int gs = 0; gs < 2; gs++) {
+                    const uint32_t stay = gs == 0 ? och.y : och.x;
+                    if (kc + count_of(stay) <= RT_LBVH_LEAF) continue; // O would collapse into a non-contiguous leaf
+                    float4 slo, shi;
+                    load_box(stay, slo, shi);
+                    const float4 nlo = make_float4(fminf(klo.x, slo.x), fminf(klo.y, slo.y), fminf(klo.z, slo.z), 0.0f);
+                    const float4 nhi = make_float4(fmaxf(khi.x, shi.x), fmaxf(khi.y, shi.y), fmaxf(khi.z, shi.z), 0.0f);
+                    const float d = box_area(nlo, nhi) - cur;
+                    if (d < best) { best = d; best_side = side; best_gs = gs; best_lo = nlo; best_hi = nhi; }
+                }
+            }
+            if (best_side >= 0) {
+                const uint32_t keep = best_side == 0 ? ch.x : ch.y, other = best_side == 0 ? ch.y : ch.x;
+                uint2 och = __ldcg(children + other);
+                const uint32_t gc = best_gs == 0 ? och.x : och.y, stay = best_gs == 0 ? och.y : och.x;
+                if (best_gs == 0) och.x = keep; else och.y = keep;
+                if (best_side == 0) ch.x = gc; else ch.y = gc;
+                __stcg(children + other, och);
+                __stcg(children + node, ch);
+                __stcg(range + other, make_uint2(0u, count_of(keep) + count_of(stay) - 1u)); // count only (see above)
+                __stcg(nbox + (size_t)other * 2, best_lo);
+                __stcg(nbox + (size_t)other * 2 + 1, best_hi);
+                if (keep & 0x80000000u) parent_leaf[keep & 0x7FFFFFFFu] = other; else parent_internal[keep] = other;
+                if (gc & 0x80000000u) parent_leaf[gc & 0x7FFFFFFFu] = node; else parent_internal[gc] = node;
+            }
         }
-        __stcg(nbox + (size_t)node * 2, lo);
-        __stcg(nbox + (size_t)node * 2 + 1, hi);
         node = parent_internal[node];
     }
 }

@@ -55,6 +55,65 @@ void rt_scene_terrain(uint32_t nx, uint32_t nz, uint32_t seed, RtVertex* vertice
     camera->fov = 45.0f;
 }
 
+// Field(n_tori, seg, ring, gnx, gnz, seed): a scene that is NOT a height field (tree-quality study off the terrain):
+// n_tori closed, non-convex meshes (tori of seg x ring quads = 2 seg ring triangles each) at log-uniform scales
+// 0.3 .. 6 with random orientations, scattered through the volume [-50,50] x [1,26] x [-50,50] so that they overlap
+// in every projection, above a flat ground grid of gnx x gnz quads.  Vertices: n_tori seg ring + (gnx+1)(gnz+1);
+// triangles: 2 n_tori seg ring + 2 gnx gnz.  Field(1996, 25, 10, 40, 25) = exactly 1 000 000 triangles.
+void rt_scene_field(uint32_t n_tori, uint32_t seg, uint32_t ring, uint32_t gnx, uint32_t gnz, uint32_t seed,
+                    RtVertex* vertices, RtTriangle* triangles, RtMaterial materials[3], RtLight lights[2], RtCamera* camera) {
+    size_t nv = 0, nt = 0;
+    const double two_pi = 6.283185307179586;
+    for (uint32_t o = 0; o < n_tori; o++) {
+        const double R = 0.3 * pow(20.0, (double)hash01(seed, o, 1u)), r = 0.35 * R;
+        const double cx = -50.0 + 100.0 * hash01(seed, o, 2u), cy = 1.0 + R + (25.0 - R) * hash01(seed, o, 3u),
+                     cz = -50.0 + 100.0 * hash01(seed, o, 4u);
+        // orientation: rotate the torus axis (0,1,0) by angle a about x, then b about y
+        const double a = two_pi * hash01(seed, o, 5u), b = two_pi * hash01(seed, o, 6u);
+        const double ca = cos(a), sa = sin(a), cb = cos(b), sb = sin(b);
+        const size_t base = nv;
+        for (uint32_t i = 0; i < seg; i++)
+            for (uint32_t j = 0; j < ring; j++) {
+                const double u = two_pi * i / seg, v = two_pi * j / ring;
+                const double x = (R + r * cos(v)) * cos(u), y = r * sin(v), z = (R + r * cos(v)) * sin(u);
+                const double y1 = ca * y - sa * z, z1 = sa * y + ca * z;  // about x
+                const double x2 = cb * x + sb * z1, z2 = -sb * x + cb * z1; // about y
+                set3(vertices[nv++].position, (float)(cx + x2), (float)(cy + y1), (float)(cz + z2));
+            }
+        const uint32_t mat = o % 3u;
+        for (uint32_t i = 0; i < seg; i++)
+            for (uint32_t j = 0; j < ring; j++) {
+                const uint32_t i1 = (i + 1) % seg, j1 = (j + 1) % ring;
+                const uint32_t v00 = (uint32_t)(base + i * ring + j), v01 = (uint32_t)(base + i * ring + j1),
+                               v10 = (uint32_t)(base + i1 * ring + j), v11 = (uint32_t)(base + i1 * ring + j1);
+                triangles[nt].v0_index = v00; triangles[nt].v1_index = v01; triangles[nt].v2_index = v11; triangles[nt].material_id = mat; nt++;
+                triangles[nt].v0_index = v00; triangles[nt].v1_index = v11; triangles[nt].v2_index = v10; triangles[nt].material_id = mat; nt++;
+            }
+    }
+    const size_t gbase = nv;
+    for (uint32_t iz = 0; iz <= gnz; iz++)
+        for (uint32_t ix = 0; ix <= gnx; ix++)
+            set3(vertices[nv++].position, -60.0f + 120.0f * (float)ix / (float)gnx, 0.0f, -60.0f + 120.0f * (float)iz / (float)gnz);
+    for (uint32_t iz = 0; iz < gnz; iz++)
+        for (uint32_t ix = 0; ix < gnx; ix++) {
+            const uint32_t v00 = (uint32_t)(gbase + iz * (gnx + 1) + ix), v10 = v00 + 1, v01 = v00 + (gnx + 1), v11 = v01 + 1;
+            triangles[nt].v0_index = v00; triangles[nt].v1_index = v01; triangles[nt].v2_index = v11; triangles[nt].material_id = 0; nt++;
+            triangles[nt].v0_index = v00; triangles[nt].v1_index = v11; triangles[nt].v2_index = v10; triangles[nt].material_id = 0; nt++;
+        }
+    const float sand[3] = {0.7f, 0.65f, 0.5f}, steel[3] = {0.75f, 0.75f, 0.8f}, aqua[3] = {0.3f, 0.6f, 0.9f};
+    rt_material_diffuse(&materials[0], sand);
+    rt_material_metallic(&materials[1], steel, 0.2f);
+    rt_material_glass(&materials[2], aqua, 1.5f, 0.6f);
+    const float lp[3] = {0.0f, 60.0f, 20.0f}, white[3] = {1.0f, 1.0f, 1.0f};
+    rt_light_point(&lights[0], lp, white, 30.0f, INFINITY);
+    const float ld[3] = {-0.3f, -1.0f, -0.2f}, warm[3] = {1.0f, 0.95f, 0.9f};
+    rt_light_directional(&lights[1], ld, warm, 0.8f);
+    set3(camera->position, 0.0f, 32.0f, 98.0f);
+    set3(camera->direction, 0.0f, -0.24253563f, -0.97014250f);
+    set3(camera->up, 0.0f, 1.0f, 0.0f);
+    camera->fov = 45.0f;
+}
+
 namespace {
 struct Builder {
     RtVertex* v; RtTriangle* t; uint32_t nv = 0, nt = 0;

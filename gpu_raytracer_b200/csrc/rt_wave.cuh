@@ -20,7 +20,17 @@
 //   * sample radiances go to Lbuf[sample][pixel] and wv_resolve adds them in sample order,
 //     so fp32 accumulation stays bit-identical to the sequential definition (SPEC.md step 4).
 #pragma once
+#include <assert.h>
 #include "rt_kernels.cuh"
+
+// -DRT_CHECKED builds (make tune NAME=checked FLAGS=-DRT_CHECKED; scripts/sanitize.sh): device-side bounds checks on
+// every index this engine computes into its queues, stacks and per-warp lists.  compute-sanitizer is closed on this
+// pool, so the parity subset is run against this build instead; a violated check traps the kernel.
+#ifdef RT_CHECKED
+#define WV_CHECK(cond) assert(cond)
+#else
+#define WV_CHECK(cond) ((void)0)
+#endif
 
 struct WvCtrl {
     unsigned int n[2];          // live paths at the current / next depth (ping-pong)
@@ -47,6 +57,7 @@ struct WvBuffers {
     uint32_t first_wave;   // resolve honours reset_accum
     uint32_t valid_pixels; // work items of this sub-frame that lie inside the image (fused generation: segment count of depth 0)
     uint32_t depth;        // bounce depth of this launch (bookkeeping only: rays_at_depth)
+    uint32_t capacity;     // paths this sub-frame's queues / lists hold (RT_CHECKED bounds checks)
     uint32_t split_quarters; // wv_shade takes its split form when misses * 4 > rays * split_quarters (>= 5: never)
 };
 
@@ -226,7 +237,7 @@ __global__ void __launch_bounds__(256, WV_BLOCKS) wv_extend(const __grid_constan
         sp++;
     };
     auto pop = [&]() -> uint32_t {
-        if (!DEEP) { sptr -= 256; return *sptr; }
+        if (!DEEP) { sptr -= 256; WV_CHECK(sptr >= &s_stack[0][tid]); return *sptr; }
         sp--;
         return sp < WV_STK ? s_stack[sp][tid] : lstack[sp - WV_STK];
     };
@@ -290,6 +301,7 @@ __global__ void __launch_bounds__(256, WV_BLOCKS) wv_extend(const __grid_constan
                         best_t = __uint_as_float(seed.x); seed_id = seed.y;
                     }
                     if (valid) {
+                        WV_CHECK(q < n);
                         slot = q;
                         limit = best_t * RT_PRUNE_SCALE + RT_PRUNE_ABS;
                         best_slot = EMPTY; best_pos = 0u; sp = 1; sptr = &s_stack[1][tid]; pend = EMPTY; literal = false;
@@ -378,8 +390,10 @@ __global__ void __launch_bounds__(256, WV_BLOCKS) wv_extend(const __grid_constan
                     const bool both = hl && hr, any = hl || hr;
                     const bool rf = hr && (!hl || er < el); // the right child is the nearer (or the only) one
                     const uint32_t nearc = rf ? rref : lref, farc = rf ? lref : rref;
+                    WV_CHECK(!both || sptr <= &s_stack[WV_STK - 1][tid]);
                     if (both) { *sptr = farc; sptr += 256; }
                     if (!any) sptr -= 256;
+                    WV_CHECK(sptr >= &s_stack[0][tid] && sptr <= &s_stack[WV_STK - 1][tid] + 256);
                     const uint32_t top = *sptr; // read only when nothing was hit (predicated)
                     cur = any ? nearc : top;
                 } else if (hl && hr) {
@@ -456,7 +470,7 @@ __device__ __forceinline__ void wv_finish_path(const KParams& p, const WvBuffers
         }
         const bool end = path_bounce(p, h, ray, tp, L, rng, depth); // SPEC.md steps 3.2-3.8 (rt_kernels.cuh)
         cont = !end;
-        if (end) WV_ST(w.lbuf + (size_t)sl * p.n_work + idx, make_float4(L.x, L.y, L.z, 1.0f)); // SPEC.md step 4, summed by wv_resolve
+        if (end) { WV_CHECK(sl < w.spp_wave && idx < p.n_work); WV_ST(w.lbuf + (size_t)sl * p.n_work + idx, make_float4(L.x, L.y, L.z, 1.0f)); } // SPEC.md step 4, summed by wv_resolve
     }
     unsigned m = __ballot_sync(full, cont);
     if (m) {
@@ -466,6 +480,7 @@ __device__ __forceinline__ void wv_finish_path(const KParams& p, const WvBuffers
         base = __shfl_sync(full, base, leader);
         if (cont) {
             uint32_t ns = base + __popc(m & ((1u << lane) - 1u));
+            WV_CHECK(ns < w.capacity);
             float4* st = w.state[qi ^ 1] + (size_t)ns * 4;
             WV_ST(st, make_float4(ray.o.x, ray.o.y, ray.o.z, __uint_as_float(rng.seed)));
             WV_ST(st + 1, make_float4(ray.d.x, ray.d.y, ray.d.z, __uint_as_float(depth)));
@@ -613,13 +628,14 @@ __device__ __forceinline__ void wv_shade_body(const KParams& p, const WvBuffers&
                             reinterpret_cast<uint4*>(p.hits)[(size_t)py * p.width + px] = make_uint4(0u, 0xFFFFFFFFu, __float_as_uint(FLT_MAX), 0xFFFFFFFFu);
                         }
                         L = L + mk(0.1f, 0.2f, 0.3f) * tp;
-                        WV_ST(w.lbuf + (size_t)sl * p.n_work + idx, make_float4(L.x, L.y, L.z, 1.0f));
+                        { WV_CHECK(sl < w.spp_wave && idx < p.n_work); WV_ST(w.lbuf + (size_t)sl * p.n_work + idx, make_float4(L.x, L.y, L.z, 1.0f)); }
                     }
                 }
             }
             const unsigned hm = __ballot_sync(full, heavy);
             if (heavy) {
                 const uint32_t e = queued_now + (uint32_t)__popc(hm & ((1u << lane) - 1u));
+                WV_CHECK(e < 64u);
                 my_list[0][e] = i; my_list[1][e] = hr.x; my_list[2][e] = hr.y;
             }
             queued_now += (uint32_t)__popc(hm);
@@ -697,7 +713,9 @@ __device__ __forceinline__ void wv_shade_body(const KParams& p, const WvBuffers&
             if (lit) { // rare: the internal tree's answer does not stand for this ray -> wv_fallback (launched after this kernel)
                 // bit 31: the ray went through the internal tree and its winner failed certification (filtered re-search);
                 // clear: the tree could not be used at all (zero / tiny direction component, far origin)
-                w.fb_list[atomicAdd(&w.ctrl->n_fb, 1u)] = i | ((hr.y != WV_ID_MISS && kind == WV_KIND_TRI) ? 0x80000000u : 0u);
+                const uint32_t fe = atomicAdd(&w.ctrl->n_fb, 1u);
+                WV_CHECK(fe < w.capacity);
+                w.fb_list[fe] = i | ((hr.y != WV_ID_MISS && kind == WV_KIND_TRI) ? 0x80000000u : 0u);
             } else {
             if (b.hit) {
                 h.t = b.t; h.kind = 2u; h.prim = b.prim; h.material_id = b.mat;
@@ -718,7 +736,7 @@ __device__ __forceinline__ void wv_shade_body(const KParams& p, const WvBuffers&
             }
             const bool end = path_bounce(p, h, ray, tp, L, rng, depth); // SPEC.md steps 3.2-3.8 (rt_kernels.cuh)
             cont = !end;
-            if (end) WV_ST(w.lbuf + (size_t)sl * p.n_work + idx, make_float4(L.x, L.y, L.z, 1.0f)); // SPEC.md step 4, summed by wv_resolve
+            if (end) { WV_CHECK(sl < w.spp_wave && idx < p.n_work); WV_ST(w.lbuf + (size_t)sl * p.n_work + idx, make_float4(L.x, L.y, L.z, 1.0f)); } // SPEC.md step 4, summed by wv_resolve
             } // !lit
         }
         // ---- survivors become the compact path list of the next depth (order within the warp kept; the same
@@ -731,6 +749,8 @@ __device__ __forceinline__ void wv_shade_body(const KParams& p, const WvBuffers&
             base = __shfl_sync(full, base, leader);
             if (cont) {
                 uint32_t ns = base + __popc(m & ((1u << lane) - 1u));
+                WV_CHECK(ns < w.capacity);
+            WV_CHECK(ns < w.capacity);
                 float4* st = w.state[qi ^ 1] + (size_t)ns * 4;
                 WV_ST(st, make_float4(ray.o.x, ray.o.y, ray.o.z, __uint_as_float(rng.seed)));
                 WV_ST(st + 1, make_float4(ray.d.x, ray.d.y, ray.d.z, __uint_as_float(depth)));

@@ -161,6 +161,19 @@ def terrain_scene(nx, nz, seed=1, strategy=abi.BVH_AUTO):
     return sc.rebuild_bvh(strategy) if strategy is not None else sc
 
 
+def field_scene(n_tori=1996, seg=25, ring=10, gnx=40, gnz=25, seed=1, strategy=abi.BVH_AUTO):
+    """Field: tori at mixed scales scattered through a volume over a ground grid (not a height field).  The default
+    is exactly 1 000 000 triangles."""
+    v = np.zeros(n_tori * seg * ring + (gnx + 1) * (gnz + 1), dtype=abi.Vertex)
+    t = np.zeros(2 * n_tori * seg * ring + 2 * gnx * gnz, dtype=abi.Triangle)
+    m = np.zeros(3, dtype=abi.Material)
+    l = np.zeros(2, dtype=abi.Light)
+    cam = np.zeros((), dtype=abi.Camera)
+    load().rt_scene_field(n_tori, seg, ring, gnx, gnz, seed, _p(v), _p(t), _p(m), _p(l), _p(cam))
+    sc = Scene(cam, np.zeros(0, dtype=abi.Sphere), t, v, m, l, name=f"field{n_tori}")
+    return sc.rebuild_bvh(strategy) if strategy is not None else sc
+
+
 def cornell_scene(strategy=abi.BVH_AUTO):
     v = np.zeros(72, dtype=abi.Vertex)
     t = np.zeros(36, dtype=abi.Triangle)

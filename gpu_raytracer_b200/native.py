@@ -25,7 +25,7 @@ HOST_SYMBOLS = [
     "rt_material_metallic", "rt_material_glass", "rt_material_emissive", "rt_light_directional", "rt_light_point",
     "rt_light_spot", "rt_push_constants_new", "rt_push_constants_new_wavefront", "rt_default_scene",
     "rt_triangle_aabb", "rt_aabb_empty", "rt_aabb_union", "rt_aabb_center", "rt_aabb_surface_area",
-    "rt_bvh_max_nodes", "rt_bvh_build", "rt_bvh_has_cycle", "rt_scene_terrain", "rt_scene_cornell",
+    "rt_bvh_max_nodes", "rt_bvh_build", "rt_bvh_has_cycle", "rt_scene_terrain", "rt_scene_cornell", "rt_scene_field",
     "rt_gltf_load_file", "rt_gltf_load_memory", "rt_gltf_free", "rt_gltf_counts", "rt_gltf_triangles", "rt_gltf_vertices",
     "rt_gltf_materials", "rt_gltf_spheres", "rt_gltf_lights", "rt_gltf_cameras", "rt_gltf_textures",
     "rt_gltf_texture_data", "rt_gltf_warning", "rt_write_ppm_rgba8", "rt_write_png_rgba8", "rt_write_pfm_accum"]
@@ -84,6 +84,7 @@ def load():
         "rt_bvh_build": (i32, [vp, u64, vp, u64, i32, vp, vp, vp, vp]), "rt_bvh_has_cycle": (i32, [vp, u32]),
         "rt_scene_terrain": (None, [u32, u32, u32, vp, vp, vp, vp, vp]),
         "rt_scene_cornell": (None, [vp, vp, vp, vp, vp, vp]),
+        "rt_scene_field": (None, [u32, u32, u32, u32, u32, u32, vp, vp, vp, vp, vp]),
         "rt_gltf_load_file": (i32, [C.c_char_p, i32, C.POINTER(vp), C.c_char_p, u64]),
         "rt_gltf_load_memory": (i32, [vp, u64, C.c_char_p, i32, C.POINTER(vp), C.c_char_p, u64]),
         "rt_gltf_free": (None, [vp]), "rt_gltf_counts": (None, [vp, vp]),

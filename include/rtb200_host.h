@@ -75,6 +75,11 @@ void rt_scene_terrain(uint32_t nx, uint32_t nz, uint32_t seed, RtVertex* vertice
                       RtMaterial materials[3], RtLight lights[2], RtCamera* camera);
 /* Cornell box: 5 walls + 2 boxes + ceiling light quad = 36 triangles, 4 materials, 1 light.
  * vertices: room for 72; returns the vertex count through n_vertices. */
+/* Field: a non-height-field test scene (tree-quality study): n_tori closed tori of seg x ring quads at mixed scales
+ * and orientations scattered through a volume, above a flat ground grid.  Vertices n_tori*seg*ring + (gnx+1)(gnz+1),
+ * triangles 2*n_tori*seg*ring + 2*gnx*gnz.  No reference analogue (test/bench input). */
+void rt_scene_field(uint32_t n_tori, uint32_t seg, uint32_t ring, uint32_t gnx, uint32_t gnz, uint32_t seed,
+                    RtVertex* vertices, RtTriangle* triangles, RtMaterial materials[3], RtLight lights[2], RtCamera* camera);
 void rt_scene_cornell(RtVertex* vertices, uint32_t* n_vertices, RtTriangle triangles[36], RtMaterial materials[4],
                       RtLight lights[1], RtCamera* camera);
 

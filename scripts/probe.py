@@ -11,6 +11,8 @@ def scene(name):
         SCENES[name] = {"c3": lambda: (g.terrain_scene(1000, 500), 1920, 1080, 4, 4),
                         "c3p": lambda: (g.terrain_scene(1000, 500), 1920, 1080, 0, 0),
                         "c5": lambda: (g.terrain_scene(2500, 2000), 3840, 2160, 1, 4),
+                        "field": lambda: (g.field_scene(), 1920, 1080, 4, 4),
+                        "fieldsl": lambda: (g.field_scene(strategy=abi.BVH_SMALL_LEAF), 1920, 1080, 4, 4),
                         "c2": lambda: (g.terrain_scene(250, 200), 1920, 1080, 0, 0),
                         "c4": lambda: (g.cornell_scene(), 1024, 1024, 16, 8)}[name]()
     return SCENES[name]

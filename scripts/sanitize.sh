@@ -10,6 +10,11 @@ mkdir -p gpurun_out
 # the plain run first: a faulting program under a tool has left the GPU unusable before
 timeout 600 python -m pytest tests/test_gpu_parity.py -x -q -m gpu -k "$SUBSET" > gpurun_out/sanitize_plain.log 2>&1 || { echo "plain run failed"; tail -5 gpurun_out/sanitize_plain.log; exit 1; }
 tail -1 gpurun_out/sanitize_plain.log
+if [ "$TOOL" = "checked" ]; then
+  # compute-sanitizer is closed on this pool: the same subset against the -DRT_CHECKED build (device-side bounds asserts)
+  RTB200_LIB=$PWD/build/tune/checked.so timeout 900 python -m pytest tests/test_gpu_parity.py tests/test_zz_no_alloc.py -x -q -m gpu -k "not c5_10m" > gpurun_out/sanitize_checked_pytest.log 2>&1
+  echo "checked build exit $?"; tail -3 gpurun_out/sanitize_checked_pytest.log; exit 0
+fi
 EXTRA=""
 [ "$TOOL" = "initcheck" ] && EXTRA="--track-unused-memory no"
 timeout 3000 compute-sanitizer --tool $TOOL $EXTRA --target-processes all --print-limit 30 --log-file gpurun_out/sanitize_$TOOL.log \

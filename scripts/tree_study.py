@@ -231,7 +231,12 @@ def evaluate(sc, nodes, idx, w, h, label):
 def main():
     a = [int(x) for x in sys.argv[1:5]] if len(sys.argv) >= 5 else [500, 250, 960, 540]
     nx, nz, w, h = a
-    sc = g.terrain_scene(nx, nz, seed=1, strategy=abi.BVH_SMALL_LEAF)
+    if os.environ.get("STUDY_SCENE", "").startswith("field"):  # STUDY_SCENE=field:499 -> 499 tori + ground, not a height field
+        n_tori = int(os.environ["STUDY_SCENE"].partition(":")[2] or 499)
+        sc = g.field_scene(n_tori=n_tori, gnx=20, gnz=(250000 - 500 * n_tori) // 40 if n_tori == 499 else 25, strategy=abi.BVH_SMALL_LEAF)
+        print("field scene: %d tori, %d triangles" % (n_tori, len(sc.triangles)), flush=True)
+    else:
+        sc = g.terrain_scene(nx, nz, seed=1, strategy=abi.BVH_SMALL_LEAF)
     evaluate(sc, sc.bvh_nodes, sc.triangle_indices, w, h, "binned SAH <=4 (rt_bvh_build)")
     if len(sc.triangles) <= 100000:
         n, i = g.build_bvh(sc.triangles, sc.vertices, abi.BVH_STANDARD)
