@@ -1170,6 +1170,16 @@ int check_ready(RtContext* c) {
 
 extern "C" {
 
+// Bring the device-side re-layout (ORDERED / REBUILT policy buffers, internal LBVH) of the uploaded scene up to date
+// now instead of inside the next dispatch / frame: a host that double-buffers scenes over two contexts calls this from
+// its upload thread so that the next frame's launch finds everything ready.
+int rt_prepare_scene(RtContext* c) {
+    if (!c) return RT_ERR_INVALID_ARGUMENT;
+    if (!c->have_meta) return fail(c, RT_ERR_NOT_READY, "rt_update_scene_metadata has not been called");
+    CK(c, cudaSetDevice(c->device));
+    return prepare_relayout(c);
+}
+
 int rt_dispatch(RtContext* c, const RtPushConstants* pc) {
     int r = check_ready(c);
     if (r) return r;

@@ -6,7 +6,7 @@ from dataclasses import dataclass, field
 import numpy as np
 
 from . import abi
-from .native import load
+from .native import load_host as load  # host-only library: no CUDA code is mapped by scene preparation
 
 
 def _p(a):

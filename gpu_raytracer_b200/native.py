@@ -13,7 +13,7 @@ API_SYMBOLS = [
     "rt_mark_scene_metadata_dirty", "rt_mark_triangles_dirty", "rt_mark_materials_dirty", "rt_mark_textures_dirty",
     "rt_mark_texture_data_dirty", "rt_mark_all_dirty", "rt_needs_update", "rt_triangles_per_buffer",
     "rt_set_triangles_per_buffer",
-    "rt_get_metadata_offsets", "rt_dispatch", "rt_run_compute", "rt_render_frame", "rt_read_channel_rgba8",
+    "rt_get_metadata_offsets", "rt_prepare_scene", "rt_dispatch", "rt_run_compute", "rt_render_frame", "rt_read_channel_rgba8",
     "rt_read_composite_rgba8", "rt_read_accum_f32", "rt_write_accum_f32", "rt_read_hit_records", "rt_device_accum",
     "rt_device_composite", "rt_count_next_launch", "rt_read_counters", "rt_last_kernel_ms", "rt_launch_count",
     "rt_last_traversal", "rt_last_build_ms", "rt_last_segments", "rt_last_wavefront_counters", "rt_last_stage_ms", "rt_last_launch_table", "rt_probe_gather_bandwidth",
@@ -30,21 +30,17 @@ HOST_SYMBOLS = [
     "rt_gltf_materials", "rt_gltf_spheres", "rt_gltf_lights", "rt_gltf_cameras", "rt_gltf_textures",
     "rt_gltf_texture_data", "rt_gltf_warning", "rt_write_ppm_rgba8", "rt_write_png_rgba8", "rt_write_pfm_accum"]
 
+# The host-side encoders / builders / loaders (include/rtb200_host.h: no CUDA in them) are also built as a library of
+# their own, so that a process that only prepares scenes (tests of the host logic, the CPU reference arm of bench.py)
+# never maps the CUDA kernels.  The product library still contains them: one .so is all a host links.
+HOST_LIB_PATH = os.path.join(_HERE, "librtb200_host.so")
 _lib = None
+_host_lib = None
 
 
-def load():
-    """Load librtb200.so (once) and declare its prototypes."""
-    global _lib
-    if _lib is not None:
-        return _lib
-    if not os.path.exists(LIB_PATH):
-        raise RuntimeError(
-            f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
-            "(nvcc, sm_100a).  gpu_raytracer_b200 has no fallback path.")
-    lib = C.CDLL(LIB_PATH)
+def _signatures():
     vp, u32, u64, i32, f32 = C.c_void_p, C.c_uint32, C.c_uint64, C.c_int, C.c_float
-    sig = {
+    return {
         "rt_create": (i32, [i32, C.POINTER(vp)]), "rt_destroy": (None, [vp]), "rt_last_error": (C.c_char_p, [vp]),
         "rt_resize": (i32, [vp, u32, u32]), "rt_synchronize": (i32, [vp]),
         "rt_update_scene_metadata": (i32, [vp, vp, u32, vp, u32, vp, u32, vp, u32, vp, u32, vp]),
@@ -55,7 +51,7 @@ def load():
         "rt_mark_texture_data_dirty": (None, [vp]), "rt_mark_all_dirty": (None, [vp]),
         "rt_needs_update": (i32, [vp]), "rt_triangles_per_buffer": (u32, [vp]),
         "rt_set_triangles_per_buffer": (i32, [vp, u32]),
-        "rt_get_metadata_offsets": (i32, [vp, vp]), "rt_dispatch": (i32, [vp, vp]),
+        "rt_get_metadata_offsets": (i32, [vp, vp]), "rt_prepare_scene": (i32, [vp]), "rt_dispatch": (i32, [vp, vp]),
         "rt_run_compute": (i32, [vp, vp, i32]), "rt_render_frame": (i32, [vp, vp, vp]),
         "rt_read_channel_rgba8": (i32, [vp, u32, vp]), "rt_read_composite_rgba8": (i32, [vp, vp]),
         "rt_read_accum_f32": (i32, [vp, vp]), "rt_write_accum_f32": (i32, [vp, vp]),
@@ -94,8 +90,36 @@ def load():
         "rt_write_ppm_rgba8": (i32, [C.c_char_p, vp, u32, u32]), "rt_write_png_rgba8": (i32, [C.c_char_p, vp, u32, u32]),
         "rt_write_pfm_accum": (i32, [C.c_char_p, vp, u32, u32]),
     }
-    for name, (res, args) in sig.items():
+
+
+def _declare(lib, names):
+    sig = _signatures()
+    for name in names:
         fn = getattr(lib, name)  # AttributeError if the symbol is not exported
-        fn.restype, fn.argtypes = res, args
-    _lib = lib
+        fn.restype, fn.argtypes = sig[name]
     return lib
+
+
+def load():
+    """Load librtb200.so (once) and declare its prototypes."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(nvcc, sm_100a).  gpu_raytracer_b200 has no fallback path.")
+    _lib = _declare(C.CDLL(LIB_PATH), API_SYMBOLS + HOST_SYMBOLS)
+    return _lib
+
+
+def load_host():
+    """The host-only library (scene encoders, BVH builder, glTF loader, image writers); the product library if the
+    host-only one has not been built (it holds the same functions) or a tuning build is selected."""
+    global _host_lib
+    if _host_lib is None:
+        if os.path.exists(HOST_LIB_PATH) and "RTB200_LIB" not in os.environ:
+            _host_lib = _declare(C.CDLL(HOST_LIB_PATH), HOST_SYMBOLS)
+        else:
+            _host_lib = load()
+    return _host_lib

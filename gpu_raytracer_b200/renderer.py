@@ -251,7 +251,11 @@ class BufferManager:
     def needs_update(self):
         return bool(self.ctx.lib.rt_needs_update(self.ctx.handle))
 
-    def upload_scene(self, scene):
+    def prepare_scene(self):
+        """rt_prepare_scene: run the device-side re-layout / LBVH build of the uploaded scene now."""
+        self.ctx._ck(self.ctx.lib.rt_prepare_scene(self.ctx.handle))
+
+    def upload_scene(self, scene, prepare=False):
         """ComputeRenderer::update_buffers_and_bind_groups (src/compute.rs:109-134)."""
         _, off = self.update_scene_metadata(scene.spheres, scene.lights, scene.bvh_nodes, scene.triangle_indices,
                                             scene.vertices)
@@ -259,6 +263,8 @@ class BufferManager:
         self.update_materials(scene.materials)
         self.update_textures(scene.textures)
         self.update_texture_data(scene.texture_data)
+        if prepare:
+            self.prepare_scene()
         return off
 
 

@@ -138,6 +138,13 @@ int rt_set_triangles_per_buffer(RtContext* ctx, uint32_t triangles_per_buffer);
 /* offsets of the last metadata upload (what run_compute passes on, src/compute.rs:109-134) */
 int rt_get_metadata_offsets(const RtContext* ctx, RtSceneMetadataOffsets* out);
 
+/* ComputeRenderer::update_buffers_and_bind_groups ends with the bind-group rebuild (src/compute.rs:109-134,
+ * src/renderer.rs:496-520); its counterpart here is the device-side re-layout of the uploaded scene (two-child nodes,
+ * pre-gathered triangles, internal LBVH), which otherwise runs lazily inside the next dispatch / frame.  Calling it
+ * right after the rt_update_* calls lets a host that double-buffers scenes over two contexts do all per-scene work on
+ * its upload thread.  Idempotent; waits for the build. */
+int rt_prepare_scene(RtContext* ctx);
+
 /* ---- dispatch (src/compute.rs) */
 /* One reference dispatch: process_color_channel, src/compute.rs:212-251 —
  * main_cs over ceil(w/16) x ceil(h/16) groups with these push constants; writes
