@@ -60,7 +60,7 @@ for name, f in fam.items():
                      "fma_pipe_pct": g("fma"), "lsu_pipe_pct": g("lsu"), "l1_wavefronts_pct": g("l1wf"),
                      "warps_active_per_smsp": g("warps"), "warps_eligible_per_smsp": g("eligible")}
 root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-path = os.path.join(root, "profiles", "ncu_summary.json")
+path = os.environ.get("NCU_SUMMARY_OUT") or os.path.join(root, "profiles", "ncu_summary.json")
 try:
     allrec = json.load(open(path))
 except Exception:
