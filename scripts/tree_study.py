@@ -261,5 +261,72 @@ def main():
                 evaluate(sc, n, i, w, h, "%s leaf<=%d rot%d (%d) sah %.1f" % (name, L, it + 1, nr, tr.sah(L)))
 
 
-if __name__ == "__main__":
+if __name__ == "__main__" and not (len(sys.argv) > 1 and sys.argv[1] == "ploc"):
     main()
+
+
+def ploc(lo, hi, order, radius=16):
+    """PLOC (Meister & Bittner 2018) over the Morton order `order`: repeated merging of mutually nearest clusters within
+    `radius` positions.  Returns children (root = node 0, leaves = ~sorted slot) like radix_tree()."""
+    n = len(order)
+    clo, chi = lo[order].astype(np.float32).copy(), hi[order].astype(np.float32).copy()
+    cid = -(np.arange(n, dtype=np.int64) + 1)  # leaf k encoded as ~k = -(k+1)
+    nodes = []  # (left, right) in creation order
+    while len(cid) > 1:
+        m = len(cid)
+        best = np.full(m, np.inf, np.float32)
+        nn = np.full(m, -1, np.int64)
+        for d in range(1, min(radius, m - 1) + 1):
+            a = area(np.minimum(clo[:-d], clo[d:]), np.maximum(chi[:-d], chi[d:]))
+            i = np.arange(m - d)
+            upd = a < best[:-d]
+            best[:-d][upd] = a[upd]; nn[:-d][upd] = (i + d)[upd]
+            upd = a < best[d:]
+            best[d:][upd] = a[upd]; nn[d:][upd] = i[upd]
+        idx = np.arange(m)
+        mutual = (nn[nn] == idx) & (idx < nn)
+        left = idx[mutual]; right = nn[left]
+        base = len(nodes)
+        for l, r in zip(cid[left], cid[right]):
+            nodes.append((int(l), int(r)))
+        new_ids = base + np.arange(len(left))
+        clo[left] = np.minimum(clo[left], clo[right]); chi[left] = np.maximum(chi[left], chi[right])
+        cid[left] = new_ids
+        keep = np.ones(m, bool); keep[right] = False
+        clo, chi, cid = clo[keep], chi[keep], cid[keep]
+    t = len(nodes)
+    ch = np.zeros((t, 2), np.int64)
+    for k, (l, r) in enumerate(nodes):  # renumber: creation index k -> t - 1 - k (root = 0)
+        ch[t - 1 - k] = (l if l < 0 else t - 1 - l, r if r < 0 else t - 1 - r)
+    return ch
+
+
+def main_ploc():
+    a = [int(x) for x in sys.argv[2:6]] if len(sys.argv) >= 6 else [500, 250, 960, 540]
+    nx, nz, w, h = a
+    if os.environ.get("STUDY_SCENE", "").startswith("field"):
+        n_tori = int(os.environ["STUDY_SCENE"].partition(":")[2] or 499)
+        sc = g.field_scene(n_tori=n_tori, gnx=20, gnz=(250000 - 500 * n_tori) // 40 if n_tori == 499 else 25, strategy=abi.BVH_SMALL_LEAF)
+    else:
+        sc = g.terrain_scene(nx, nz, seed=1, strategy=abi.BVH_SMALL_LEAF)
+    evaluate(sc, sc.bvh_nodes, sc.triangle_indices, w, h, "binned SAH <=4 (rt_bvh_build)")
+    lo, hi = tri_boxes(sc)
+    ext = (0.5 * (lo + hi)).max(0) - (0.5 * (lo + hi)).min(0)
+    axes = (0, 1, 2) if ext.min() >= 0.125 * ext.max() else tuple(int(k) for k in np.argsort(-ext)[:2])
+    axes = tuple(sorted(axes))
+    keys = morton(lo, hi, axes)
+    order = np.argsort(keys, kind="stable")
+    ch, rg = radix_tree(keys[order])
+    for L in (2,):
+        tr = Tree(ch, rg, lo[order], hi[order])
+        n, i = tr.flatten(order, L)
+        evaluate(sc, n, i, w, h, "morton%s radix tree leaf<=%d sah %.1f" % (axes, L, tr.sah(L)))
+        for r in [int(x) for x in os.environ.get("STUDY_RADIUS", "8,16,32").split(",")]:
+            pc = ploc(lo, hi, order, r)
+            tp = Tree(pc, np.zeros((len(pc), 2), np.int64), lo[order], hi[order])
+            n, i = tp.flatten(order, L)
+            evaluate(sc, n, i, w, h, "PLOC r=%d leaf<=%d sah %.1f" % (r, L, tp.sah(L)))
+
+
+if __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "ploc":
+    main_ploc()
