@@ -873,3 +873,44 @@ def test_literal_fallback_rays_take_the_fallback_kernel(monkeypatch, literal_wal
         assert np.array_equal(ctx.read_accum().view(np.uint32), ref["accum"].view(np.uint32))
         check_hits(ctx.read_hits(), ref["hits"])
         ctx.close()
+
+
+def test_two_contexts_double_buffered_from_two_threads():
+    """The e2e mode of bench.py: two contexts on one GPU, an uploader thread preparing the next scene (rt_update_* +
+    rt_prepare_scene) in one context while the main thread renders in the other.  Frames must equal the serial ones."""
+    from concurrent.futures import ThreadPoolExecutor
+    w, h = 320, 180
+    scenes = [g.default_scene(), g.terrain_scene(60, 45, strategy=abi.BVH_CHUNKED), g.cornell_scene(),
+              g.terrain_scene(40, 30, strategy=abi.BVH_SMALL_LEAF), g.default_scene()]
+    kw = dict(mode=abi.MODE_PATH, spp=2, max_depth=3, base_seed=5, outputs=abi.OUT_ACCUM | abi.OUT_COMPOSITE)
+    want = []
+    one = g.Context(0, w, h)
+    for s in scenes:
+        bm = g.BufferManager(one)
+        bm.mark_all_dirty()
+        bm.upload_scene(s)
+        g.ComputeRenderer(one).render_frame(s.camera, **kw)
+        want.append((one.read_accum(), one.read_composite(), one.last_traversal))
+    one.close()
+    lanes = [g.Context(0, w, h), g.Context(0, w, h)]
+    bms = [g.BufferManager(c) for c in lanes]
+
+    def upload(k, s):
+        bms[k].mark_all_dirty()
+        bms[k].upload_scene(s, prepare=True)
+
+    pool = ThreadPoolExecutor(max_workers=1)
+    pending = pool.submit(upload, 0, scenes[0])
+    for i, s in enumerate(scenes):
+        pending.result()
+        if i + 1 < len(scenes):
+            pending = pool.submit(upload, (i + 1) % 2, scenes[i + 1])  # runs beside this frame, other context
+        c = lanes[i % 2]
+        g.ComputeRenderer(c).render_frame(s.camera, **kw)
+        acc, comp = c.read_accum(), c.read_composite()
+        assert c.last_traversal == want[i][2]
+        assert np.array_equal(acc.view(np.uint32), want[i][0].view(np.uint32)), i
+        assert np.array_equal(comp, want[i][1]), i
+    pool.shutdown()
+    for c in lanes:
+        c.close()
