@@ -129,3 +129,22 @@ def test_aabb_helpers():
     assert np.all(np.isposinf(e["min"])) and np.all(np.isneginf(e["max"]))
     lib.rt_aabb_union(e.ctypes.data, a.ctypes.data, u.ctypes.data)  # union with empty is identity
     assert list(u["min"]) == [0, 0, 0] and list(u["max"]) == [1, 1, 1]
+
+
+def test_committed_ncu_summary_belongs_to_the_committed_sources():
+    """The roofline's traffic / hit-rate figures in bench.py come from profiles/ncu_summary.json; every workload
+    recorded there must have been captured from the native sources in this tree (bench.source_hash), so a change
+    to csrc/ or include/ without a fresh capture fails here instead of shipping stale evidence."""
+    import importlib.util
+    import json
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    spec = importlib.util.spec_from_file_location("bench_for_hash", os.path.join(root, "bench.py"))
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+    with open(os.path.join(root, "profiles", "ncu_summary.json")) as f:
+        summary = json.load(f)
+    assert summary, "profiles/ncu_summary.json is empty"
+    want = bench.source_hash()
+    stale = {w: rec.get("src_hash") for w, rec in summary.items() if rec.get("src_hash") != want}
+    assert not stale, "captured from another build than %s: %s" % (want, stale)
+    assert "c3" in summary
