@@ -875,6 +875,43 @@ def test_literal_fallback_rays_take_the_fallback_kernel(monkeypatch, literal_wal
         ctx.close()
 
 
+def test_filtered_research_rays_equal_the_oracle():
+    """Rays whose internal-tree winner fails its certification are searched again by wv_fallback with the filter, one
+    warp per ray, the lanes sharing the node tests (wv_filtered_search_warp).  Scenes that produce such rays (a field
+    of tori over a flat ground; a terrain seen from 10 / 15 scene sizes away) must still equal the oracle bit for bit,
+    instrumented and plain launches alike, and the megakernel (literal walk for those rays)."""
+    field = g.field_scene(n_tori=120, strategy=abi.BVH_CHUNKED)
+    terrain = g.terrain_scene(120, 90, strategy=abi.BVH_CHUNKED)
+    ext = float(np.abs(terrain.vertices["position"]).max())
+    cases = [(field, field.camera, 384, 216, 8, 4)]
+    for dist in (10.0, 15.0):
+        cam = terrain.camera.copy()
+        cam["position"] = -cam["direction"] * np.float32(dist * ext)
+        cam["fov"] = np.float32(2.0 / dist * 40.0)
+        cases.append((terrain, cam, 256, 144, 4, 3))
+    total_fb = 0
+    for s, cam, w, h, spp, depth in cases:
+        ref = ob.render_path(s, w, h, spp=spp, max_depth=depth, base_seed=11, camera=cam)
+        ctx = g.Context(0, w, h)
+        g.BufferManager(ctx).upload_scene(s)
+        cr = g.ComputeRenderer(ctx)
+        kw = dict(mode=abi.MODE_PATH, spp=spp, max_depth=depth, base_seed=11, traversal=abi.TRAVERSAL_REBUILT,
+                  outputs=abi.OUT_ACCUM | abi.OUT_HITS | abi.OUT_COMPOSITE)
+        ctx.count_next_launch()
+        cr.render_frame(cam, variant=4, **kw)
+        n_fb = ctx.read_counters()["literal_fallbacks"]
+        print("filtered re-search: %s %dx%d: %d of %d segments" % (s.name, w, h, n_fb, ctx.last_segments))
+        total_fb += n_fb
+        for variant in (None, 4, 1):  # the instrumented frame above; a plain wave-engine frame; the megakernel
+            if variant is not None:
+                cr.render_frame(cam, variant=variant, **kw)
+            assert ctx.last_segments == ref["counters"]["rays"]
+            assert np.array_equal(ctx.read_accum().view(np.uint32), ref["accum"].view(np.uint32)), (s.name, variant)
+            check_hits(ctx.read_hits(), ref["hits"])
+        ctx.close()
+    assert total_fb > 0, "no certification failure in any case: the filtered search was not exercised"
+
+
 def test_two_contexts_double_buffered_from_two_threads():
     """The e2e mode of bench.py: two contexts on one GPU, an uploader thread preparing the next scene (rt_update_* +
     rt_prepare_scene) in one context while the main thread renders in the other.  Frames must equal the serial ones."""
