@@ -509,12 +509,14 @@ def run_b200(args, wl, world, rank, local):
             ln["bm"].mark_all_dirty()
             ln["bm"].upload_scene(ps, prepare=True)  # H2D + host validation + GPU re-layout + LBVH build, waits for them
 
-        def lane_frame(ln):
+        def lane_render(ln):
             if path:
                 ln["cr"].render_frame(ps.camera, mode=abi.MODE_PATH, spp=wl["spp"], max_depth=wl["depth"], base_seed=1,
                                       outputs=ln["outputs"], tile_stride=stride, tile_phase=phase, traversal=trav, variant=args.variant)
             else:
                 ln["cr"].render_frame(ps.camera, outputs=ln["outputs"], tile_stride=stride, tile_phase=phase, traversal=trav)
+
+        def lane_gather(ln):
             if ln["peer"] is not None:
                 ln["peer"].finish()
             elif ln["gather"] is not None:
@@ -527,6 +529,15 @@ def run_b200(args, wl, world, rank, local):
                         ln["gather"].run(lambda dst: c_.pack_tiles(tiles.WHAT_COMPOSITE, world, rank, dst.data_ptr()),
                                          lambda src, r: c_.unpack_tiles(tiles.WHAT_COMPOSITE, world, r, src.data_ptr()))
 
+        # D2H of the assembled frame, rank 0: a copy of the lane's composite (Context.composite_cuda_array, zero-copy
+        # view of rt_device_composite) into that lane's pinned image, enqueued on the lane's stream behind the frame and
+        # its gather, NOT waited for: it runs beside the next step's frame on the other lane.  Order that makes this
+        # safe with the peer-store epilogue: rank 0 waits for step i-1's copy (host) before it enqueues step i's
+        # barrier, and a peer launches step i+1 (which stores into the image step i-1 was read from) only after its
+        # host has seen step i's barrier complete.
+        host_t = [torch.empty((h, w, 4), dtype=torch.uint8).pin_memory() for _ in lanes]
+        dev_t = [torch.as_tensor(ln["ctx"].composite_cuda_array(), device="cuda:%d" % local) for ln in lanes] if rank == 0 else None
+        read_done = [None, None]
         pool = ThreadPoolExecutor(max_workers=1)
         n_total = args.warmup + args.steps
         barrier(world)
@@ -540,21 +551,39 @@ def run_b200(args, wl, world, rank, local):
             pending.result()                                  # step i's scene is resident and re-laid-out
             if i + 1 < n_total:
                 pending = pool.submit(lane_upload, lanes[(i + 1) % 2])  # step i+1's upload runs beside this frame
-            lane_frame(ln)
+            lane_render(ln)
+            if read_done[(i + 1) % 2] is not None:
+                read_done[(i + 1) % 2].synchronize()          # step i-1's image is in host memory (other lane)
+            lane_gather(ln)
+            # the host waits for the frame (and its gather); only the copy below stays in flight.  (Letting the host run
+            # ahead of the frame as well, with a GPU-side event between consecutive frames, was measured SLOWER on C3:
+            # 15.97 ms per step against 14.54, i.e. no better than the serial mode.)
+            ln["ctx"].synchronize()
             if rank == 0:
-                ln["ctx"].read_composite(host_img)            # D2H of the gathered frame (waits for the lane's stream)
-            else:
-                ln["ctx"].synchronize()
+                with torch.cuda.stream(ln["stream"]):
+                    host_t[i % 2].copy_(dev_t[i % 2], non_blocking=True)
+                    read_done[i % 2] = torch.cuda.Event()
+                    read_done[i % 2].record(ln["stream"])
+        for k in range(2):
+            if read_done[k] is not None:
+                read_done[k].synchronize()                    # the last images have arrived: inside the timed region
         pipe_total = max_over_ranks((time.perf_counter() - t0) * 1e3, world)
         pool.shutdown()
-        pipe = {"value": seg_per_frame * args.steps / (pipe_total * 1e-3) / 1e6, "ms_per_step": pipe_total / args.steps}
+        pipe = {"value": seg_per_frame * args.steps / (pipe_total * 1e-3) / 1e6, "ms_per_step": pipe_total / args.steps,
+                "d2h": "asynchronous copy on the lane's stream, overlapped with the next step's frame"}
         # leave the serial lane's image in host_img for the assembled-frame check below
         frame()
         if rank == 0:
-            pipe["image_equals_serial_lane"] = bool(np.array_equal(host_img, ctx.read_composite()))
+            last = host_t[(n_total - 1) % 2].numpy()
+            pipe["image_equals_serial_lane"] = bool(np.array_equal(last, ctx.read_composite())) and \
+                bool(np.array_equal(host_t[n_total % 2].numpy(), last) or n_total < 2)
             ctx.read_composite(host_img)
+            del last
         else:
             ctx.synchronize()
+        # torch's pinned-memory allocator records an event on every stream a block was used on when the block is
+        # freed: free them while the lanes' streams still exist
+        del host_t, dev_t, read_done
         if peer2 is not None:
             peer2.close()
         barrier(world)

@@ -19,6 +19,15 @@ def _p(a):
     return a.ctypes.data_as(C.c_void_p) if a is not None and a.size else None
 
 
+class _CudaArray:
+    """Carrier of `__cuda_array_interface__` (version 3) for a device buffer a context owns."""
+
+    def __init__(self, ptr, shape, typestr, owner):
+        self._owner = owner  # keeps the context alive as long as the view
+        self.__cuda_array_interface__ = {"shape": tuple(int(x) for x in shape), "typestr": typestr,
+                                         "data": (int(ptr), False), "version": 3, "strides": None}
+
+
 class Context:
     """RenderState.device/queue + output textures (src/renderer.rs:93-246, 452-475)."""
 
@@ -142,6 +151,22 @@ class Context:
     @property
     def device_composite(self):
         return int(self.lib.rt_device_composite(self.handle))
+
+    @property
+    def device_accum(self):
+        return int(self.lib.rt_device_accum(self.handle))
+
+    def composite_cuda_array(self):
+        """Zero-copy view of the composite image (rt_device_composite) for CUDA-array consumers: an object carrying
+        `__cuda_array_interface__` (shape (H, W, 4) uint8), e.g. `torch.as_tensor(ctx.composite_cuda_array(),
+        device="cuda")`.  A host that reads frames back without stalling enqueues its own copy of this view on
+        `ctx.stream` (stream-ordered after the frame) instead of the waiting rt_read_composite_rgba8.  The view is
+        valid until the next rt_resize / rt_destroy."""
+        return _CudaArray(self.device_composite, (self.height, self.width, 4), "|u1", self)
+
+    def accum_cuda_array(self):
+        """The accumulation buffer (rt_device_accum) the same way: shape (H, W, 4) float32 (rgb sums, sample count)."""
+        return _CudaArray(self.device_accum, (self.height, self.width, 4), "<f4", self)
 
     def probe_gather_bandwidth(self, footprint_bytes):
         """GB/s of random independent 32-byte sector loads over a footprint (traversal roofline denominators)."""

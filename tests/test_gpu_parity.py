@@ -912,6 +912,39 @@ def test_filtered_research_rays_equal_the_oracle():
     assert total_fb > 0, "no certification failure in any case: the filtered search was not exercised"
 
 
+def test_cuda_array_views_and_stream_ordered_copy():
+    """Context.composite_cuda_array / accum_cuda_array: zero-copy views of rt_device_composite / rt_device_accum for
+    CUDA-array consumers.  A copy enqueued on the context's stream right after a frame (no rt_read_* wait) must
+    deliver that frame: the asynchronous read-back of bench.py's pipelined e2e mode."""
+    import torch
+    s = g.default_scene()
+    w, h = 333, 222
+    ctx = g.Context(0, w, h)
+    g.BufferManager(ctx).upload_scene(s)
+    comp = torch.as_tensor(ctx.composite_cuda_array(), device="cuda:0")
+    acc = torch.as_tensor(ctx.accum_cuda_array(), device="cuda:0")
+    assert comp.shape == (h, w, 4) and comp.dtype == torch.uint8 and comp.data_ptr() == ctx.device_composite
+    assert acc.shape == (h, w, 4) and acc.dtype == torch.float32 and acc.data_ptr() == ctx.device_accum
+    stream = torch.cuda.ExternalStream(ctx.stream, device=0)
+    host_c = torch.empty((h, w, 4), dtype=torch.uint8).pin_memory()
+    host_a = torch.empty((h, w, 4), dtype=torch.float32).pin_memory()
+    for seed in (3, 4):
+        g.ComputeRenderer(ctx).render_frame(s.camera, mode=abi.MODE_PATH, spp=4, max_depth=3, base_seed=seed,
+                                            outputs=abi.OUT_ACCUM | abi.OUT_COMPOSITE)
+        with torch.cuda.stream(stream):
+            host_c.copy_(comp, non_blocking=True)
+            host_a.copy_(acc, non_blocking=True)
+            done = torch.cuda.Event()
+            done.record(stream)
+        done.synchronize()
+        assert np.array_equal(host_c.numpy(), ctx.read_composite())
+        assert np.array_equal(host_a.numpy().view(np.uint32), ctx.read_accum().view(np.uint32))
+    # torch's pinned-memory allocator records an event on the streams a block was used on when it is freed: free the
+    # host tensors (and the views) while the context's stream still exists
+    del host_c, host_a, comp, acc, done, stream
+    ctx.close()
+
+
 def test_two_contexts_double_buffered_from_two_threads():
     """The e2e mode of bench.py: two contexts on one GPU, an uploader thread preparing the next scene (rt_update_* +
     rt_prepare_scene) in one context while the main thread renders in the other.  Frames must equal the serial ones."""
