@@ -115,8 +115,8 @@ def parse_args():
                     help="N > 1: load-balancing steps during warm-up (explicit per-rank tile lists adjusted on the previous "
                          "frames' per-rank GPU times, tiles.rebalance); 0 keeps tile i -> rank i %% N")
     ap.add_argument("--pipeline", type=int, default=1,
-                    help="1: also measure e2e double-buffered over two contexts per GPU (upload + build of step i+1 beside the "
-                         "render of step i) and report it as `e2e` (the serial figure stays in `e2e_serial`); 0: serial only")
+                    help="1: also measure e2e pipelined over three contexts per GPU (upload + build two steps ahead beside the running "
+                         "frames, asynchronous read-back) and report it as `e2e` (the serial figure stays in `e2e_serial`); 0: serial only")
     ap.add_argument("--gather", default="peer", choices=["peer", "nccl"],
                     help="N > 1: how finished tiles reach rank 0: peer = P2P stores from the render kernels into rank 0's "
                          "frame (CUDA IPC) + a 4-byte NCCL all-reduce as barrier; nccl = pack + dist.gather + unpack")
@@ -484,26 +484,36 @@ def run_b200(args, wl, world, rank, local):
     e2e_value = seg_per_frame * args.steps / (e2e_total * 1e-3) / 1e6
 
     # ---- e2e, pipelined: the same work per step (upload of every scene buffer from pinned host memory, device
-    # re-layout + LBVH build, frame, gather, D2H of the image), double-buffered over TWO contexts per GPU: an uploader
-    # thread prepares step i+1's scene in the other context while step i renders.  What a host with a scene that
-    # changes every frame does with this API (contexts are independent; one thread per context).
+    # re-layout + LBVH build, frame, gather, D2H of the image), over THREE contexts ("lanes") per GPU.  What a host with a
+    # scene that changes every frame does with this API (contexts are independent; one thread per context):
+    #   * an uploader thread prepares step i+2's scene while step i renders.  Beside a running frame an upload takes one
+    #     frame time (its 25 small build launches only get SMs at the frame's kernel boundaries), so the lead has to be
+    #     two steps for the host to be able to enqueue frame i+1 before frame i ends (profiles/r2zd_e2e_pipeline_timeline_c3.log);
+    #   * frames follow each other on the GPU without a host round trip (a GPU-side event between consecutive frames);
+    #   * rank 0 reads the assembled image with an asynchronous copy of Context.composite_cuda_array() (zero-copy view
+    #     of rt_device_composite) on the lane's stream, and waits for it one step later.
+    # Order that keeps the peer-store epilogue safe: a rank waits (host) for step i-1 to be complete - rank 0: its image
+    # has arrived; others: its barrier has completed - after it has enqueued frame i and BEFORE it enqueues barrier i.
+    # So a peer launches frame i+3, which stores into the image frame i was read from, only after it has seen barrier
+    # i+1 complete, and rank 0 enqueued that barrier only after the image of frame i had arrived.
     pipe = None
     if args.pipeline:
         from concurrent.futures import ThreadPoolExecutor
-        ctx2 = g.Context(local, w, h)
-        bm2, cr2 = g.BufferManager(ctx2), g.ComputeRenderer(ctx2)
-        stream2 = torch.cuda.ExternalStream(ctx2.stream, device=local)
-        bm2.upload_scene(ps, prepare=True)
-        outputs2, peer2, gather2 = abi.OUT_ACCUM | abi.OUT_COMPOSITE, None, None
-        if peer is not None:
-            peer2 = tiles.PeerFrame(dist, torch, ctx2, stream2)
-            outputs2 |= peer2.extra_outputs
-        elif world > 1:
-            gather2 = make_gather()
-        if lists is not None:
-            ctx2.set_tile_list(lists[rank])
-        lanes = [dict(ctx=ctx, bm=bm, cr=cr, stream=stream, peer=peer, gather=gather, outputs=outputs),
-                 dict(ctx=ctx2, bm=bm2, cr=cr2, stream=stream2, peer=peer2, gather=gather2, outputs=outputs2)]
+        N_LANES, LEAD = 3, 2
+        lanes = [dict(ctx=ctx, bm=bm, cr=cr, stream=stream, peer=peer, gather=gather, outputs=outputs)]
+        for _ in range(N_LANES - 1):
+            c_ = g.Context(local, w, h)
+            ln = dict(ctx=c_, bm=g.BufferManager(c_), cr=g.ComputeRenderer(c_), stream=torch.cuda.ExternalStream(c_.stream, device=local),
+                      peer=None, gather=None, outputs=abi.OUT_ACCUM | abi.OUT_COMPOSITE)
+            ln["bm"].upload_scene(ps, prepare=True)
+            if peer is not None:
+                ln["peer"] = tiles.PeerFrame(dist, torch, c_, ln["stream"])
+                ln["outputs"] |= ln["peer"].extra_outputs
+            elif world > 1:
+                ln["gather"] = make_gather()
+            if lists is not None:
+                c_.set_tile_list(lists[rank])
+            lanes.append(ln)
 
         def lane_upload(ln):
             ln["bm"].mark_all_dirty()
@@ -529,65 +539,91 @@ def run_b200(args, wl, world, rank, local):
                         ln["gather"].run(lambda dst: c_.pack_tiles(tiles.WHAT_COMPOSITE, world, rank, dst.data_ptr()),
                                          lambda src, r: c_.unpack_tiles(tiles.WHAT_COMPOSITE, world, r, src.data_ptr()))
 
-        # D2H of the assembled frame, rank 0: a copy of the lane's composite (Context.composite_cuda_array, zero-copy
-        # view of rt_device_composite) into that lane's pinned image, enqueued on the lane's stream behind the frame and
-        # its gather, NOT waited for: it runs beside the next step's frame on the other lane.  Order that makes this
-        # safe with the peer-store epilogue: rank 0 waits for step i-1's copy (host) before it enqueues step i's
-        # barrier, and a peer launches step i+1 (which stores into the image step i-1 was read from) only after its
-        # host has seen step i's barrier complete.
         host_t = [torch.empty((h, w, 4), dtype=torch.uint8).pin_memory() for _ in lanes]
         dev_t = [torch.as_tensor(ln["ctx"].composite_cuda_array(), device="cuda:%d" % local) for ln in lanes] if rank == 0 else None
-        read_done = [None, None]
+        step_done = [None] * N_LANES   # per lane: rank 0 - the image has arrived; other ranks - the barrier has completed
+        render_done = None
+        arrived = {}                   # step -> wall clock at which this rank saw it complete
         pool = ThreadPoolExecutor(max_workers=1)
         n_total = args.warmup + args.steps
         barrier(world)
         torch.cuda.synchronize()
-        pending = pool.submit(lane_upload, lanes[0])
-        t0 = None
+        pending = {k: pool.submit(lane_upload, lanes[k % N_LANES]) for k in range(min(LEAD, n_total))}
+        for f in list(pending.values()):
+            f.result()                                        # the two-step lead exists before the first frame (untimed)
+        barrier(world)
+        t_begin = time.perf_counter()
+        trace = [] if os.environ.get("RTB200_E2E_TRACE") else None  # per step: host time stamps + GPU events (timeline to stderr)
+        ms_now = lambda: (time.perf_counter() - t_begin) * 1e3
+        if trace is not None:
+            ev_base = torch.cuda.Event(enable_timing=True)
+            ev_base.record(lanes[0]["stream"])
         for i in range(n_total):
-            if i == args.warmup:
-                t0 = time.perf_counter()
-            ln = lanes[i % 2]
-            pending.result()                                  # step i's scene is resident and re-laid-out
-            if i + 1 < n_total:
-                pending = pool.submit(lane_upload, lanes[(i + 1) % 2])  # step i+1's upload runs beside this frame
+            ln = lanes[i % N_LANES]
+            row = [ms_now()] if trace is not None else None
+            pending.pop(i).result()                           # step i's scene is resident and re-laid-out
+            if row is not None:
+                row.append(ms_now())
+            if i + LEAD < n_total:
+                pending[i + LEAD] = pool.submit(lane_upload, lanes[(i + LEAD) % N_LANES])
+            if render_done is not None:
+                ln["stream"].wait_event(render_done)          # GPU-side: one frame after the other, no host round trip
+            if row is not None:
+                ev_start = torch.cuda.Event(enable_timing=True)
+                ev_start.record(ln["stream"])
             lane_render(ln)
-            if read_done[(i + 1) % 2] is not None:
-                read_done[(i + 1) % 2].synchronize()          # step i-1's image is in host memory (other lane)
+            render_done = torch.cuda.Event(enable_timing=trace is not None)
+            render_done.record(ln["stream"])
+            if row is not None:
+                row.append(ms_now())
+            if i > 0:
+                step_done[(i - 1) % N_LANES].synchronize()    # step i-1 is complete (see the order above)
+                arrived[i - 1] = time.perf_counter()
+            if row is not None:
+                row.append(ms_now())
             lane_gather(ln)
-            # the host waits for the frame (and its gather); only the copy below stays in flight.  (Letting the host run
-            # ahead of the frame as well, with a GPU-side event between consecutive frames, was measured SLOWER on C3:
-            # 15.97 ms per step against 14.54, i.e. no better than the serial mode.)
-            ln["ctx"].synchronize()
-            if rank == 0:
-                with torch.cuda.stream(ln["stream"]):
-                    host_t[i % 2].copy_(dev_t[i % 2], non_blocking=True)
-                    read_done[i % 2] = torch.cuda.Event()
-                    read_done[i % 2].record(ln["stream"])
-        for k in range(2):
-            if read_done[k] is not None:
-                read_done[k].synchronize()                    # the last images have arrived: inside the timed region
-        pipe_total = max_over_ranks((time.perf_counter() - t0) * 1e3, world)
+            with torch.cuda.stream(ln["stream"]):
+                if rank == 0:
+                    host_t[i % N_LANES].copy_(dev_t[i % N_LANES], non_blocking=True)
+                step_done[i % N_LANES] = torch.cuda.Event(enable_timing=trace is not None)
+                step_done[i % N_LANES].record(ln["stream"])
+            if row is not None:
+                trace.append((row, ev_start, render_done, step_done[i % N_LANES]))
+        step_done[(n_total - 1) % N_LANES].synchronize()      # the last image has arrived
+        arrived[n_total - 1] = time.perf_counter()
+        # K steps in steady state: wall clock from the arrival of the last warm-up step's image to the last image's
+        pipe_total = max_over_ranks((arrived[n_total - 1] - (arrived[args.warmup - 1] if args.warmup > 0 else t_begin)) * 1e3, world)
         pool.shutdown()
+        for ln in lanes:
+            ln["ctx"].synchronize()
+        if trace is not None:
+            sys.stderr.write("[e2e trace rank %d] step | host: loop start, upload ready, render() returned, step i-1 seen | GPU: frame start, frame end, step complete\n" % rank)
+            for i, (row, e_s, e_r, e_d) in enumerate(trace):
+                sys.stderr.write("[e2e trace rank %d] %4d | %8.2f %8.2f %8.2f %8.2f | %8.2f %8.2f %8.2f\n" % (
+                    rank, i, row[0], row[1], row[2], row[3], ev_base.elapsed_time(e_s), ev_base.elapsed_time(e_r), ev_base.elapsed_time(e_d)))
+            del trace
         pipe = {"value": seg_per_frame * args.steps / (pipe_total * 1e-3) / 1e6, "ms_per_step": pipe_total / args.steps,
-                "d2h": "asynchronous copy on the lane's stream, overlapped with the next step's frame"}
+                "lanes": N_LANES, "uploads_ahead": LEAD,
+                "d2h": "asynchronous copy on the lane's stream, waited for one step later",
+                "timed": "wall clock between the arrival of the last warm-up image and of the last image (steady state)"}
         # leave the serial lane's image in host_img for the assembled-frame check below
         frame()
         if rank == 0:
-            last = host_t[(n_total - 1) % 2].numpy()
-            pipe["image_equals_serial_lane"] = bool(np.array_equal(last, ctx.read_composite())) and \
-                bool(np.array_equal(host_t[n_total % 2].numpy(), last) or n_total < 2)
+            imgs = [host_t[k].numpy() for k in range(min(N_LANES, n_total))]
+            pipe["image_equals_serial_lane"] = bool(all(np.array_equal(x, ctx.read_composite()) for x in imgs))
             ctx.read_composite(host_img)
-            del last
+            del imgs
         else:
             ctx.synchronize()
         # torch's pinned-memory allocator records an event on every stream a block was used on when the block is
         # freed: free them while the lanes' streams still exist
-        del host_t, dev_t, read_done
-        if peer2 is not None:
-            peer2.close()
+        del host_t, dev_t, step_done, render_done
+        for ln in lanes[1:]:
+            if ln["peer"] is not None:
+                ln["peer"].close()
         barrier(world)
-        ctx2.close()
+        for ln in lanes[1:]:
+            ln["ctx"].close()
 
     # ---- N > 1: the assembled frame on rank 0 must equal rank 0's own render of the whole frame
     assembled_ok = None
@@ -789,12 +825,14 @@ def run_b200(args, wl, world, rank, local):
         "e2e": ({"value": pipe["value"], "unit": "Mrays/s", "mode": "pipelined", "h2d_bytes_per_step": h2d_bytes,
                  "d2h_bytes_per_step": int(host_img.nbytes), "ms_per_step": pipe["ms_per_step"],
                  "how": "every step: all scene buffers host->device from pinned memory + host validation + GPU re-layout + LBVH "
-                        "build + frame + gather + device->host read of the image; double-buffered over two contexts per GPU, "
-                        "an uploader thread prepares step i+1 while step i renders (wall clock over the steps, max over ranks)",
-                 "image_equals_serial_lane": pipe.get("image_equals_serial_lane")} if (pipe and pipe["value"] >= e2e_value) else
+                        "build + frame + gather + device->host read of the image; pipelined over three contexts per GPU: an "
+                        "uploader thread prepares step i+2 while step i renders, frames follow each other through a GPU-side "
+                        "event, the image copy is asynchronous and waited for one step later (wall clock between the arrival of "
+                        "the last warm-up image and of the last image, max over ranks)",
+                 "lanes": pipe.get("lanes"), "image_equals_serial_lane": pipe.get("image_equals_serial_lane")} if (pipe and pipe["value"] >= e2e_value) else
                 {"value": e2e_value, "unit": "Mrays/s", "mode": "serial", "h2d_bytes_per_step": h2d_bytes,
                  "d2h_bytes_per_step": int(host_img.nbytes), "ms_per_step": e2e_total / args.steps,
-                 "how": "serial: upload, build, frame, read back one after the other in one context (the double-buffered "
+                 "how": "serial: upload, build, frame, read back one after the other in one context (the pipelined "
                         "mode was %s)" % ("not measured" if not pipe else "slower on this workload: %.0f Mrays/s" % pipe["value"])}),
         "e2e_serial": {"value": e2e_value, "unit": "Mrays/s", "ms_per_step": e2e_total / args.steps,
                        "how": "the same step with nothing overlapped: upload, build, frame, read-back one after the other in one context"},
