@@ -254,3 +254,41 @@ def test_bvh_cycle_detection():
     assert not g.bvh_has_cycle(chain)
     chain["left_child"][-1] = 5
     assert g.bvh_has_cycle(chain)
+
+
+def test_bench_reference_arm_contract_on_cpu():
+    """`bench.py --impl reference` (the driver's reference arm) needs no GPU: it times the oracle port on the host
+    threads and prints ONE JSON line with the arm's keys; under torchrun only rank 0 prints.  It must not map
+    librtb200.so (scene generation comes from librtb200_host.so)."""
+    import json
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, CUDA_VISIBLE_DEVICES="")
+    child = ("import runpy, sys\n"
+             "sys.argv = ['bench.py', '--impl', 'reference', '--workload', 'c4', '--steps', '1', '--warmup', '0']\n"
+             "code = 0\n"
+             "try:\n"
+             "    runpy.run_path('bench.py', run_name='__main__')\n"
+             "except SystemExit as e:\n"
+             "    code = e.code or 0\n"
+             "maps = open('/proc/self/maps').read()\n"
+             "sys.stderr.write('MAPS_OK\\n' if 'librtb200.so' not in maps and 'librtb200_host.so' in maps else 'MAPS_BAD\\n')\n"
+             "sys.exit(code)\n")
+    out = subprocess.run([sys.executable, "-c", child], capture_output=True, text=True, env=env, cwd=root, timeout=600)
+    assert out.returncode == 0, out.stderr[-2000:]
+    assert "MAPS_OK" in out.stderr, "the reference arm mapped the CUDA library (or not the host-only one)"
+    lines = [l for l in out.stdout.splitlines() if l.startswith("{")]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    assert d["impl"] == "reference" and d["metric"] == "Mrays/s" and d["unit"] == "Mrays/s" and d["higher_is_better"] is True
+    assert d["value"] > 0 and d["n_gpus"] == 1 and d["steps"] == 1
+    assert d["cpu_baseline"]["kind"] == "port" and d["cpu_baseline"]["cores"] >= 1 and d["cpu_baseline"]["value"] == d["value"]
+    assert d["e2e"] == {"value": d["value"], "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+    assert "workload" in d["config"] and "model" not in d["config"]
+    # rank 1 of a 2-rank launch exits 0 without work or output
+    env2 = dict(env, RANK="1", WORLD_SIZE="2", LOCAL_RANK="1", MASTER_ADDR="127.0.0.1", MASTER_PORT="29599")
+    out2 = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--gpus", "2", "--workload", "c4",
+                           "--steps", "1", "--warmup", "0"], capture_output=True, text=True, env=env2, cwd=root, timeout=600)
+    assert out2.returncode == 0 and not [l for l in out2.stdout.splitlines() if l.startswith("{")]
