@@ -292,3 +292,16 @@ def test_bench_reference_arm_contract_on_cpu():
     out2 = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--gpus", "2", "--workload", "c4",
                            "--steps", "1", "--warmup", "0"], capture_output=True, text=True, env=env2, cwd=root, timeout=600)
     assert out2.returncode == 0 and not [l for l in out2.stdout.splitlines() if l.startswith("{")]
+
+
+def test_bench_product_arm_fails_loudly_without_a_gpu():
+    """The b200 arm of bench.py has no CPU fallback: without a CUDA device it exits non-zero and prints no metric line."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, CUDA_VISIBLE_DEVICES="")
+    out = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--workload", "c4", "--steps", "1", "--warmup", "0"],
+                         capture_output=True, text=True, env=env, cwd=root, timeout=600)
+    assert out.returncode != 0
+    assert not [l for l in out.stdout.splitlines() if l.startswith("{")]
