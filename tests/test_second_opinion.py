@@ -1,0 +1,86 @@
+"""The oracle (oracle/rt_oracle.cpp) against a second, independent numpy restatement of the reference shader
+(tests/py_reference.py): hit records and fp32 radiance of whole small frames must agree bit for bit, for both
+ray-generation modes, the BVH and the brute-force path, every light type, glass / metal / diffuse / invalid
+materials, an axis-aligned camera (zero direction components: the NaN behaviour of the slab test) and triangle
+indices that resolve through the bound-buffer rule."""
+import numpy as np
+import pytest
+
+import gpu_raytracer_b200 as g
+from gpu_raytracer_b200 import abi, host
+import oracle_binding as ob
+import py_reference as pr
+from test_oracle import random_soup
+
+
+def agree(bound, w, h, camera=None, wavefront=None, tpb=None):
+    kw = {} if tpb is None else dict(triangles_per_buffer=tpb)
+    if tpb is None:
+        got = ob.render(bound, w, h, camera=camera, wavefront=None if wavefront is None else (wavefront[0], wavefront[1], 7))
+    else:
+        got = ob.render_rects(bound, w, h, [(0, 0, w, h)], camera=camera, **kw)
+    want = pr.render(bound, w, h, camera=camera, wavefront=wavefront, tpb=tpb)
+    hits = got["hits"]
+    if wavefront is not None and wavefront[0] > wavefront[1]:  # nothing is traced: no hit records, a black frame
+        assert not got["radiance"].any() and not want["radiance"].any() and not hits["kind"].any()
+        return want
+    assert np.array_equal(hits["kind"], want["kind"])
+    assert np.array_equal(hits["prim"], want["prim"])
+    hit = want["kind"] != 0
+    assert np.array_equal(hits["t_bits"][hit], want["t"].view(np.uint32)[hit])
+    assert np.array_equal(hits["material_id"][hit], want["material_id"][hit])
+    assert np.array_equal(got["radiance"].view(np.uint32), want["radiance"].view(np.uint32))
+    return want
+
+
+def test_default_scene_both_modes():
+    b = ob.BoundScene(g.default_scene())
+    r = agree(b, 160, 90)
+    assert (r["kind"] == 1).any() and (r["kind"] == 2).any() and (r["kind"] == 0).any()
+    agree(b, 160, 90, wavefront=(0, 4))
+    agree(b, 33, 17, wavefront=(5, 4))  # current bounce beyond the maximum: no iteration runs, black
+
+
+def test_terrain_chunked_and_small_leaf_trees():
+    for strat in (abi.BVH_CHUNKED, abi.BVH_SMALL_LEAF):
+        b = ob.BoundScene(g.terrain_scene(24, 18, strategy=strat))
+        r = agree(b, 96, 54)
+        assert (r["kind"] == 2).sum() > 500
+        agree(b, 96, 54, wavefront=(0, 4))
+
+
+def test_soup_with_spheres_every_light_type_and_material_class():
+    s = random_soup(150, 3)
+    s.lights = np.concatenate([np.atleast_1d(s.lights),
+                               np.atleast_1d(host.light_directional([0.3, -1.0, -0.2], [1.0, 0.9, 0.8], 0.7)),
+                               np.atleast_1d(host.light_spot([1.0, 4.0, 2.0], [-0.2, -1.0, -0.5], [0.6, 0.8, 1.0], 2.5, 50.0, 0.3, 0.6)),
+                               np.atleast_1d(host.light_directional([0.0, 0.0, 0.0], [1.0, 1.0, 1.0], 1.0))])  # zero direction: NaN scrubbed by max
+    assert sorted(int(t) for t in s.lights["light_type"]) == [0, 0, 1, 2]
+    s.triangles["material_id"][::7] = 9      # inside the bound capacity: a zero material
+    s.triangles["material_id"][::11] = 200   # beyond it: magenta
+    b = ob.BoundScene(s.rebuild_bvh(abi.BVH_STANDARD))
+    r = agree(b, 120, 80)
+    assert (r["kind"] == 1).any() and (r["kind"] == 2).any()
+    agree(b, 120, 80, wavefront=(0, 4))
+
+
+def test_brute_force_without_bvh():
+    s = random_soup(60, 5)
+    s.bvh_nodes = np.zeros(0, abi.BvhNode)
+    s.triangle_indices = np.zeros(0, np.uint32)
+    agree(ob.BoundScene(s), 80, 60)
+
+
+def test_axis_aligned_camera_zero_direction_components():
+    s = g.terrain_scene(20, 16, strategy=abi.BVH_CHUNKED)
+    cam = s.camera.copy()
+    cam["position"], cam["direction"], cam["up"] = [0.3, 30.0, 0.2], [0, -1, 0], [0, 0, -1]
+    r = agree(ob.BoundScene(s), 41, 23, camera=cam)  # odd sizes: the centre column / row have cx == 0 / cy == 0 exactly
+    assert (r["kind"] == 2).any()
+
+
+def test_bound_buffer_rule_in_both_restatements():
+    s = random_soup(90, 8, with_spheres=False).rebuild_bvh(abi.BVH_STANDARD)
+    b = ob.BoundScene(s, triangles_per_buffer=40)   # three bound buffers of 40: indices 80-89 live in buffer 2
+    agree(b, 64, 48, tpb=40)
+    agree(b, 64, 48, tpb=25)                        # push constants disagree with the bound length: buffer > 2 is invalid
