@@ -341,3 +341,158 @@ def render(bound, width, height, camera=None, wavefront=None, tpb=None, triangle
     shp = (height, width)
     return dict(kind=kind.reshape(shp), prim=prim.reshape(shp), t=t.reshape(shp),
                 material_id=np.where(hit, mat, INVALID).astype(np.uint32).reshape(shp), radiance=radiance.reshape(height, width, 3))
+
+
+# ---- EXTENSION semantics (SPEC.md), restated from the SPEC text: per-sample paths with bounces ------------------------
+def closest_hit(fr, tpb, o, d):
+    """find_closest_intersection (lib.rs:174-249) for arbitrary rays -> (hit, t, point, normal, material id)."""
+    n = o[0].shape[0]
+    closest = np.full(n, F32_MAX - F(2.0), np.float32)
+    s_hit, s_t, s_idx, closest = sphere_pass(fr, o, d, closest)
+    if fr.o("bvh_nodes_count") > 0:
+        tri = bvh_pass(fr, tpb, o, d, closest)
+    else:
+        tri = brute_force_pass(fr, tpb, len(fr.tris), o, d, closest)
+    sphere_closer = s_t < tri.t
+    use_sphere = (tri.hit & s_hit & sphere_closer) | (s_hit & ~tri.hit)
+    use_tri = (tri.hit & s_hit & ~sphere_closer) | (tri.hit & ~s_hit)
+    t = np.where(use_sphere, s_t, np.where(use_tri, tri.t, F32_MAX)).astype(np.float32)
+    with np.errstate(all="ignore"):
+        point = tuple(o[k] + d[k] * t for k in range(3))
+        sb = fr.o("spheres_offset")
+        si = np.where(s_hit, s_idx, 0).astype(np.int64)
+        if fr.o("spheres_count"):
+            centre = tuple(fr.f[sb + si * 5 + k] for k in range(3))
+            s_nrm = normalize(sub(point, centre))
+            s_mat = fr.u[sb + si * 5 + 4]
+        else:
+            s_nrm, s_mat = tri.nrm, tri.mat
+    normal = tuple(np.where(use_sphere, s_nrm[k], tri.nrm[k]).astype(np.float32) for k in range(3))
+    mat = np.where(use_sphere, s_mat, tri.mat).astype(np.uint32)
+    return use_sphere | use_tri, t, point, normal, mat
+
+
+class Rng:
+    """SimpleRng (wavefront.rs:46-72) for an array of independent streams; `who` selects the streams that draw."""
+
+    def __init__(self, seed):
+        self.s = seed.astype(np.uint32)
+
+    def next_f32(self, who):
+        nxt = (self.s.astype(np.uint64) * np.uint64(1664525) + np.uint64(1013904223)).astype(np.uint32)  # wrapping
+        self.s = np.where(who, nxt, self.s)
+        return (self.s >> np.uint32(8)).astype(np.float32) / F(16777216.0)
+
+    def next_f32_signed(self, who):
+        return self.next_f32(who) * F(2.0) - F(1.0)
+
+
+def render_path(bound, width, height, spp, max_depth, base_seed, camera=None):
+    """SPEC.md steps 1-4 for every pixel.  Returns dict(accum [H, W, 4] float32, segments)."""
+    sc = bound.scene
+    fr = Frame(bound.meta, {k: bound.offsets[k] for k in bound.offsets.dtype.names}, np.ascontiguousarray(sc.triangles),
+               bound.materials, sc.camera if camera is None else camera, width, height, bound.tpb)
+    n = width * height
+    ys, xs = np.mgrid[0:height, 0:width]
+    xs, ys = xs.ravel(), ys.ravel()
+    accum = np.zeros((n, 4), np.float32)
+    segments = 0
+    everyone = np.ones(n, bool)
+    res0, res1 = F(width), F(height)
+    fov_scale = F(_libm.tanf(F(fr.cam["fov"]) * F(0.5) * F(np.pi) / F(180.0)))
+    fwd, up = vec(fr.cam["direction"]), vec(fr.cam["up"])
+    right = cross(fwd, up)
+    true_up = cross(right, fwd)
+    with np.errstate(all="ignore"):
+        for s in range(spp):
+            seed = (np.uint64((base_seed + s) & 0xFFFFFFFF) + xs.astype(np.uint64) + ys.astype(np.uint64) * np.uint64(width)).astype(np.uint32)
+            rng = Rng(seed)  # step 1
+            if s == 0:       # step 2
+                jx = jy = np.full(n, F(0.5), np.float32)
+            else:
+                jx = rng.next_f32(everyone)
+                jy = rng.next_f32(everyone)
+            u, v = (xs.astype(np.float32) + jx) / res0, (ys.astype(np.float32) + jy) / res1
+            cx = (u * F(2.0) - F(1.0)) * (res0 / res1) * fov_scale
+            cy = (F(1.0) - v * F(2.0)) * fov_scale
+            d = normalize(add(add(fwd, scale(right, cx)), scale(true_up, cy)))
+            o = tuple(np.full(n, c, np.float32) for c in vec(fr.cam["position"]))
+            tp = [np.ones(n, np.float32) for _ in range(3)]
+            L = [np.zeros(n, np.float32) for _ in range(3)]
+            alive = everyone.copy()
+            depth = 0
+            while alive.any():
+                segments += int(alive.sum())
+                hit, t, point, normal, mat = closest_hit(fr, bound.tpb, o, d)   # 3.1
+                miss = alive & ~hit
+                sky = (F(0.1), F(0.2), F(0.3))
+                for k in range(3):                                                # 3.2
+                    L[k] = np.where(miss, L[k] + sky[k] * tp[k], L[k])
+                alive &= hit
+                valid = mat < len(fr.mats)
+                mid = np.where(alive & valid, mat, 0).astype(np.uint32)
+                C = [shade(fr, point, normal, mid, ch)[ch] for ch in range(3)]    # 3.3
+                magenta = (F(1.0), F(0.0), F(1.0))
+                for k in range(3):
+                    c = np.where(valid, C[k], magenta[k])
+                    L[k] = np.where(alive, L[k] + c * tp[k], L[k])
+                alive &= valid
+                if depth == max_depth:                                            # 3.4
+                    break
+                if depth >= 3:                                                    # 3.5
+                    p = np.fmin(np.fmax(np.fmax(np.fmax(tp[0], tp[1]), tp[2]), F(0.05)), F(1.0))
+                    r = rng.next_f32(alive)
+                    alive &= ~(r > p)
+                    for k in range(3):
+                        tp[k] = np.where(alive, tp[k] / p, tp[k])
+                r0 = rng.next_f32(alive)                                          # 3.6
+                uvec = [np.zeros(n, np.float32) for _ in range(3)]
+                need = alive.copy()
+                for _ in range(8):
+                    a = rng.next_f32_signed(need)
+                    b = rng.next_f32_signed(need)
+                    c = rng.next_f32_signed(need)
+                    q = a * a + b * b + c * c
+                    ok = need & (q > F(1e-6)) & (q <= F(1.0))
+                    inv = F(1.0) / np.sqrt(q)
+                    for k, comp in enumerate((a, b, c)):
+                        uvec[k] = np.where(ok, comp * inv, uvec[k])
+                    need &= ~ok
+                cosi = dot(normal, d)                                              # 3.7
+                nf = tuple(np.where(cosi < 0, normal[k], -normal[k]) for k in range(3))
+                w = add(nf, uvec)
+                small = dot(w, w) < F(1e-8)
+                w = tuple(np.where(small, nf[k], w[k]) for k in range(3))
+                w = normalize(w)
+                m = fr.mats[mid.astype(np.int64)]                                  # 3.8
+                albedo = tuple(m["albedo"][:, k].astype(np.float32) for k in range(3))
+                mr, it = m["metallic_roughness_f16"].astype(np.uint32), m["ior_transmission_f16"].astype(np.uint32)
+                metallic, roughness = f16_to_f32(mr & 0xFFFF), f16_to_f32(mr >> 16)
+                ior, transmission = f16_to_f32(it & 0xFFFF), f16_to_f32(it >> 16)
+                T = np.fmin(np.fmax(transmission, F(0.0)), F(1.0))
+                refr = (T > 0) & (r0 < T)
+                eta = np.where(cosi < 0, F(1.0) / ior, ior)
+                c1 = -dot(d, nf)
+                kk = F(1.0) - eta * eta * (F(1.0) - c1 * c1)
+                two_dn = F(2.0) * dot(d, nf)
+                mirror = tuple(d[k] - nf[k] * two_dn for k in range(3))
+                bend = tuple(d[k] * eta + nf[k] * (eta * c1 - np.sqrt(kk)) for k in range(3))
+                tir = kk < 0
+                d_refr = normalize(tuple(np.where(tir, mirror[k], bend[k]) for k in range(3)))
+                side_refr = np.where(tir, F(1.0), F(-1.0))
+                gl = tuple(mirror[k] * (F(1.0) - roughness) + w[k] * roughness for k in range(3))
+                bad = (dot(gl, gl) < F(1e-8)) | (dot(gl, nf) <= 0)
+                d_metal = normalize(tuple(np.where(bad, w[k], gl[k]) for k in range(3)))
+                is_metal = metallic > F(0.5)
+                new_d = tuple(np.where(refr, d_refr[k], np.where(is_metal, d_metal[k], w[k])) for k in range(3))
+                side = np.where(refr, side_refr, F(1.0))
+                new_o = tuple(point[k] + nf[k] * (side * F(1e-3)) for k in range(3))
+                for k in range(3):
+                    tp[k] = np.where(alive, tp[k] * albedo[k], tp[k])
+                o = tuple(np.where(alive, new_o[k], o[k]).astype(np.float32) for k in range(3))
+                d = tuple(np.where(alive, new_d[k], d[k]).astype(np.float32) for k in range(3))
+                depth += 1
+            for k in range(3):                                                    # step 4
+                accum[:, k] = accum[:, k] + L[k]
+            accum[:, 3] = accum[:, 3] + F(1.0)
+    return dict(accum=accum.reshape(height, width, 4), segments=segments)
