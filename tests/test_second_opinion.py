@@ -100,3 +100,29 @@ def test_path_tracer_follows_the_spec_text(case):
     want = pr.render_path(b, w, h, spp, depth, 21)
     assert got["counters"]["rays"] == want["segments"]
     assert np.array_equal(got["accum"].view(np.uint32), want["accum"].view(np.uint32))
+
+
+def test_random_scenes_and_cameras_sweep():
+    """Seeded sweep: random triangle soups (with and without spheres) under the three host builders, cameras anywhere
+    around them (normalised and un-normalised forward vectors, an axis-aligned one, fov 20-100 degrees), ragged frame
+    sizes, both ray-generation modes, and a path-traced frame now and then."""
+    rng = np.random.default_rng(123)
+    for it in range(12):
+        s = random_soup(int(rng.integers(5, 200)), int(rng.integers(1, 10 ** 6)), with_spheres=bool(rng.integers(0, 2)))
+        s = s.rebuild_bvh([abi.BVH_STANDARD, abi.BVH_SMALL_LEAF, abi.BVH_CHUNKED][it % 3])
+        cam = s.camera.copy()
+        cam["position"] = rng.uniform(-6, 6, 3).astype(np.float32)
+        fwd = np.array([0, 0, -4], np.float32) + rng.uniform(-1, 1, 3).astype(np.float32) - cam["position"]
+        if it % 5 == 0:
+            fwd = np.array([0, 0, -1], np.float32)
+        cam["direction"] = fwd / np.linalg.norm(fwd) if it % 2 else fwd  # the shader uses `direction` as given
+        cam["fov"] = np.float32(rng.uniform(20, 100))
+        b = ob.BoundScene(s)
+        w, h = int(rng.integers(8, 70)), int(rng.integers(8, 50))
+        agree(b, w, h, camera=cam)
+        agree(b, w, h, camera=cam, wavefront=(0, 4))
+        if it % 4 == 0:
+            got = ob.render_path(b, w, h, spp=2, max_depth=4, base_seed=it, camera=cam)
+            want = pr.render_path(b, w, h, 2, 4, it, camera=cam)
+            assert got["counters"]["rays"] == want["segments"]
+            assert np.array_equal(got["accum"].view(np.uint32), want["accum"].view(np.uint32))
