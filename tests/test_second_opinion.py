@@ -126,3 +126,24 @@ def test_random_scenes_and_cameras_sweep():
             want = pr.render_path(b, w, h, 2, 4, it, camera=cam)
             assert got["counters"]["rays"] == want["segments"]
             assert np.array_equal(got["accum"].view(np.uint32), want["accum"].view(np.uint32))
+
+
+@pytest.mark.parametrize("name", ["default_160x90", "default_wavefront_96x54", "terrain_40x30_chunkedbvh_128x72",
+                                  "terrain_24x20_standardbvh_130x70", "cornell_96x96"])
+def test_committed_golden_vectors_are_reproduced_by_the_second_restatement(name):
+    """tests/golden/*.npz were written by the oracle (make_golden.py); the independent numpy restatement must produce
+    the same committed hit records and radiance bits, so the fixtures do not rest on one transcription alone."""
+    import os
+    import sys
+    here = os.path.dirname(os.path.abspath(__file__))
+    sys.path.insert(0, os.path.join(here, "golden"))
+    import make_golden
+    mk, w, h, wf = make_golden.CASES[name]
+    want = np.load(os.path.join(here, "golden", name + ".npz"))
+    got = pr.render(ob.BoundScene(mk()), w, h, wavefront=None if wf is None else (wf[0], wf[1]))
+    hits = want["hits"]
+    assert np.array_equal(hits["kind"], got["kind"]) and np.array_equal(hits["prim"], got["prim"])
+    hit = got["kind"] != 0
+    assert np.array_equal(hits["t_bits"][hit], got["t"].view(np.uint32)[hit])
+    assert np.array_equal(hits["material_id"][hit], got["material_id"][hit])
+    assert np.array_equal(want["radiance_bits"], got["radiance"].view(np.uint32))
